@@ -1,0 +1,419 @@
+// Persistent, warp-specialised bf16 GEMM for sm_100a:
+//   TMA (cp.async.bulk.tensor, SWIZZLE_128B)  ->  shared memory ring (mbarrier full/empty)
+//   -> tcgen05.mma (one elected thread, fp32 accumulators in TMEM, double-buffered)
+//   -> tcgen05.ld epilogue (bias + tanh/relu + cast, optional replicated "all-gather"
+//      stores to peer-mapped buffers, optional split-K red.global.add).
+//
+// Replaces the cuBLAS SGEMM calls under nn.Linear in the reference
+// (nodemodule.lua:47,65,72,95,116) and under SpatialConvolutionMM in its example
+// (cifar_example/sgd-torchad_nn-cifar.lua:91,96).  The fused epilogue replaces
+// THNN.Tanh_updateOutput (nodemodule.lua:134) and, with n_push>0, the collective that
+// follows the GEMM in MPInitialLinear/MPBaseLinear (nodemodule.lua:52,103).
+//
+// Warp roles (256 threads, 1 CTA/SM):
+//   warp 0 : TMA producer (one elected lane)
+//   warp 1 : MMA issuer   (one elected lane)
+//   warp 2 : TMEM allocator / deallocator
+//   warp 3 : idle
+//   warps 4-7 : epilogue (warp w owns TMEM lanes 32*(w%4) .. +31)
+#include "common.cuh"
+#include "sm100.cuh"
+
+#include <map>
+#include <mutex>
+#include <tuple>
+
+namespace tadnn {
+namespace {
+
+using namespace sm100;
+
+constexpr int BM = 128;
+constexpr int BK = 64;  // 64 bf16 = 128 B = one swizzle row
+constexpr int kThreads = 256;
+constexpr int kEpiThreads = 128;
+constexpr int kABytes = BM * BK * 2;
+
+template <int BN>
+struct Cfg {
+  static constexpr int kBBytes = BN * BK * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  // keep the ring <= ~200 KB
+  static constexpr int kStages = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
+  static constexpr int kSmemBytes = kStages * kStageBytes + 1024;  // +1024 alignment slack
+  static constexpr uint32_t kTmemCols = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
+};
+
+struct DevArgs {
+  int M, N, K;
+  void* C;
+  int ldc;
+  int c_fp32;
+  const float* bias;
+  int act;
+  float alpha;
+  int atomic;  // accumulate or split-K: red.global.add into fp32 C
+  int split_k;
+  int n_push;
+  void* push[8];
+  int push_ldc;
+  int push_col_offset;
+};
+
+__device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(c),
+               "f"(d)
+               : "memory");
+}
+
+__device__ __forceinline__ float apply_act(float v, int act) {
+  if (act == 1) return tanh_f32(v);
+  if (act == 2) return fmaxf(v, 0.0f);
+  return v;
+}
+
+// Store 32 consecutive output columns of one row (registers v[0..31]) into `base`
+// ([rows, ld] of bf16 or fp32), honouring N bounds.
+__device__ __forceinline__ void store_row32(void* base, int ld, int c_fp32, int row, int col0,
+                                            int N, const float (&v)[32], int atomic) {
+  const bool full = (col0 + 32 <= N);
+  if (c_fp32) {
+    float* p = reinterpret_cast<float*>(base) + static_cast<size_t>(row) * ld + col0;
+    const bool vec = full && ((reinterpret_cast<uintptr_t>(p) & 15) == 0);
+    if (atomic) {
+      if (vec) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4) red_add_v4(p + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+      } else {
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < N) atomicAdd(p + j, v[j]);
+      }
+    } else {
+      if (vec) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+          *reinterpret_cast<float4*>(p + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+      } else {
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < N) p[j] = v[j];
+      }
+    }
+  } else {
+    __nv_bfloat16* p = reinterpret_cast<__nv_bfloat16*>(base) + static_cast<size_t>(row) * ld + col0;
+    const bool vec = full && ((reinterpret_cast<uintptr_t>(p) & 15) == 0);
+    if (vec) {
+#pragma unroll
+      for (int j = 0; j < 32; j += 8) {
+        uint4 u;
+        u.x = pack_bf16x2(v[j], v[j + 1]);
+        u.y = pack_bf16x2(v[j + 2], v[j + 3]);
+        u.z = pack_bf16x2(v[j + 4], v[j + 5]);
+        u.w = pack_bf16x2(v[j + 6], v[j + 7]);
+        *reinterpret_cast<uint4*>(p + j) = u;
+      }
+    } else {
+      for (int j = 0; j < 32; ++j)
+        if (col0 + j < N) p[j] = __float2bfloat16_rn(v[j]);
+    }
+  }
+}
+
+template <bool A_MN, bool B_MN, int BN>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
+                         const __grid_constant__ CUtensorMap tma_b, const DevArgs p) {
+  using C = Cfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  // SWIZZLE_128B tiles need 1024-byte alignment.
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~static_cast<uintptr_t>(1023));
+  __shared__ __align__(8) uint64_t full_bar[C::kStages];
+  __shared__ __align__(8) uint64_t empty_bar[C::kStages];
+  __shared__ __align__(8) uint64_t tmem_full_bar[2];
+  __shared__ __align__(8) uint64_t tmem_empty_bar[2];
+  __shared__ uint32_t tmem_base_smem;
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  const int num_m = (p.M + BM - 1) / BM;
+  const int num_n = (p.N + BN - 1) / BN;
+  const int num_kb = (p.K + BK - 1) / BK;
+  const int splits = p.split_k > 1 ? p.split_k : 1;
+  const int kb_per_split = (num_kb + splits - 1) / splits;
+  const int num_work = num_m * num_n * splits;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tma_a);
+    tma_prefetch_desc(&tma_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < C::kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    for (int s = 0; s < 2; ++s) {
+      mbar_init(&tmem_full_bar[s], 1);
+      mbar_init(&tmem_empty_bar[s], kEpiThreads);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) tmem_alloc<C::kTmemCols>(&tmem_base_smem);
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
+        const int split = w % splits;
+        const int tile = w / splits;
+        const int m_blk = tile % num_m;
+        const int n_blk = tile / num_m;
+        const int kb0 = split * kb_per_split;
+        const int kb1 = min(num_kb, kb0 + kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * C::kStageBytes;
+          uint8_t* sb = sa + kABytes;
+          mbar_arrive_expect_tx(&full_bar[stage], C::kStageBytes);
+          if (!A_MN) {
+            tma_load_2d(sa, &tma_a, &full_bar[stage], kb * BK, m_blk * BM);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j)
+              tma_load_2d(sa + j * (BK * 128), &tma_a, &full_bar[stage], m_blk * BM + j * 64,
+                          kb * BK);
+          }
+          if (!B_MN) {
+            tma_load_2d(sb, &tma_b, &full_bar[stage], kb * BK, n_blk * BN);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(sb + j * (BK * 128), &tma_b, &full_bar[stage], n_blk * BN + j * 64,
+                          kb * BK);
+          }
+          if (++stage == C::kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN ? 1u : 0u, B_MN ? 1u : 0u);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
+        const int split = w % splits;
+        const int kb0 = split * kb_per_split;
+        const int kb1 = min(num_kb, kb0 + kb_per_split);
+        mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
+        tc_fence_after_sync();
+        const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * BN);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(&full_bar[stage], phase);
+          tc_fence_after_sync();
+          const uint32_t a_addr = smem_u32(smem + stage * C::kStageBytes);
+          const uint32_t b_addr = a_addr + kABytes;
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            const uint64_t da = A_MN ? make_smem_desc_sw128(a_addr + k * 2048, BK * 128, 1024)
+                                     : make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
+            const uint64_t db = B_MN ? make_smem_desc_sw128(b_addr + k * 2048, BK * 128, 1024)
+                                     : make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
+            umma_f16(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
+          if (++stage == C::kStages) {
+            stage = 0;
+            phase ^= 1;
+          }
+        }
+        umma_commit(&tmem_full_bar[acc]);  // accumulator ready for the epilogue
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4) {
+    // ===================== epilogue =====================
+    const int wg = warp & 3;  // TMEM lane quarter this warp may touch
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
+      const int tile = w / splits;
+      const int m_blk = tile % num_m;
+      const int n_blk = tile / num_m;
+      mbar_wait(&tmem_full_bar[acc], acc_phase);
+      tc_fence_after_sync();
+      const int row = m_blk * BM + wg * 32 + lane;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(wg * 32) << 16) +
+                             static_cast<uint32_t>(acc * BN);
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        const int col0 = n_blk * BN + c * 32;
+        if (col0 >= p.N) break;  // warp-uniform
+        uint32_t r[32];
+        tmem_ld_32x32b_x32(taddr + static_cast<uint32_t>(c * 32), r);
+        tmem_ld_wait();
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float x = __uint_as_float(r[j]) * p.alpha;
+          if (p.bias != nullptr && col0 + j < p.N) x += __ldg(p.bias + col0 + j);
+          v[j] = apply_act(x, p.act);
+        }
+        if (row < p.M) {
+          store_row32(p.C, p.ldc, p.c_fp32, row, col0, p.N, v, p.atomic);
+          for (int q = 0; q < p.n_push; ++q)
+            store_row32(p.push[q], p.push_ldc, p.c_fp32, row, p.push_col_offset + col0,
+                        p.push_col_offset + p.N, v, 0);
+        }
+      }
+      tc_fence_before_sync();
+      mbar_arrive(&tmem_empty_bar[acc]);
+      if (++acc == 2) {
+        acc = 0;
+        acc_phase ^= 1;
+      }
+    }
+  }
+
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after_sync();
+    tmem_dealloc<C::kTmemCols>(tmem_base);
+  }
+}
+
+// ---- host side: tensor maps -------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// 2-D bf16 tensor [rows, cols] (cols contiguous, pitch ld elements); box = 64 cols x box_rows.
+int make_tmap(CUtensorMap* out, const void* ptr, long long rows, long long cols, long long ld,
+              int box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  TADNN_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled not available from the driver");
+  TADNN_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "TMA operand %p is not 16-byte aligned", ptr);
+  TADNN_REQUIRE(ld % 8 == 0, "TMA operand pitch %lld is not a multiple of 8 bf16 elements", ld);
+  cuuint64_t gdim[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+  cuuint64_t gstr[1] = {static_cast<cuuint64_t>(ld) * 2};
+  cuuint32_t box[2] = {64u, static_cast<cuuint32_t>(box_rows)};
+  cuuint32_t estr[2] = {1u, 1u};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstr, box,
+                  estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  TADNN_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed with CUresult %d (rows=%lld cols=%lld ld=%lld box_rows=%d)",
+                static_cast<int>(r), rows, cols, ld, box_rows);
+  return 0;
+}
+
+template <bool A_MN, bool B_MN, int BN>
+int launch(const tadnn_gemm_args* a, const DevArgs& d, cudaStream_t stream) {
+  using C = Cfg<BN>;
+  CUtensorMap ta, tb;
+  int rc;
+  // K-major operand: tensor [MN, K], box 64(K) x tile rows.  MN-major: tensor [K, MN], box 64(MN) x BK.
+  rc = A_MN ? make_tmap(&ta, a->A, a->K, a->M, a->lda, BK) : make_tmap(&ta, a->A, a->M, a->K, a->lda, BM);
+  if (rc) return rc;
+  rc = B_MN ? make_tmap(&tb, a->B, a->K, a->N, a->ldb, BK) : make_tmap(&tb, a->B, a->N, a->K, a->ldb, BN);
+  if (rc) return rc;
+  auto kern = gemm_bf16_tcgen05_kernel<A_MN, B_MN, BN>;
+  static bool attr_set = false;  // per instantiation
+  if (!attr_set) {
+    TADNN_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
+    attr_set = true;
+  }
+  const int num_m = ceil_div(a->M, BM), num_n = ceil_div(a->N, BN);
+  const int splits = d.split_k > 1 ? d.split_k : 1;
+  const int work = num_m * num_n * splits;
+  const int grid = work < sm_count() ? work : sm_count();
+  kern<<<grid, kThreads, C::kSmemBytes, stream>>>(ta, tb, d);
+  TADNN_LAUNCH_CHECK("gemm_bf16_tcgen05");
+  return 0;
+}
+
+template <int BN>
+int dispatch_major(const tadnn_gemm_args* a, const DevArgs& d, cudaStream_t s) {
+  if (!a->a_mn_major && !a->b_mn_major) return launch<false, false, BN>(a, d, s);
+  if (!a->a_mn_major && a->b_mn_major) return launch<false, true, BN>(a, d, s);
+  if (a->a_mn_major && a->b_mn_major) return launch<true, true, BN>(a, d, s);
+  return launch<true, false, BN>(a, d, s);
+}
+
+}  // namespace
+}  // namespace tadnn
+
+extern "C" int tadnn_gemm_bf16(const tadnn_gemm_args* a, tadnn_stream_t stream_) {
+  using namespace tadnn;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  TADNN_REQUIRE(a != nullptr, "tadnn_gemm_bf16: null args");
+  TADNN_REQUIRE(a->M > 0 && a->N > 0 && a->K > 0, "tadnn_gemm_bf16: bad shape M=%d N=%d K=%d", a->M, a->N, a->K);
+  TADNN_REQUIRE(a->n_push >= 0 && a->n_push <= 8, "tadnn_gemm_bf16: n_push=%d out of range", a->n_push);
+  const int num_kb = ceil_div(a->K, BK);
+  int split = a->split_k > 1 ? a->split_k : 1;
+  if (split > num_kb) split = num_kb;
+  // make sure no split is empty
+  while (split > 1 && (split - 1) * ceil_div(num_kb, split) >= num_kb) --split;
+  const int atomic = (a->accumulate || split > 1) ? 1 : 0;
+  TADNN_REQUIRE(!atomic || a->c_fp32, "tadnn_gemm_bf16: accumulate/split_k need an fp32 C");
+  TADNN_REQUIRE(split == 1 || (a->bias == nullptr && a->act == 0 && a->n_push == 0),
+                "tadnn_gemm_bf16: split_k cannot be combined with bias/act/push epilogues");
+  if (split > 1 && !a->accumulate) {
+    // split-K partials are summed with red.global.add: start from zero.
+    if (a->ldc == a->N) {
+      TADNN_CHECK_CUDA(cudaMemsetAsync(a->C, 0, sizeof(float) * static_cast<size_t>(a->M) * a->N, stream));
+    } else {
+      TADNN_CHECK_CUDA(cudaMemset2DAsync(a->C, sizeof(float) * a->ldc, 0, sizeof(float) * a->N, a->M, stream));
+    }
+  }
+  DevArgs d;
+  memset(&d, 0, sizeof(d));
+  d.M = a->M; d.N = a->N; d.K = a->K;
+  d.C = a->C; d.ldc = a->ldc; d.c_fp32 = a->c_fp32;
+  d.bias = a->bias; d.act = a->act; d.alpha = a->alpha;
+  d.atomic = atomic; d.split_k = split;
+  d.n_push = a->n_push;
+  for (int i = 0; i < a->n_push; ++i) d.push[i] = a->push[i];
+  d.push_ldc = a->push_ldc; d.push_col_offset = a->push_col_offset;
+
+  int bn = a->tile_n;
+  if (bn == 0) bn = a->N <= 64 ? 64 : (a->N <= 128 ? 128 : 256);
+  switch (bn) {
+    case 64: return dispatch_major<64>(a, d, stream);
+    case 128: return dispatch_major<128>(a, d, stream);
+    case 256: return dispatch_major<256>(a, d, stream);
+    default: TADNN_REQUIRE(false, "tadnn_gemm_bf16: tile_n must be 0, 64, 128 or 256 (got %d)", bn);
+  }
+  return 0;
+}

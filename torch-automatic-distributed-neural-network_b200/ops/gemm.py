@@ -1,0 +1,61 @@
+"""tcgen05 GEMM wrapper (csrc/gemm_tcgen05.cu, ``tadnn_gemm_bf16``).
+
+``gemm_bf16`` computes ``act(alpha * A @ B^T + bias)`` on the 5th-gen tensor cores with
+the storage convention of include/tadnn.h.  Replaces the cuBLAS calls behind
+``nn.Linear`` in the reference (nodemodule.lua:47,65,72,95,116).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from .. import _native
+
+_ACT = {None: 0, "none": 0, "tanh": 1, "relu": 2}
+
+
+def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False,
+              b_mn_major: bool = False, out: torch.Tensor | None = None,
+              out_dtype: torch.dtype = torch.bfloat16, bias: torch.Tensor | None = None,
+              act: str | None = None, alpha: float = 1.0, accumulate: bool = False,
+              split_k: int = 0, push=None, push_col_offset: int = 0, push_ldc: int = 0,
+              tile_n: int = 0, stream=None) -> torch.Tensor:
+    """out[M,N] = act(alpha * A·Bᵀ + bias).
+
+    a: [M,K] (or [K,M] if a_mn_major), b: [N,K] (or [K,N] if b_mn_major); bf16, last dim
+    contiguous, row pitch a multiple of 8.  ``push`` is an optional list of raw device
+    pointers (peer-mapped buffers) that receive a copy of every output tile at column
+    offset ``push_col_offset`` (fused all-gather).
+    """
+    assert a.is_cuda and b.is_cuda and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    assert a.dim() == 2 and b.dim() == 2 and a.stride(1) == 1 and b.stride(1) == 1
+    M, K = (a.shape[1], a.shape[0]) if a_mn_major else (a.shape[0], a.shape[1])
+    N, Kb = (b.shape[1], b.shape[0]) if b_mn_major else (b.shape[0], b.shape[1])
+    assert K == Kb, f"inner dims differ: {K} vs {Kb}"
+    if out is None:
+        out = torch.empty((M, N), device=a.device, dtype=out_dtype)
+    assert out.shape == (M, N) and out.stride(1) == 1
+    assert out.dtype in (torch.bfloat16, torch.float32)
+    if bias is not None:
+        assert bias.dtype == torch.float32 and bias.numel() == N and bias.is_contiguous()
+    args = _native.GemmArgs()
+    args.M, args.N, args.K = M, N, K
+    args.A, args.lda, args.a_mn_major = a.data_ptr(), a.stride(0), int(a_mn_major)
+    args.B, args.ldb, args.b_mn_major = b.data_ptr(), b.stride(0), int(b_mn_major)
+    args.C, args.ldc, args.c_fp32 = out.data_ptr(), out.stride(0), int(out.dtype == torch.float32)
+    args.bias = _native.ptr(bias)
+    args.act = _ACT[act]
+    args.alpha = float(alpha)
+    args.accumulate = int(accumulate)
+    args.split_k = int(split_k)
+    push = list(push or [])
+    args.n_push = len(push)
+    for i, p in enumerate(push):
+        args.push[i] = int(p)
+    args.push_ldc = int(push_ldc)
+    args.push_col_offset = int(push_col_offset)
+    args.tile_n = int(tile_n)
+    rc = _native.lib().tadnn_gemm_bf16(C.byref(args), C.c_void_p(_native.stream_ptr(stream)))
+    _native.check(rc, "tadnn_gemm_bf16")
+    return out

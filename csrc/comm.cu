@@ -1,0 +1,573 @@
+// Symmetric-memory communication context and the collective kernels that run on it
+// (K1 one-shot / K2 two-shot / K3 NVLS all-reduce-average, K4 broadcast, K5 device barrier,
+//  K7 reduce-scatter, K8 all-gather).  All data movement is done by sm_100a kernels that
+// load/store peer-mapped memory over NVLink 5 / NVSwitch; there is no NCCL on this path.
+//
+// What it replaces in the reference: the TorchMPI library calls made from
+// synchronizeModel (datamodule.lua:211-224: per-tensor allreduceTensor + div), from
+// parallelize (datamodule.lua:33 synchronizeParameters, :50 barrier) and from the MP layers
+// (nodemodule.lua:52,66,103,117 allreduceTensor; :166,266 allgatherTensor).
+#include "common.cuh"
+
+#include <vector>
+
+namespace tadnn {
+
+constexpr int kMaxRanks = TADNN_COMM_MAX_RANKS;
+constexpr int kChannels = TADNN_COMM_CHANNELS;
+constexpr int kMaxBlocks = TADNN_COMM_MAX_BLOCKS;
+constexpr size_t kPadBytes = static_cast<size_t>(kChannels) * kMaxBlocks * kMaxRanks * sizeof(uint32_t);
+constexpr unsigned long long kSpinTimeoutNs = 20ull * 1000ull * 1000ull * 1000ull;  // 20 s
+
+struct CommDev {
+  uint8_t* heap[kMaxRanks];
+  uint32_t* pad[kMaxRanks];
+  uint8_t* mc_heap;  // multicast mapping of the heaps (NVLS) or nullptr
+  int rank;          // -1: single-launch emulation, rank = blockIdx.y
+  int world;
+};
+
+}  // namespace tadnn
+
+struct tadnn_comm {
+  tadnn::CommDev dev;
+  int rank = 0, world = 1;
+  int device = 0;
+  unsigned long long heap_bytes = 0;
+  void* base = nullptr;  // own allocation (heap + pad); nullptr if attached
+  bool owns = false;
+  bool local_set = false;  // created by tadnn_comm_create_local
+  std::vector<void*> opened;  // cudaIpcOpenMemHandle results to close
+};
+
+namespace tadnn {
+namespace {
+
+__device__ __forceinline__ int my_rank(const CommDev& c) {
+  return c.rank >= 0 ? c.rank : static_cast<int>(blockIdx.y);
+}
+
+__device__ __forceinline__ unsigned long long globaltimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ uint32_t cas_release_sys(uint32_t* p, uint32_t cmp, uint32_t val) {
+  uint32_t old;
+  asm volatile("atom.global.release.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(p), "r"(cmp), "r"(val) : "memory");
+  return old;
+}
+__device__ __forceinline__ uint32_t cas_acquire_sys(uint32_t* p, uint32_t cmp, uint32_t val) {
+  uint32_t old;
+  asm volatile("atom.global.acquire.sys.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(p), "r"(cmp), "r"(val) : "memory");
+  return old;
+}
+
+// K5: block b of every rank meets block b of every other rank.  Flag protocol: signal =
+// CAS(peer slot 0->1) with release, wait = CAS(own slot 1->0) with acquire; self-resetting,
+// so launches can be replayed (CUDA graphs) without host-side epochs.
+__device__ __forceinline__ void block_barrier(const CommDev& c, int channel) {
+  __syncthreads();
+  if (threadIdx.x < c.world) {
+    const int rank = my_rank(c);
+    const int peer = threadIdx.x;
+    const size_t slot = (static_cast<size_t>(channel) * kMaxBlocks + blockIdx.x) * kMaxRanks;
+    uint32_t* remote = c.pad[peer] + slot + rank;
+    uint32_t* local = c.pad[rank] + slot + peer;
+    __threadfence_system();
+    const unsigned long long t0 = globaltimer_ns();
+    while (cas_release_sys(remote, 0u, 1u) != 0u) {
+      if (globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();  // dead peer: fail, do not hang
+    }
+    while (cas_acquire_sys(local, 1u, 0u) != 1u) {
+      if (globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ uint4 ld_peer16(const void* p) {
+  uint4 v;
+  asm volatile("ld.volatile.global.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_peer16(void* p, const uint4& v) {
+  asm volatile("st.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+template <int DT>
+struct Vec;
+template <>
+struct Vec<0> {  // fp32 x4
+  static constexpr int kN = 4;
+  __device__ static void add(float (&a)[8], const uint4& v) {
+    a[0] += __uint_as_float(v.x); a[1] += __uint_as_float(v.y);
+    a[2] += __uint_as_float(v.z); a[3] += __uint_as_float(v.w);
+  }
+  __device__ static uint4 pack(const float (&a)[8], float s) {
+    return make_uint4(__float_as_uint(a[0] * s), __float_as_uint(a[1] * s), __float_as_uint(a[2] * s), __float_as_uint(a[3] * s));
+  }
+};
+template <>
+struct Vec<1> {  // bf16 x8, fp32 accumulation
+  static constexpr int kN = 8;
+  __device__ static void add(float (&a)[8], const uint4& v) {
+    float2 f;
+    f = unpack_bf16x2(v.x); a[0] += f.x; a[1] += f.y;
+    f = unpack_bf16x2(v.y); a[2] += f.x; a[3] += f.y;
+    f = unpack_bf16x2(v.z); a[4] += f.x; a[5] += f.y;
+    f = unpack_bf16x2(v.w); a[6] += f.x; a[7] += f.y;
+  }
+  __device__ static uint4 pack(const float (&a)[8], float s) {
+    return make_uint4(pack_bf16x2(a[0] * s, a[1] * s), pack_bf16x2(a[2] * s, a[3] * s),
+                      pack_bf16x2(a[4] * s, a[5] * s), pack_bf16x2(a[6] * s, a[7] * s));
+  }
+};
+
+// ---- K1: one-shot ----------------------------------------------------------
+// Every rank reads all P copies of every element, sums in rank order (fp32), scales,
+// and -- after a second barrier, so nobody is still reading -- overwrites its own copy.
+template <int DT>
+__global__ void __launch_bounds__(512) allreduce_oneshot_kernel(CommDev c, size_t off, size_t nvec, float scale, int channel) {
+  constexpr int U = 2;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const size_t tid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int rank = my_rank(c);
+  block_barrier(c, channel);
+  for (size_t base = 0; base < nvec; base += stride * U) {
+    uint4 out[U];
+    uint4 v[U][kMaxRanks];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = base + tid + u * stride;
+      if (i < nvec) {
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r)
+          if (r < c.world) v[u][r] = ld_peer16(c.heap[r] + off + i * 16);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+      for (int r = 0; r < kMaxRanks; ++r)
+        if (r < c.world) Vec<DT>::add(a, v[u][r]);
+      out[u] = Vec<DT>::pack(a, scale);
+    }
+    block_barrier(c, channel);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = base + tid + u * stride;
+      if (i < nvec) *reinterpret_cast<uint4*>(c.heap[rank] + off + i * 16) = out[u];
+    }
+  }
+}
+
+// ---- K2: two-shot ----------------------------------------------------------
+// Rank r owns chunk r: it pulls that chunk from all P heaps, reduces, scales and pushes the
+// result into chunk r of all P heaps.  In place and race-free: only rank r ever touches chunk r.
+template <int DT>
+__global__ void __launch_bounds__(512) allreduce_twoshot_kernel(CommDev c, size_t off, size_t nvec, float scale, int channel) {
+  constexpr int U = 2;
+  const int rank = my_rank(c);
+  const size_t chunk = (nvec + c.world - 1) / c.world;
+  const size_t lo = min(nvec, chunk * rank), hi = min(nvec, lo + chunk);
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const size_t tid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  block_barrier(c, channel);
+  for (size_t base = lo; base < hi; base += stride * U) {
+    uint4 v[U][kMaxRanks];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = base + tid + u * stride;
+      if (i < hi) {
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r)
+          if (r < c.world) v[u][r] = ld_peer16(c.heap[r] + off + i * 16);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = base + tid + u * stride;
+      if (i < hi) {
+        float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r)
+          if (r < c.world) Vec<DT>::add(a, v[u][r]);
+        const uint4 o = Vec<DT>::pack(a, scale);
+#pragma unroll
+        for (int r = 0; r < kMaxRanks; ++r)
+          if (r < c.world) st_peer16(c.heap[r] + off + i * 16, o);
+      }
+    }
+  }
+  block_barrier(c, channel);
+}
+
+// ---- K3: NVLS (multimem) ---------------------------------------------------
+// The switch reduces: one multimem.ld_reduce of the multicast address returns the sum over
+// all ranks, one multimem.st broadcasts the result.  Rank r handles chunk r.
+template <int DT>
+__global__ void __launch_bounds__(512) allreduce_nvls_kernel(CommDev c, size_t off, size_t nvec, float scale, int channel) {
+  const int rank = my_rank(c);
+  const size_t chunk = (nvec + c.world - 1) / c.world;
+  const size_t lo = min(nvec, chunk * rank), hi = min(nvec, lo + chunk);
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  block_barrier(c, channel);
+  for (size_t i = lo + static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < hi; i += stride) {
+    uint8_t* p = c.mc_heap + off + i * 16;
+    if (DT == 0) {
+      float a, b, d, e;
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(a), "=f"(b), "=f"(d), "=f"(e) : "l"(p) : "memory");
+      a *= scale; b *= scale; d *= scale; e *= scale;
+      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(d), "f"(e) : "memory");
+    } else {
+      uint32_t x, y, z, w;
+      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];" : "=r"(x), "=r"(y), "=r"(z), "=r"(w) : "l"(p) : "memory");
+      float2 f;
+      f = unpack_bf16x2(x); x = pack_bf16x2(f.x * scale, f.y * scale);
+      f = unpack_bf16x2(y); y = pack_bf16x2(f.x * scale, f.y * scale);
+      f = unpack_bf16x2(z); z = pack_bf16x2(f.x * scale, f.y * scale);
+      f = unpack_bf16x2(w); w = pack_bf16x2(f.x * scale, f.y * scale);
+      asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
+    }
+  }
+  block_barrier(c, channel);
+}
+
+// ---- tail (< 16 B) handled by a scalar one-shot on a single block -----------
+template <int DT>
+__global__ void allreduce_tail_kernel(CommDev c, size_t off_bytes, int n, float scale, int channel) {
+  const int rank = my_rank(c);
+  block_barrier(c, channel);
+  float acc = 0.f;
+  if (static_cast<int>(threadIdx.x) < n) {
+    for (int r = 0; r < c.world; ++r) {
+      if (DT == 0) acc += *reinterpret_cast<volatile float*>(c.heap[r] + off_bytes + threadIdx.x * 4);
+      else acc += __bfloat162float(*reinterpret_cast<volatile __nv_bfloat16*>(c.heap[r] + off_bytes + threadIdx.x * 2));
+    }
+  }
+  block_barrier(c, channel);
+  if (static_cast<int>(threadIdx.x) < n) {
+    if (DT == 0) *reinterpret_cast<float*>(c.heap[rank] + off_bytes + threadIdx.x * 4) = acc * scale;
+    else *reinterpret_cast<__nv_bfloat16*>(c.heap[rank] + off_bytes + threadIdx.x * 2) = __float2bfloat16_rn(acc * scale);
+  }
+}
+
+__global__ void barrier_kernel(CommDev c, int channel) { block_barrier(c, channel); }
+
+// ---- K4: broadcast (root pushes) ------------------------------------------
+__global__ void __launch_bounds__(512) broadcast_kernel(CommDev c, size_t off, size_t nvec, size_t tail_off, int tail_bytes, int root, int channel) {
+  const int rank = my_rank(c);
+  block_barrier(c, channel);
+  if (rank == root) {
+    const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+    for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < nvec; i += stride) {
+      const uint4 v = *reinterpret_cast<const uint4*>(c.heap[rank] + off + i * 16);
+      for (int r = 0; r < c.world; ++r)
+        if (r != rank) st_peer16(c.heap[r] + off + i * 16, v);
+    }
+    if (blockIdx.x == 0 && static_cast<int>(threadIdx.x) < tail_bytes) {
+      const uint8_t b = c.heap[rank][tail_off + threadIdx.x];
+      for (int r = 0; r < c.world; ++r)
+        if (r != rank) c.heap[r][tail_off + threadIdx.x] = b;
+    }
+  }
+  block_barrier(c, channel);
+}
+
+// ---- K8: all-gather along the last dim (push) -----------------------------
+template <typename V>
+__global__ void __launch_bounds__(512) allgather_cols_kernel(CommDev c, const uint8_t* src, size_t src_pitch, size_t off, int rows, size_t width_v /* in V units */, int channel) {
+  const int rank = my_rank(c);
+  const size_t total = static_cast<size_t>(rows) * width_v;
+  const size_t out_pitch = width_v * sizeof(V) * c.world;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  block_barrier(c, channel);
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const size_t row = i / width_v, col = i - row * width_v;
+    const V v = *reinterpret_cast<const V*>(src + row * src_pitch + col * sizeof(V));
+    const size_t o = off + row * out_pitch + (static_cast<size_t>(rank) * width_v + col) * sizeof(V);
+    for (int r = 0; r < c.world; ++r) *reinterpret_cast<V*>(c.heap[r] + o) = v;
+  }
+  block_barrier(c, channel);
+}
+
+// ---- K7: reduce-scatter along the last dim (pull) with fused bias + act ----
+template <int DT>
+__global__ void __launch_bounds__(512) reduce_scatter_cols_kernel(CommDev c, size_t off, void* dst, size_t dst_pitch, int rows, int width, float scale, const float* bias, int act, int channel) {
+  const int rank = my_rank(c);
+  const size_t es = DT == 0 ? 4 : 2;
+  const size_t total = static_cast<size_t>(rows) * width;
+  const size_t in_pitch = static_cast<size_t>(width) * c.world * es;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  block_barrier(c, channel);
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const size_t row = i / width, col = i - row * width;
+    const size_t o = off + row * in_pitch + (static_cast<size_t>(rank) * width + col) * es;
+    float acc = 0.f;
+    for (int r = 0; r < c.world; ++r) {
+      if (DT == 0) acc += *reinterpret_cast<volatile float*>(c.heap[r] + o);
+      else acc += __bfloat162float(*reinterpret_cast<volatile __nv_bfloat16*>(c.heap[r] + o));
+    }
+    acc *= scale;
+    if (bias != nullptr) acc += bias[static_cast<size_t>(rank) * width + col];
+    if (act == 1) acc = tanh_f32(acc);
+    else if (act == 2) acc = fmaxf(acc, 0.f);
+    if (DT == 0) reinterpret_cast<float*>(dst)[row * dst_pitch + col] = acc;
+    else reinterpret_cast<__nv_bfloat16*>(dst)[row * dst_pitch + col] = __float2bfloat16_rn(acc);
+  }
+  block_barrier(c, channel);
+}
+
+int pick_blocks(size_t work_items_per_thread_1, int max_blocks, int cap_default) {
+  int cap = max_blocks > 0 ? max_blocks : cap_default;
+  if (cap > kMaxBlocks) cap = kMaxBlocks;
+  long long need = static_cast<long long>((work_items_per_thread_1 + 511) / 512);
+  if (need < 1) need = 1;
+  return need < cap ? static_cast<int>(need) : cap;
+}
+
+int validate(const tadnn_comm* c, int channel, const char* what) {
+  TADNN_REQUIRE(c != nullptr, "%s: null comm", what);
+  TADNN_REQUIRE(channel >= 0 && channel < kChannels, "%s: channel %d out of range [0,%d)", what, channel, kChannels);
+  TADNN_REQUIRE(!c->local_set || c->dev.rank < 0, "%s: a local (single-GPU) comm set can only be used through the *_emulated entry points", what);
+  return 0;
+}
+
+template <typename K, typename... Args>
+int launch_maybe_coop(const CommDev& dev, K kern, int blocks, int threads, cudaStream_t stream, const char* name, Args... args) {
+  if (dev.rank >= 0) {
+    kern<<<blocks, threads, 0, stream>>>(args...);
+  } else {
+    // emulation: all ranks in ONE cooperative launch (co-residency guaranteed or the launch fails)
+    void* params[] = {(void*)&args...};
+    dim3 grid(blocks, dev.world, 1);
+    cudaError_t e = cudaLaunchCooperativeKernel((const void*)kern, grid, dim3(threads, 1, 1), params, 0, stream);
+    if (e != cudaSuccess) {
+      set_error("cooperative launch of %s (%d x %d blocks) failed: %s", name, blocks, dev.world, cudaGetErrorString(e));
+      return 3;
+    }
+  }
+  TADNN_LAUNCH_CHECK(name);
+  return 0;
+}
+
+int do_allreduce(const CommDev& dev, bool has_mc, unsigned long long off_bytes, unsigned long long count, int dtype, float scale, int algo, int max_blocks, int channel, cudaStream_t stream) {
+  TADNN_REQUIRE(dtype == 0 || dtype == 1, "allreduce: dtype must be 0 (fp32) or 1 (bf16)");
+  TADNN_REQUIRE(off_bytes % 16 == 0, "allreduce: offset %llu is not 16-byte aligned", off_bytes);
+  if (count == 0) return 0;
+  const size_t es = dtype == 0 ? 4 : 2;
+  const size_t per_vec = 16 / es;
+  const size_t nvec = count / per_vec;
+  const int tail = static_cast<int>(count - nvec * per_vec);
+  const size_t bytes = count * es;
+  if (algo == 0) {
+    // one-shot moves (P-1)*S per rank but has the shortest critical path; two-shot / NVLS
+    // move ~2(P-1)/P*S.  Crossover measured on NVSwitch sits at a few hundred KB.
+    if (bytes <= (512u << 10)) algo = 1;
+    else algo = has_mc ? 3 : 2;
+  }
+  TADNN_REQUIRE(algo >= 1 && algo <= 3, "allreduce: unknown algo %d", algo);
+  TADNN_REQUIRE(algo != 3 || has_mc, "allreduce: NVLS requested but this context has no multicast mapping");
+  const bool emu = dev.rank < 0;
+  int rc = 0;
+  if (nvec > 0) {
+    if (algo == 1) {
+      const int blocks = pick_blocks((nvec + 1) / 2, emu ? (max_blocks > 0 ? max_blocks : 8) : max_blocks, 64);
+      rc = dtype == 0 ? launch_maybe_coop(dev, allreduce_oneshot_kernel<0>, blocks, 512, stream, "allreduce_oneshot_f32", dev, (size_t)off_bytes, nvec, scale, channel)
+                      : launch_maybe_coop(dev, allreduce_oneshot_kernel<1>, blocks, 512, stream, "allreduce_oneshot_bf16", dev, (size_t)off_bytes, nvec, scale, channel);
+    } else if (algo == 2) {
+      const int blocks = pick_blocks((nvec / dev.world + 1) / 2 + 1, emu ? (max_blocks > 0 ? max_blocks : 8) : max_blocks, 128);
+      rc = dtype == 0 ? launch_maybe_coop(dev, allreduce_twoshot_kernel<0>, blocks, 512, stream, "allreduce_twoshot_f32", dev, (size_t)off_bytes, nvec, scale, channel)
+                      : launch_maybe_coop(dev, allreduce_twoshot_kernel<1>, blocks, 512, stream, "allreduce_twoshot_bf16", dev, (size_t)off_bytes, nvec, scale, channel);
+    } else {
+      const int blocks = pick_blocks(nvec / dev.world + 1, max_blocks, 64);
+      rc = dtype == 0 ? launch_maybe_coop(dev, allreduce_nvls_kernel<0>, blocks, 512, stream, "allreduce_nvls_f32", dev, (size_t)off_bytes, nvec, scale, channel)
+                      : launch_maybe_coop(dev, allreduce_nvls_kernel<1>, blocks, 512, stream, "allreduce_nvls_bf16", dev, (size_t)off_bytes, nvec, scale, channel);
+    }
+    if (rc) return rc;
+  }
+  if (tail > 0) {
+    const size_t toff = off_bytes + nvec * 16;
+    rc = dtype == 0 ? launch_maybe_coop(dev, allreduce_tail_kernel<0>, 1, 32, stream, "allreduce_tail_f32", dev, toff, tail, scale, channel)
+                    : launch_maybe_coop(dev, allreduce_tail_kernel<1>, 1, 32, stream, "allreduce_tail_bf16", dev, toff, tail, scale, channel);
+  }
+  return rc;
+}
+
+}  // namespace
+}  // namespace tadnn
+
+using namespace tadnn;
+
+extern "C" int tadnn_comm_create(int rank, int world, unsigned long long heap_bytes, tadnn_comm** out) {
+  TADNN_REQUIRE(out != nullptr, "comm_create: null out");
+  TADNN_REQUIRE(world >= 1 && world <= kMaxRanks, "comm_create: world %d not in [1,%d]", world, kMaxRanks);
+  TADNN_REQUIRE(rank >= 0 && rank < world, "comm_create: rank %d not in [0,%d)", rank, world);
+  heap_bytes = (heap_bytes + 1023ull) & ~1023ull;
+  tadnn_comm* c = new tadnn_comm();
+  c->rank = rank; c->world = world; c->heap_bytes = heap_bytes;
+  TADNN_CHECK_CUDA(cudaGetDevice(&c->device));
+  TADNN_CHECK_CUDA(cudaMalloc(&c->base, heap_bytes + kPadBytes));
+  TADNN_CHECK_CUDA(cudaMemset(static_cast<uint8_t*>(c->base) + heap_bytes, 0, kPadBytes));
+  TADNN_CHECK_CUDA(cudaDeviceSynchronize());
+  c->owns = true;
+  memset(&c->dev, 0, sizeof(c->dev));
+  c->dev.rank = rank; c->dev.world = world;
+  c->dev.heap[rank] = static_cast<uint8_t*>(c->base);
+  c->dev.pad[rank] = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(c->base) + heap_bytes);
+  *out = c;
+  return 0;
+}
+
+extern "C" int tadnn_comm_create_local(int world, unsigned long long heap_bytes, tadnn_comm** out) {
+  TADNN_REQUIRE(out != nullptr, "comm_create_local: null out");
+  TADNN_REQUIRE(world >= 1 && world <= kMaxRanks, "comm_create_local: world %d not in [1,%d]", world, kMaxRanks);
+  for (int r = 0; r < world; ++r) {
+    int rc = tadnn_comm_create(r, world, heap_bytes, &out[r]);
+    if (rc) return rc;
+    out[r]->local_set = true;
+  }
+  for (int r = 0; r < world; ++r)
+    for (int q = 0; q < world; ++q) {
+      out[r]->dev.heap[q] = out[q]->dev.heap[q];
+      out[r]->dev.pad[q] = out[q]->dev.pad[q];
+    }
+  return 0;
+}
+
+extern "C" int tadnn_comm_ipc_handle(tadnn_comm* c, void* host_out64) {
+  TADNN_REQUIRE(c && c->owns, "comm_ipc_handle: context does not own its heap");
+  static_assert(sizeof(cudaIpcMemHandle_t) == TADNN_IPC_HANDLE_BYTES, "IPC handle size");
+  cudaIpcMemHandle_t h;
+  TADNN_CHECK_CUDA(cudaIpcGetMemHandle(&h, c->base));
+  memcpy(host_out64, &h, sizeof(h));
+  return 0;
+}
+
+extern "C" int tadnn_comm_open_peers(tadnn_comm* c, const void* host_all_handles) {
+  TADNN_REQUIRE(c && host_all_handles, "comm_open_peers: null argument");
+  const uint8_t* hs = static_cast<const uint8_t*>(host_all_handles);
+  for (int r = 0; r < c->world; ++r) {
+    if (r == c->rank) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, hs + static_cast<size_t>(r) * TADNN_IPC_HANDLE_BYTES, sizeof(h));
+    void* p = nullptr;
+    TADNN_CHECK_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    c->opened.push_back(p);
+    c->dev.heap[r] = static_cast<uint8_t*>(p);
+    c->dev.pad[r] = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(p) + c->heap_bytes);
+  }
+  return 0;
+}
+
+extern "C" int tadnn_comm_attach(tadnn_comm* c, void* const* heaps, void* const* pads, void* multicast_heap) {
+  TADNN_REQUIRE(c != nullptr, "comm_attach: null comm");
+  for (int r = 0; r < c->world; ++r) {
+    if (heaps && heaps[r]) c->dev.heap[r] = static_cast<uint8_t*>(heaps[r]);
+    if (pads && pads[r]) c->dev.pad[r] = static_cast<uint32_t*>(pads[r]);
+  }
+  c->dev.mc_heap = static_cast<uint8_t*>(multicast_heap);
+  return 0;
+}
+
+extern "C" int tadnn_comm_heap(tadnn_comm* c, int peer, void** out_ptr) {
+  TADNN_REQUIRE(c && out_ptr && peer >= 0 && peer < c->world, "comm_heap: bad argument");
+  *out_ptr = c->dev.heap[peer];
+  return 0;
+}
+
+extern "C" int tadnn_comm_info(tadnn_comm* c, int* rank, int* world, unsigned long long* heap_bytes, int* has_mc) {
+  TADNN_REQUIRE(c != nullptr, "comm_info: null comm");
+  if (rank) *rank = c->rank;
+  if (world) *world = c->world;
+  if (heap_bytes) *heap_bytes = c->heap_bytes;
+  if (has_mc) *has_mc = c->dev.mc_heap != nullptr;
+  return 0;
+}
+
+extern "C" int tadnn_comm_destroy(tadnn_comm* c) {
+  if (c == nullptr) return 0;
+  cudaDeviceSynchronize();
+  for (void* p : c->opened) cudaIpcCloseMemHandle(p);
+  if (c->owns && c->base) cudaFree(c->base);
+  delete c;
+  return 0;
+}
+
+extern "C" int tadnn_barrier(tadnn_comm* c, int channel, tadnn_stream_t stream) {
+  if (int rc = validate(c, channel, "barrier")) return rc;
+  if (c->world == 1) return 0;
+  barrier_kernel<<<1, 32, 0, static_cast<cudaStream_t>(stream)>>>(c->dev, channel);
+  TADNN_LAUNCH_CHECK("device_barrier");
+  return 0;
+}
+
+extern "C" int tadnn_allreduce(tadnn_comm* c, unsigned long long off_bytes, unsigned long long count, int dtype, float scale, int algo, int max_blocks, int channel, tadnn_stream_t stream) {
+  if (int rc = validate(c, channel, "allreduce")) return rc;
+  const unsigned long long es = dtype == 0 ? 4 : 2;
+  TADNN_REQUIRE(off_bytes + count * es <= c->heap_bytes, "allreduce: [%llu, +%llu) exceeds the %llu-byte heap", off_bytes, count * es, c->heap_bytes);
+  return do_allreduce(c->dev, c->dev.mc_heap != nullptr, off_bytes, count, dtype, scale, algo, max_blocks, channel, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int tadnn_allreduce_emulated(tadnn_comm* const* comms, int world, unsigned long long off_bytes, unsigned long long count, int dtype, float scale, int algo, tadnn_stream_t stream) {
+  TADNN_REQUIRE(comms && world >= 1 && world <= kMaxRanks, "allreduce_emulated: bad arguments");
+  TADNN_REQUIRE(algo == 1 || algo == 2, "allreduce_emulated: algo must be 1 (one-shot) or 2 (two-shot)");
+  CommDev dev = comms[0]->dev;
+  dev.rank = -1;
+  dev.world = world;
+  return do_allreduce(dev, false, off_bytes, count, dtype, scale, algo, 8, 0, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int tadnn_broadcast(tadnn_comm* c, unsigned long long off_bytes, unsigned long long bytes, int root, int max_blocks, int channel, tadnn_stream_t stream) {
+  if (int rc = validate(c, channel, "broadcast")) return rc;
+  TADNN_REQUIRE(root >= 0 && root < c->world, "broadcast: root %d out of range", root);
+  TADNN_REQUIRE(off_bytes % 16 == 0, "broadcast: offset not 16-byte aligned");
+  TADNN_REQUIRE(off_bytes + bytes <= c->heap_bytes, "broadcast: range exceeds the heap");
+  if (c->world == 1 || bytes == 0) return 0;
+  const size_t nvec = bytes / 16;
+  const int tail = static_cast<int>(bytes - nvec * 16);
+  const int blocks = pick_blocks(nvec / 4 + 1, max_blocks, 64);
+  broadcast_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(c->dev, off_bytes, nvec, off_bytes + nvec * 16, tail, root, channel);
+  TADNN_LAUNCH_CHECK("broadcast_flat");
+  return 0;
+}
+
+extern "C" int tadnn_allgather_cols(tadnn_comm* c, const void* src, unsigned long long src_pitch, unsigned long long off_bytes, int rows, unsigned long long width_bytes, int max_blocks, int channel, tadnn_stream_t stream_) {
+  if (int rc = validate(c, channel, "allgather_cols")) return rc;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  TADNN_REQUIRE(rows > 0 && width_bytes > 0, "allgather_cols: empty");
+  TADNN_REQUIRE(off_bytes + static_cast<unsigned long long>(rows) * width_bytes * c->world <= c->heap_bytes, "allgather_cols: output exceeds the heap");
+  const uintptr_t a = reinterpret_cast<uintptr_t>(src) | src_pitch | off_bytes | width_bytes;
+  const uint8_t* s = static_cast<const uint8_t*>(src);
+  if (a % 16 == 0) {
+    const size_t wv = width_bytes / 16;
+    allgather_cols_kernel<uint4><<<pick_blocks(rows * wv / 2 + 1, max_blocks, 64), 512, 0, stream>>>(c->dev, s, src_pitch, off_bytes, rows, wv, channel);
+  } else if (a % 4 == 0) {
+    const size_t wv = width_bytes / 4;
+    allgather_cols_kernel<uint32_t><<<pick_blocks(rows * wv / 2 + 1, max_blocks, 64), 512, 0, stream>>>(c->dev, s, src_pitch, off_bytes, rows, wv, channel);
+  } else {
+    TADNN_REQUIRE(a % 2 == 0, "allgather_cols: operands must be at least 2-byte aligned");
+    const size_t wv = width_bytes / 2;
+    allgather_cols_kernel<uint16_t><<<pick_blocks(rows * wv / 2 + 1, max_blocks, 64), 512, 0, stream>>>(c->dev, s, src_pitch, off_bytes, rows, wv, channel);
+  }
+  TADNN_LAUNCH_CHECK("allgather_cols");
+  return 0;
+}
+
+extern "C" int tadnn_reduce_scatter_cols(tadnn_comm* c, unsigned long long off_bytes, void* dst, unsigned long long dst_pitch, int rows, int width, int dtype, float scale, const float* bias, int act, int max_blocks, int channel, tadnn_stream_t stream_) {
+  if (int rc = validate(c, channel, "reduce_scatter_cols")) return rc;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  TADNN_REQUIRE(dtype == 0 || dtype == 1, "reduce_scatter_cols: dtype must be 0 or 1");
+  TADNN_REQUIRE(rows > 0 && width > 0, "reduce_scatter_cols: empty");
+  const unsigned long long es = dtype == 0 ? 4 : 2;
+  TADNN_REQUIRE(off_bytes + static_cast<unsigned long long>(rows) * width * c->world * es <= c->heap_bytes, "reduce_scatter_cols: input exceeds the heap");
+  const int blocks = pick_blocks(static_cast<size_t>(rows) * width / 2 + 1, max_blocks, 128);
+  if (dtype == 0)
+    reduce_scatter_cols_kernel<0><<<blocks, 512, 0, stream>>>(c->dev, off_bytes, dst, dst_pitch, rows, width, scale, bias, act, channel);
+  else
+    reduce_scatter_cols_kernel<1><<<blocks, 512, 0, stream>>>(c->dev, off_bytes, dst, dst_pitch, rows, width, scale, bias, act, channel);
+  TADNN_LAUNCH_CHECK("reduce_scatter_cols");
+  return 0;
+}

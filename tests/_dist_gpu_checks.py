@@ -1,0 +1,134 @@
+"""Multi-GPU numerics worker (launched by torchrun from test_gpu_multigpu.py or by hand):
+
+    python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 tests/_dist_gpu_checks.py
+
+Checks every collective kernel of csrc/comm.cu against a plain PyTorch fp32 reference
+computed from NCCL all_gather'ed inputs, then prints one JSON line from rank 0.
+"""
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import tadnn.mpi as mpi  # noqa: E402
+from tadnn.parallel import symm as S  # noqa: E402
+
+
+def gather_all(t):
+    parts = [torch.empty_like(t) for _ in range(dist.get_world_size())]
+    dist.all_gather(parts, t.contiguous())
+    return parts
+
+
+def main():
+    h = mpi.start(True)
+    ctx = h.symm
+    assert ctx is not None, "symmetric context not created"
+    rank, P = h.rank(), h.size()
+    dev = ctx.device
+    fails = []
+    checks = 0
+    torch.manual_seed(1234 + rank)
+
+    def expect(name, got, ref, tol):
+        nonlocal checks
+        checks += 1
+        err = (got.float() - ref.float()).abs().max().item()
+        lim = tol * max(1.0, ref.float().abs().max().item())
+        if not (err <= lim):
+            fails.append(f"{name}: err {err:.3e} > {lim:.3e}")
+
+    # ---- all-reduce, in heap, every algo/dtype/size (incl. odd sizes and tails)
+    big = ctx.empty((1 << 24,), torch.float32)  # 64 MB region reused for all sizes
+    for dtype in (torch.float32, torch.bfloat16):
+        for n in (1, 3, 10, 64, 1000, 4099, 65536, 114838 * 2, 1 << 20, (1 << 22) + 5):
+            for algo in (1, 2):
+                if algo == 1 and n > (1 << 20):
+                    continue
+                view = big.view(dtype)[:n]
+                x = torch.randn(n, device=dev).to(dtype)
+                view.copy_(x)
+                parts = gather_all(x)
+                ref = torch.stack([p.float() for p in parts]).sum(0) / P
+                ctx.allreduce_(view, scale=1.0 / P, algo=algo)
+                torch.cuda.synchronize()
+                expect(f"allreduce n={n} {dtype} algo={algo}", view, ref, 1e-5 if dtype == torch.float32 else 8e-3)
+                # bit-identical across ranks
+                got_all = gather_all(view.clone())
+                if any(not torch.equal(got_all[0], g) for g in got_all):
+                    fails.append(f"allreduce n={n} {dtype} algo={algo}: ranks disagree bitwise")
+    # repeated launches back-to-back (flag reuse without host sync)
+    view = big[:50000]
+    x = torch.randn(50000, device=dev)
+    view.copy_(x)
+    for _ in range(200):
+        ctx.allreduce_(view, scale=1.0 / P, algo=1)
+    for _ in range(200):
+        ctx.allreduce_(view, scale=1.0 / P, algo=2)
+    torch.cuda.synchronize()
+    parts = gather_all(x)
+    expect("allreduce x400 (mean is idempotent after the first)", view, torch.stack(parts).sum(0) / P, 1e-4)
+
+    # ---- staged path (tensor outside the heap) through the TorchMPI-shaped API
+    y = torch.randn(777, 33, device=dev)
+    ref = torch.stack(gather_all(y)).sum(0)
+    h.allreduceTensor(y)
+    torch.cuda.synchronize()
+    expect("mpi.allreduceTensor staged", y, ref, 1e-5)
+
+    # ---- broadcast
+    reg = ctx.empty((100003,), torch.float32)
+    reg.copy_(torch.full((100003,), float(rank + 1), device=dev))
+    off = ctx.offset_of(reg)
+    for root in range(P):
+        reg.fill_(float(rank + 1))
+        torch.cuda.synchronize()
+        dist.barrier()
+        ctx.broadcast_offset(off, reg.numel() * 4, root=root)
+        torch.cuda.synchronize()
+        expect(f"broadcast root={root}", reg, torch.full_like(reg, float(root + 1)), 0.0)
+
+    # ---- all-gather along last dim
+    for (rows, w, dtype) in ((1, 256, torch.float32), (37, 10, torch.float32), (128, 2048, torch.bfloat16), (5, 3, torch.bfloat16)):
+        inp = torch.randn(rows, w, device=dev).to(dtype)
+        out = torch.empty(rows, w * P, device=dev, dtype=dtype)
+        ref = torch.cat(gather_all(inp), dim=-1)
+        h.allgatherTensor(inp, out)
+        torch.cuda.synchronize()
+        expect(f"allgather {rows}x{w} {dtype}", out, ref, 0.0)
+
+    # ---- reduce-scatter along last dim with fused bias + tanh
+    for (rows, w, dtype) in ((64, 256, torch.float32), (33, 40, torch.bfloat16)):
+        full = torch.randn(rows, w * P, device=dev).to(dtype)
+        reg2 = ctx.empty((rows, w * P), dtype)
+        reg2.copy_(full)
+        bias = torch.randn(w * P, device=dev)
+        dst = torch.empty(rows, w, device=dev, dtype=dtype)
+        allp = gather_all(full)
+        ref = torch.tanh(torch.stack([p.float() for p in allp]).sum(0)[:, rank * w:(rank + 1) * w] * 0.5 + bias[rank * w:(rank + 1) * w])
+        torch.cuda.synchronize()
+        dist.barrier()
+        ctx.reduce_scatter_cols_offset(ctx.offset_of(reg2), dst, scale=0.5, bias=bias, act=1)
+        torch.cuda.synchronize()
+        expect(f"reduce_scatter {rows}x{w} {dtype}", dst, ref, 1e-5 if dtype == torch.float32 else 1e-2)
+
+    # ---- device barrier stress
+    for _ in range(500):
+        ctx.barrier()
+    torch.cuda.synchronize()
+
+    allf = [None] * P
+    dist.all_gather_object(allf, fails)
+    if rank == 0:
+        flat = [f"r{r}: {m}" for r, fs in enumerate(allf) for m in fs]
+        print(json.dumps({"world": P, "checks": checks, "failures": flat}))
+    h.stop()
+    sys.exit(1 if any(allf) else 0)
+
+
+if __name__ == "__main__":
+    main()

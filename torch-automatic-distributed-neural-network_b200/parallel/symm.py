@@ -1,0 +1,220 @@
+"""Symmetric-memory context: one peer-mapped heap per GPU + the collective kernels on it.
+
+This is the B200 replacement for the TorchMPI library the reference links against
+(SURVEY §2.4): every rank ``cudaMalloc``s an identically sized heap (followed by a signal
+pad), exchanges CUDA-IPC handles through ``torch.distributed`` (plumbing only) and maps its
+peers' heaps, after which hand-written sm_100a kernels (csrc/comm.cu) do every collective
+with plain loads/stores over NVLink 5 / NVSwitch — no NCCL on this path.
+
+Allocation is a symmetric bump allocator: all ranks must call ``alloc`` in the same order
+with the same sizes (they do: the callers are SPMD).  ``tensor()`` returns a zero-copy
+``torch.Tensor`` view of heap memory, so model parameters and gradients can *live* in the
+heap (tadnn.parallel.fusion) and be reduced in place.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Optional
+
+import torch
+
+from .. import _native
+
+_DT = {torch.float32: 0, torch.bfloat16: 1}
+
+# signal-pad channels: collectives that can be in flight concurrently use different ones
+CH_DEFAULT = 0   # mpi.allreduceTensor & friends on the compute stream
+CH_DP = 1        # data-parallel gradient/parameter sync on the comm stream
+CH_TP = 2        # model-parallel layer collectives
+CH_BARRIER = 3
+
+
+class _RawCuda:
+    """Minimal ``__cuda_array_interface__`` carrier for zero-copy torch views of heap memory."""
+
+    def __init__(self, ptr: int, nbytes: int, owner):
+        self.owner = owner
+        self.__cuda_array_interface__ = {
+            "shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False),
+            "version": 3, "strides": None,
+        }
+
+
+class SymmContext:
+    def __init__(self):
+        self.handle = C.c_void_p()
+        self.rank = 0
+        self.world = 1
+        self.heap_bytes = 0
+        self.heap_ptrs: list[int] = []
+        self.has_multicast = False
+        self._bump = 0
+        self._heap_u8: Optional[torch.Tensor] = None
+        self._staging_off = 0
+        self._staging_bytes = 0
+        self.mpi = None
+        self.device = None
+
+    # ------------------------------------------------------------------ creation
+    @classmethod
+    def create(cls, mpi, heap_mb: Optional[int] = None, staging_mb: Optional[int] = None) -> "SymmContext":
+        import torch.distributed as dist
+        self = cls()
+        lib = _native.lib()
+        self.mpi = mpi
+        self.rank, self.world = mpi.rank(), mpi.size()
+        if self.world > 8:
+            raise _native.NativeError("tadnn symmetric memory supports up to 8 ranks (one NVSwitch domain)")
+        heap_mb = int(os.environ.get("TADNN_SYMM_HEAP_MB", heap_mb or 1024))
+        staging_mb = int(os.environ.get("TADNN_SYMM_STAGING_MB", staging_mb or 128))
+        self.heap_bytes = heap_mb << 20
+        self.device = torch.device("cuda", torch.cuda.current_device())
+        _native.check(lib.tadnn_comm_create(C.c_int(self.rank), C.c_int(self.world),
+                                            C.c_ulonglong(self.heap_bytes), C.byref(self.handle)),
+                      "tadnn_comm_create")
+        if self.world > 1:
+            mine = C.create_string_buffer(64)
+            _native.check(lib.tadnn_comm_ipc_handle(self.handle, mine), "tadnn_comm_ipc_handle")
+            allh: list = [None] * self.world
+            dist.all_gather_object(allh, bytes(mine.raw))
+            blob = b"".join(allh)
+            _native.check(lib.tadnn_comm_open_peers(self.handle, C.c_char_p(blob)), "tadnn_comm_open_peers")
+        self.heap_ptrs = []
+        for r in range(self.world):
+            p = C.c_void_p()
+            _native.check(lib.tadnn_comm_heap(self.handle, C.c_int(r), C.byref(p)), "tadnn_comm_heap")
+            self.heap_ptrs.append(int(p.value))
+        raw = _RawCuda(self.heap_ptrs[self.rank], self.heap_bytes, self)
+        self._heap_u8 = torch.as_tensor(raw, device=self.device)
+        assert self._heap_u8.data_ptr() == self.heap_ptrs[self.rank], "zero-copy heap view failed"
+        self._staging_bytes = staging_mb << 20
+        self._staging_off = self.alloc(self._staging_bytes)
+        if self.world > 1:
+            torch.cuda.synchronize()
+            dist.barrier()  # pads are zeroed and mapped everywhere before the first kernel
+        return self
+
+    def close(self):
+        if self.handle:
+            torch.cuda.synchronize()
+            self._heap_u8 = None
+            _native.lib().tadnn_comm_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    # ------------------------------------------------------------------ memory
+    def alloc(self, nbytes: int, align: int = 256) -> int:
+        off = (self._bump + align - 1) // align * align
+        if off + nbytes > self.heap_bytes:
+            raise MemoryError(
+                f"tadnn symmetric heap exhausted ({off + nbytes} > {self.heap_bytes} bytes); "
+                "raise TADNN_SYMM_HEAP_MB")
+        self._bump = off + nbytes
+        return off
+
+    def tensor(self, off: int, shape, dtype: torch.dtype) -> torch.Tensor:
+        n = 1
+        for s in shape:
+            n *= int(s)
+        nbytes = n * torch.empty((), dtype=dtype).element_size()
+        return self._heap_u8[off:off + nbytes].view(dtype).view(*shape)
+
+    def empty(self, shape, dtype: torch.dtype) -> torch.Tensor:
+        n = 1
+        for s in shape:
+            n *= int(s)
+        off = self.alloc(n * torch.empty((), dtype=dtype).element_size())
+        return self.tensor(off, shape, dtype)
+
+    def offset_of(self, t: torch.Tensor) -> Optional[int]:
+        """Heap offset of ``t`` if it is a dense view of this rank's heap, else None."""
+        base = self.heap_ptrs[self.rank]
+        p = t.data_ptr()
+        nbytes = t.numel() * t.element_size()
+        if t.is_cuda and t.is_contiguous() and base <= p and p + nbytes <= base + self.heap_bytes:
+            return p - base
+        return None
+
+    def peer_ptr(self, peer: int, off: int) -> int:
+        return self.heap_ptrs[peer] + off
+
+    def supports(self, t: torch.Tensor) -> bool:
+        if not (t.is_cuda and t.dtype in _DT):
+            return False
+        return self.offset_of(t) is not None or t.numel() * t.element_size() <= self._staging_bytes
+
+    # ------------------------------------------------------------------ collectives
+    def barrier(self, channel: int = CH_BARRIER, stream=None):
+        _native.check(_native.lib().tadnn_barrier(self.handle, C.c_int(channel),
+                                                  C.c_void_p(_native.stream_ptr(stream))), "tadnn_barrier")
+
+    def allreduce_offset(self, off: int, count: int, dtype: torch.dtype, scale: float = 1.0,
+                         algo: int = 0, max_blocks: int = 0, channel: int = CH_DEFAULT, stream=None):
+        _native.check(_native.lib().tadnn_allreduce(
+            self.handle, C.c_ulonglong(off), C.c_ulonglong(count), C.c_int(_DT[dtype]),
+            C.c_float(scale), C.c_int(algo), C.c_int(max_blocks), C.c_int(channel),
+            C.c_void_p(_native.stream_ptr(stream))), "tadnn_allreduce")
+
+    def allreduce_(self, t: torch.Tensor, scale: float = 1.0, algo: int = 0,
+                   channel: int = CH_DEFAULT, stream=None) -> torch.Tensor:
+        """In-place ``t = scale * sum_ranks(t)``.  Zero-copy when ``t`` lives in the heap,
+        otherwise staged through the heap's staging area."""
+        if self.world == 1:
+            if scale != 1.0:
+                t.mul_(scale)
+            return t
+        algo = int(os.environ.get("TADNN_FORCE_ALGO", algo)) if algo == 0 else algo
+        off = self.offset_of(t)
+        if off is not None and off % 16 == 0:
+            self.allreduce_offset(off, t.numel(), t.dtype, scale, algo, 0, channel, stream)
+            return t
+        nbytes = t.numel() * t.element_size()
+        if nbytes > self._staging_bytes:
+            raise MemoryError("tensor larger than the symmetric staging area; raise TADNN_SYMM_STAGING_MB")
+        st = self.tensor(self._staging_off, t.shape, t.dtype)
+        st.copy_(t)
+        self.allreduce_offset(self._staging_off, t.numel(), t.dtype, scale, algo, 0, channel, stream)
+        t.copy_(st)
+        return t
+
+    def broadcast_offset(self, off: int, nbytes: int, root: int = 0, channel: int = CH_DEFAULT, stream=None):
+        _native.check(_native.lib().tadnn_broadcast(
+            self.handle, C.c_ulonglong(off), C.c_ulonglong(nbytes), C.c_int(root), C.c_int(0),
+            C.c_int(channel), C.c_void_p(_native.stream_ptr(stream))), "tadnn_broadcast")
+
+    def allgather_cols_offset(self, src: torch.Tensor, off: int, channel: int = CH_DEFAULT, stream=None):
+        """Push local ``src[rows, w]`` into heap[off] of every rank viewed as [rows, world*w]."""
+        assert src.dim() == 2 and src.stride(1) == 1
+        es = src.element_size()
+        _native.check(_native.lib().tadnn_allgather_cols(
+            self.handle, C.c_void_p(src.data_ptr()), C.c_ulonglong(src.stride(0) * es),
+            C.c_ulonglong(off), C.c_int(src.shape[0]), C.c_ulonglong(src.shape[1] * es), C.c_int(0),
+            C.c_int(channel), C.c_void_p(_native.stream_ptr(stream))), "tadnn_allgather_cols")
+
+    def allgather_lastdim(self, inp: torch.Tensor, out: torch.Tensor, channel: int = CH_DEFAULT, stream=None):
+        """mpi.allgatherTensor semantics: ``out`` = rank-ordered concat of ``inp`` on the last dim."""
+        w = inp.shape[-1]
+        src = inp.reshape(-1, w)
+        if src.stride(1) != 1:
+            src = src.contiguous()
+        rows = src.shape[0]
+        nbytes = rows * w * self.world * inp.element_size()
+        off = self.offset_of(out) if out.is_contiguous() else None
+        if off is not None:
+            self.allgather_cols_offset(src, off, channel, stream)
+            return out
+        if nbytes > self._staging_bytes:
+            raise MemoryError("all-gather larger than the symmetric staging area")
+        self.allgather_cols_offset(src, self._staging_off, channel, stream)
+        out.copy_(self.tensor(self._staging_off, (rows, w * self.world), inp.dtype).view(out.shape))
+        return out
+
+    def reduce_scatter_cols_offset(self, off: int, dst: torch.Tensor, scale: float = 1.0,
+                                   bias: Optional[torch.Tensor] = None, act: int = 0,
+                                   channel: int = CH_DEFAULT, stream=None):
+        assert dst.dim() == 2 and dst.stride(1) == 1 and dst.dtype in _DT
+        _native.check(_native.lib().tadnn_reduce_scatter_cols(
+            self.handle, C.c_ulonglong(off), C.c_void_p(dst.data_ptr()), C.c_ulonglong(dst.stride(0)),
+            C.c_int(dst.shape[0]), C.c_int(dst.shape[1]), C.c_int(_DT[dst.dtype]), C.c_float(scale),
+            C.c_void_p(_native.ptr(bias)), C.c_int(act), C.c_int(0), C.c_int(channel),
+            C.c_void_p(_native.stream_ptr(stream))), "tadnn_reduce_scatter_cols")

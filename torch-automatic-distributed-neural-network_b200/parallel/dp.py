@@ -1,0 +1,175 @@
+"""Data-parallel synchronisation state: the counter/firing rule of the reference's hooks and
+the machinery that makes the sync one fused, overlapped kernel on B200.
+
+Reference behaviour kept (datamodule.lua:96-110,146-158): a counter starts at 1, the model is
+synchronised when ``counter % batchSize == 0 or counter == size`` (size = shard length), then
+the counter is incremented; it counts *calls*, never resets.  What changes is the
+hooking mechanism — the reference redefines ``nn.Sequential:backward`` and
+``nn.StochasticGradient:train`` class-wide and permanently; here ``optimize_sync`` attaches a
+``SyncState`` to *the model* (``model._tadnn_sync``) with a ``remove()``, and three entry points
+consult it: ``tadnn.nn.Sequential.backward`` (Torch7 style), ``StochasticGradient.train`` and
+plain autograd ``loss.backward()`` (post-accumulate-grad hooks + an end-of-backward callback).
+
+Overlap: on a step that will synchronise, parameter averaging is launched on a side stream
+when the backward starts (parameters do not change during backward) and each gradient bucket
+is launched as soon as its last gradient has been accumulated; the compute stream only waits
+for the side stream at the end of backward.
+"""
+from __future__ import annotations
+
+import os
+from typing import List, Optional
+
+import torch
+
+from . import symm as _symm
+
+
+class SyncState:
+    def __init__(self, model: torch.nn.Module, mpi, mpinn, batchSize: int, size: int,
+                 sync_mode: Optional[str] = None, overlap: Optional[bool] = None,
+                 bucket_mb: float = 8.0):
+        self.model = model
+        self.mpi = mpi
+        self.mpinn = mpinn
+        self.batchSize = int(batchSize)
+        self.size = int(size)
+        # syncPrototype=true -> params+grads (datamodule.lua:4,103-107); false -> grads only
+        if sync_mode is None:
+            sync_mode = "grads" if os.environ.get("TADNN_SYNC_PROTOTYPE", "1") in ("0", "false") else "model"
+        assert sync_mode in ("model", "grads")
+        self.sync_mode = sync_mode
+        self.syncs = 0
+        self._handles: List = []
+        self._in_backward = False
+        self._will_sync = False
+        self._pending: List = []
+        self._ready = 0
+        self.flat = getattr(model, "_tadnn_flat", None)
+        use_overlap = self.flat is not None and self.flat.symmetric and self.flat.ctx.world > 1
+        if overlap is None:
+            overlap = os.environ.get("TADNN_DP_OVERLAP", "1") not in ("0", "false")
+        self.overlap = bool(overlap) and use_overlap
+        self.comm_stream = torch.cuda.Stream() if self.overlap else None
+        self.bucket_bytes = int(bucket_mb * (1 << 20))
+        self._buckets = self._make_buckets() if self.overlap else []
+
+    # ------------------------------------------------------------------ firing rule
+    def should_sync(self, counter: int) -> bool:
+        return (counter % self.batchSize == 0) or (counter == self.size)
+
+    def after_backward(self, owner) -> bool:
+        """Counter logic of the hooked ``Sequential:backward``; the counter lives on ``owner``
+        (whichever module's backward ran) but the captured top-level model is synchronised."""
+        c = getattr(owner, "sync_counter", None)
+        if c is None:
+            c = 1
+        fired = self.should_sync(c)
+        if fired:
+            self.sync()
+        owner.sync_counter = c + 1
+        return fired
+
+    def sync(self):
+        from .. import datamodule
+        if self.sync_mode == "model":
+            datamodule.synchronizeModel(self.model, self.mpi)
+        else:
+            self.mpinn.synchronizeGradients(self.model, self.mpi, average=True)
+        self.syncs += 1
+
+    # ------------------------------------------------------------------ autograd path
+    def install_autograd_hooks(self):
+        for p in self.model.parameters():
+            if p.requires_grad:
+                self._handles.append(p.register_post_accumulate_grad_hook(self._on_grad))
+        return self
+
+    def remove(self):
+        for h in self._handles:
+            h.remove()
+        self._handles = []
+        if getattr(self.model, "_tadnn_sync", None) is self:
+            try:
+                del self.model._tadnn_sync
+            except AttributeError:
+                pass
+
+    def _make_buckets(self):
+        """Reverse-parameter-order buckets of ~bucket_bytes inside each dtype group's grads half:
+        (dtype, heap byte offset, element count, [param ids])."""
+        buckets = []
+        for g in self.flat.groups.values():
+            es = g.region.element_size()
+            ends = [off + p.numel() for p, off in zip(g.params, g.offsets)]
+            hi = g.half
+            ids: List[int] = []
+            for i in range(len(g.params) - 1, -1, -1):
+                ids.append(id(g.params[i]))
+                lo = g.offsets[i]
+                if (hi - lo) * es >= self.bucket_bytes or i == 0:
+                    lo = 0 if i == 0 else lo
+                    lo_al = lo // 4 * 4 if es == 4 else lo // 8 * 8  # keep 16-byte alignment
+                    buckets.append({"dtype": g.dtype, "off": g.heap_off + (g.half + lo_al) * es,
+                                    "count": hi - lo_al, "ids": set(ids), "left": 0})
+                    hi = lo_al
+                    ids = []
+            del ends
+        return buckets
+
+    def _on_grad(self, p):
+        if not self._in_backward:
+            self._in_backward = True
+            owner = self.model
+            c = getattr(owner, "sync_counter", None) or 1
+            self._will_sync = self.should_sync(c)
+            torch.autograd.Variable._execution_engine.queue_callback(self._backward_done)
+            if self.overlap and self._will_sync:
+                for b in self._buckets:
+                    b["left"] = len(b["ids"])
+                ev = torch.cuda.current_stream().record_event()
+                self.comm_stream.wait_event(ev)
+                if self.sync_mode == "model":  # params are stable during backward: reduce now
+                    P = self.flat.ctx.world
+                    self.flat.allreduce("params", 1.0 / P, stream=self.comm_stream, channel=_symm.CH_DP)
+        if self.overlap and self._will_sync:
+            if self.flat is not None and p.grad is not None:
+                gv = self.flat.grad_view(p)
+                if p.grad.data_ptr() != gv.data_ptr():
+                    with torch.no_grad():
+                        gv.copy_(p.grad)
+                        p.grad = gv
+            pid = id(p)
+            for b in self._buckets:
+                if pid in b["ids"]:
+                    b["left"] -= 1
+                    if b["left"] == 0:
+                        ev = torch.cuda.current_stream().record_event()
+                        self.comm_stream.wait_event(ev)
+                        P = self.flat.ctx.world
+                        self.flat.ctx.allreduce_offset(b["off"], b["count"], b["dtype"], 1.0 / P, 0, 0,
+                                                       _symm.CH_DP, self.comm_stream)
+                    break
+
+    def _backward_done(self):
+        self._in_backward = False
+        owner = self.model
+        c = getattr(owner, "sync_counter", None) or 1
+        if self.overlap and self._will_sync:
+            # any bucket that never completed (unused params) is reduced now
+            P = self.flat.ctx.world
+            for b in self._buckets:
+                if b["left"] > 0:
+                    ev = torch.cuda.current_stream().record_event()
+                    self.comm_stream.wait_event(ev)
+                    self.flat.ctx.allreduce_offset(b["off"], b["count"], b["dtype"], 1.0 / P, 0, 0,
+                                                   _symm.CH_DP, self.comm_stream)
+                    b["left"] = 0
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+            self.syncs += 1
+            owner.sync_counter = c + 1
+        else:
+            if self.flat is not None:
+                self.flat.rehome_grads()
+            self.after_backward(owner)
+        self._will_sync = False

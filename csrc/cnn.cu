@@ -1,0 +1,588 @@
+// CIFAR-CNN kernels around the tcgen05 GEMM (config 3; K15-K20 of SURVEY §2.5).
+//
+// The reference's example model (cifar_example/sgd-torchad_nn-cifar.lua:88-118) is
+//   conv5x5(3->64)+ReLU+maxpool3/3, conv5x5(64->64)+ReLU+maxpool3/3, View(64), Dropout(.5),
+//   Linear(64,100)+ReLU, Linear(100,10), LogSoftMax, CrossEntropyCriterion
+// executed by cunn as im2col + cuBLAS SGEMM + pointwise kernels, fp32, one sample at a time.
+// Here activations are bf16 NHWC, convolutions are im2col + tadnn_gemm_bf16 (bias+ReLU in the
+// GEMM epilogue), and everything after the second pooling (dropout, both FC layers,
+// log-softmax, NLL loss and all of their gradients) is ONE fused kernel per direction.
+#include "common.cuh"
+
+namespace tadnn {
+namespace {
+
+__device__ __forceinline__ uint32_t hash32(uint32_t x) {
+  x ^= x >> 16; x *= 0x7feb352du; x ^= x >> 15; x *= 0x846ca68bu; x ^= x >> 16;
+  return x;
+}
+// Bernoulli(keep = 1-p) from a counter-based hash: recomputed in backward, no mask tensor.
+__device__ __forceinline__ float dropout_scale(uint32_t seed, uint32_t idx, float p) {
+  if (p <= 0.f) return 1.f;
+  const float u = static_cast<float>(hash32(seed ^ hash32(idx)) >> 8) * (1.0f / 16777216.0f);
+  return u >= p ? 1.0f / (1.0f - p) : 0.0f;
+}
+
+// ---- im2col ---------------------------------------------------------------
+// col[row, (kh*KW+kw)*C + c], row = (b*OH + oy)*OW + ox, valid (unpadded) convolution, stride 1.
+// NHWC source, C % 8 == 0: one 16-byte copy per (row, kh, kw, c8).
+__global__ void im2col_nhwc_kernel(const uint4* __restrict__ x, uint4* __restrict__ col, int B, int H, int W, int C8,
+                                   int KH, int KW, int OH, int OW, int Kpad8) {
+  const long long total = static_cast<long long>(B) * OH * OW * KH * KW * C8;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c8 = static_cast<int>(i % C8);
+    long long t = i / C8;
+    const int kw = static_cast<int>(t % KW); t /= KW;
+    const int kh = static_cast<int>(t % KH); t /= KH;
+    const long long row = t;
+    const int ox = static_cast<int>(row % OW);
+    const int oy = static_cast<int>((row / OW) % OH);
+    const int b = static_cast<int>(row / (static_cast<long long>(OW) * OH));
+    const uint4 v = x[((static_cast<long long>(b) * H + oy + kh) * W + ox + kw) * C8 + c8];
+    col[row * Kpad8 + (kh * KW + kw) * C8 + c8] = v;
+  }
+}
+// NCHW source with few channels (the 3-channel input image): each thread builds 8 consecutive
+// k entries (one 16-byte store); K is zero-padded to Kpad.
+__global__ void im2col_nchw_kernel(const __nv_bfloat16* __restrict__ x, uint4* __restrict__ col, int B, int C, int H,
+                                   int W, int KH, int KW, int OH, int OW, int Kpad8) {
+  const long long total = static_cast<long long>(B) * OH * OW * Kpad8;
+  const int K = KH * KW * C;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int k8 = static_cast<int>(i % Kpad8);
+    const long long row = i / Kpad8;
+    const int ox = static_cast<int>(row % OW);
+    const int oy = static_cast<int>((row / OW) % OH);
+    const int b = static_cast<int>(row / (static_cast<long long>(OW) * OH));
+    __align__(16) __nv_bfloat16 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int k = k8 * 8 + j;
+      if (k < K) {
+        const int c = k % C, kw = (k / C) % KW, kh = k / (C * KW);
+        v[j] = x[((static_cast<long long>(b) * C + c) * H + oy + kh) * W + ox + kw];
+      } else {
+        v[j] = __float2bfloat16_rn(0.f);
+      }
+    }
+    col[i] = *reinterpret_cast<const uint4*>(v);
+  }
+}
+
+// ---- col2im (gather form): dx[b,y,x,c] = sum_{kh,kw} dcol[(b,y-kh,x-kw), (kh*KW+kw)*C + c] ----
+__global__ void col2im_nhwc_kernel(const uint4* __restrict__ dcol, uint4* __restrict__ dx, int B, int H, int W, int C8,
+                                   int KH, int KW, int OH, int OW, int Kpad8) {
+  const long long total = static_cast<long long>(B) * H * W * C8;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c8 = static_cast<int>(i % C8);
+    long long t = i / C8;
+    const int xx = static_cast<int>(t % W); t /= W;
+    const int yy = static_cast<int>(t % H);
+    const int b = static_cast<int>(t / H);
+    float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    for (int kh = 0; kh < KH; ++kh) {
+      const int oy = yy - kh;
+      if (oy < 0 || oy >= OH) continue;
+      for (int kw = 0; kw < KW; ++kw) {
+        const int ox = xx - kw;
+        if (ox < 0 || ox >= OW) continue;
+        const long long row = (static_cast<long long>(b) * OH + oy) * OW + ox;
+        const uint4 v = dcol[row * Kpad8 + (kh * KW + kw) * C8 + c8];
+        float2 f;
+        f = unpack_bf16x2(v.x); acc[0] += f.x; acc[1] += f.y;
+        f = unpack_bf16x2(v.y); acc[2] += f.x; acc[3] += f.y;
+        f = unpack_bf16x2(v.z); acc[4] += f.x; acc[5] += f.y;
+        f = unpack_bf16x2(v.w); acc[6] += f.x; acc[7] += f.y;
+      }
+    }
+    dx[i] = make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]), pack_bf16x2(acc[4], acc[5]),
+                       pack_bf16x2(acc[6], acc[7]));
+  }
+}
+
+// ---- max pooling k x k, stride k, NHWC, floor mode; argmax kept as a byte -----------
+__global__ void maxpool_fwd_nhwc_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, uint2* __restrict__ idx, int B,
+                                        int H, int W, int C8, int PK, int PH, int PW) {
+  const long long total = static_cast<long long>(B) * PH * PW * C8;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c8 = static_cast<int>(i % C8);
+    long long t = i / C8;
+    const int px = static_cast<int>(t % PW); t /= PW;
+    const int py = static_cast<int>(t % PH);
+    const int b = static_cast<int>(t / PH);
+    float best[8];
+    unsigned char bi[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { best[j] = -INFINITY; bi[j] = 0; }
+    for (int dy = 0; dy < PK; ++dy)
+      for (int dx = 0; dx < PK; ++dx) {
+        const uint4 v = x[((static_cast<long long>(b) * H + py * PK + dy) * W + px * PK + dx) * C8 + c8];
+        float f[8];
+        float2 q;
+        q = unpack_bf16x2(v.x); f[0] = q.x; f[1] = q.y;
+        q = unpack_bf16x2(v.y); f[2] = q.x; f[3] = q.y;
+        q = unpack_bf16x2(v.z); f[4] = q.x; f[5] = q.y;
+        q = unpack_bf16x2(v.w); f[6] = q.x; f[7] = q.y;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (f[j] > best[j]) { best[j] = f[j]; bi[j] = static_cast<unsigned char>(dy * PK + dx); }
+      }
+    y[i] = make_uint4(pack_bf16x2(best[0], best[1]), pack_bf16x2(best[2], best[3]), pack_bf16x2(best[4], best[5]),
+                      pack_bf16x2(best[6], best[7]));
+    uint2 o;
+    o.x = bi[0] | (bi[1] << 8) | (bi[2] << 16) | (bi[3] << 24);
+    o.y = bi[4] | (bi[5] << 8) | (bi[6] << 16) | (bi[7] << 24);
+    idx[i] = o;
+  }
+}
+
+// dx[b,y,x,c] = dy[b,y/k,x/k,c] if (y,x) is the argmax of its window and the pooled value is > 0
+// (ReLU backward folded in: the pooled value is the max of ReLU outputs), else 0.
+__global__ void maxpool_relu_bwd_nhwc_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
+                                             const uint2* __restrict__ idx, uint4* __restrict__ dx, int B, int H, int W,
+                                             int C8, int PK, int PH, int PW) {
+  const long long total = static_cast<long long>(B) * H * W * C8;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c8 = static_cast<int>(i % C8);
+    long long t = i / C8;
+    const int xx = static_cast<int>(t % W); t /= W;
+    const int yy = static_cast<int>(t % H);
+    const int b = static_cast<int>(t / H);
+    const int py = yy / PK, px = xx / PK;
+    uint4 o = make_uint4(0, 0, 0, 0);
+    if (py < PH && px < PW) {
+      const long long pi = ((static_cast<long long>(b) * PH + py) * PW + px) * C8 + c8;
+      const uint2 id = idx[pi];
+      const uint4 g = dy[pi];
+      const uint4 pv = y[pi];
+      const unsigned me = static_cast<unsigned>((yy - py * PK) * PK + (xx - px * PK));
+      const uint32_t gw[4] = {g.x, g.y, g.z, g.w};
+      const uint32_t pw[4] = {pv.x, pv.y, pv.z, pv.w};
+      uint32_t ow[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const unsigned i0 = ((j < 2 ? id.x : id.y) >> (16 * (j & 1))) & 0xffu;
+        const unsigned i1 = ((j < 2 ? id.x : id.y) >> (16 * (j & 1) + 8)) & 0xffu;
+        const float2 gv = unpack_bf16x2(gw[j]);
+        const float2 yv = unpack_bf16x2(pw[j]);
+        ow[j] = pack_bf16x2((i0 == me && yv.x > 0.f) ? gv.x : 0.f, (i1 == me && yv.y > 0.f) ? gv.y : 0.f);
+      }
+      o = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+    }
+    dx[i] = o;
+  }
+}
+
+// ---- column sum (bias gradient): out[c] += sum_r x[r, c]; x bf16 [R, C], C <= 256 ------------
+__global__ void colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out, long long R, int C, int ld) {
+  // blockDim = (64, 4): threadIdx.x walks columns, threadIdx.y rows
+  __shared__ float part[4][64];
+  for (int c0 = 0; c0 < C; c0 += 64) {
+    const int c = c0 + threadIdx.x;
+    float acc = 0.f;
+    if (c < C)
+      for (long long r = blockIdx.x * 4ll + threadIdx.y; r < R; r += gridDim.x * 4ll)
+        acc += __bfloat162float(x[r * ld + c]);
+    part[threadIdx.y][threadIdx.x] = acc;
+    __syncthreads();
+    if (threadIdx.y == 0 && c < C)
+      atomicAdd(out + c, part[0][threadIdx.x] + part[1][threadIdx.x] + part[2][threadIdx.x] + part[3][threadIdx.x]);
+    __syncthreads();
+  }
+}
+
+// ---- conv weight layout/dtype conversion -----------------------------------------------------
+// Torch7 SpatialConvolutionMM keeps weight [O, C*KH*KW] with k = (c*KH + kh)*KW + kw.  The GEMMs
+// want bf16 [O, Kpad] with k' = (kh*KW + kw)*C + c (matches the NHWC im2col), zero padded.
+__global__ void conv_weight_pack_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ wp, int O, int C, int KH,
+                                        int KW, int Kpad) {
+  const int total = O * Kpad;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int o = i / Kpad, k = i % Kpad;
+    float v = 0.f;
+    if (k < C * KH * KW) {
+      const int c = k % C, kw = (k / C) % KW, kh = k / (C * KW);
+      v = w[o * (C * KH * KW) + (c * KH + kh) * KW + kw];
+    }
+    wp[i] = __float2bfloat16_rn(v);
+  }
+}
+// grad[O, C*KH*KW] (Torch7 order) += scale * dwp[O, Kpad] (packed order)
+__global__ void conv_wgrad_unpack_kernel(const float* __restrict__ dwp, float* __restrict__ grad, int O, int C, int KH,
+                                         int KW, int Kpad, float scale) {
+  const int K = C * KH * KW;
+  const int total = O * K;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int o = i / K, kk = i % K;
+    const int kw = kk % KW, kh = (kk / KW) % KH, c = kk / (KW * KH);
+    grad[i] += scale * dwp[o * Kpad + (kh * KW + kw) * C + c];
+  }
+}
+
+// ---- fused classifier head --------------------------------------------------------------------
+// p2 [B, D] bf16  -> dropout(p) -> fc1 (H x D) + ReLU -> fc2 (NC x H) -> log-softmax -> NLL(target)
+// D = 64, H = 100, NC = 10 for the reference model; limits: D <= 64, H <= 128, NC <= 32.
+constexpr int kHeadD = 64, kHeadH = 128, kHeadC = 32;
+constexpr int kHeadChunk = 32;  // samples staged per block iteration in backward
+
+struct HeadArgs {
+  const __nv_bfloat16* p2;   // [B, D]
+  const float *w1, *b1, *w2, *b2;  // fc1 [H, D], [H]; fc2 [NC, H], [NC]  (Torch7 nn.Linear layout)
+  const long long* target;   // [B], 0-based
+  int B, D, H, NC;
+  float p;                   // dropout probability (0 in eval)
+  uint32_t seed;
+  float* hbuf;               // [B, H] fp32 post-ReLU hidden (saved for backward)
+  float* logp;               // [B, NC] fp32
+  float* loss_partial;       // scratch: [gridDim.x] per-block partial sums  (+1 counter word after it)
+  unsigned int* counter;     // scratch: last-block-done counter, must be 0 on entry; left at 0
+  float* loss;               // [1] mean loss
+  // backward only
+  float *gw1, *gb1, *gw2, *gb2;  // fp32 gradient accumulators (+=)
+  __nv_bfloat16* dp2;            // [B, D]
+  float grad_scale;              // dLoss (normally 1): gradients are d(mean loss) * grad_scale
+  const float* grad_scale_dev;   // optional device scalar folded into grad_scale
+};
+
+__global__ void __launch_bounds__(256) head_fwd_kernel(HeadArgs a) {
+  extern __shared__ float sm[];
+  float* w1t = sm;                         // [D][H]
+  float* w2t = w1t + a.D * a.H;            // [H][NC]
+  float* b1 = w2t + a.H * a.NC;            // [H]
+  float* b2 = b1 + a.H;                    // [NC]
+  float* dbuf = b2 + a.NC;                 // [8 warps][D]
+  float* hb = dbuf + 8 * kHeadD;           // [8 warps][H]
+  __shared__ float block_loss[8];
+  __shared__ bool is_last;
+  for (int i = threadIdx.x; i < a.D * a.H; i += blockDim.x) { const int j = i / a.D, d = i % a.D; w1t[d * a.H + j] = a.w1[i]; }
+  for (int i = threadIdx.x; i < a.H * a.NC; i += blockDim.x) { const int c = i / a.H, j = i % a.H; w2t[j * a.NC + c] = a.w2[i]; }
+  for (int i = threadIdx.x; i < a.H; i += blockDim.x) b1[i] = a.b1[i];
+  for (int i = threadIdx.x; i < a.NC; i += blockDim.x) b2[i] = a.b2[i];
+  __syncthreads();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float* d = dbuf + warp * kHeadD;
+  float* h = hb + warp * a.H;
+  float my_loss = 0.f;
+  for (int s = blockIdx.x * 8 + warp; s < a.B; s += gridDim.x * 8) {
+    for (int i = lane; i < a.D; i += 32)
+      d[i] = __bfloat162float(a.p2[static_cast<long long>(s) * a.D + i]) * dropout_scale(a.seed, static_cast<uint32_t>(s) * a.D + i, a.p);
+    __syncwarp();
+    for (int j = lane; j < a.H; j += 32) {
+      float acc = b1[j];
+      for (int i = 0; i < a.D; ++i) acc += w1t[i * a.H + j] * d[i];
+      acc = fmaxf(acc, 0.f);
+      h[j] = acc;
+      a.hbuf[static_cast<long long>(s) * a.H + j] = acc;
+    }
+    __syncwarp();
+    float logit = -INFINITY;
+    if (lane < a.NC) {
+      float acc = b2[lane];
+      for (int j = 0; j < a.H; ++j) acc += w2t[j * a.NC + lane] * h[j];
+      logit = acc;
+    }
+    const float mx = warp_max(logit);
+    const float e = lane < a.NC ? __expf(logit - mx) : 0.f;
+    const float lse = mx + __logf(warp_sum(e));
+    const float lp = logit - lse;
+    if (lane < a.NC) a.logp[static_cast<long long>(s) * a.NC + lane] = lp;
+    const int t = static_cast<int>(a.target[s]);
+    const float lt = __shfl_sync(0xffffffffu, lp, t & 31);
+    if (lane == 0) my_loss -= lt;
+    __syncwarp();
+  }
+  // deterministic mean: per-block partials in scratch, summed in block order by the last block
+  if (lane == 0) block_loss[warp] = my_loss;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < 8; ++w) t += block_loss[w];
+    a.loss_partial[blockIdx.x] = t;
+    __threadfence();
+    const unsigned done = atomicAdd(a.counter, 1u);
+    is_last = (done == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (is_last && threadIdx.x == 0) {
+    __threadfence();
+    float t = 0.f;
+    for (unsigned b = 0; b < gridDim.x; ++b) t += reinterpret_cast<volatile float*>(a.loss_partial)[b];
+    *a.loss = t / static_cast<float>(a.B);
+    *a.counter = 0u;  // ready for the next launch
+  }
+}
+
+__global__ void __launch_bounds__(256) head_bwd_kernel(HeadArgs a) {
+  extern __shared__ float sm[];
+  float* w1 = sm;                                  // [H][D]  (row-major, as stored)
+  float* w2t = w1 + a.H * a.D;                     // [H][NC]
+  float* sd = w2t + a.H * a.NC;                    // [chunk][D]   dropped input
+  float* sdh = sd + kHeadChunk * kHeadD;           // [chunk][H]   dL/d(pre-ReLU hidden)
+  float* sh = sdh + kHeadChunk * a.H;              // [chunk][H]   hidden
+  float* sdl = sh + kHeadChunk * a.H;              // [chunk][NC]  dL/dlogits
+  for (int i = threadIdx.x; i < a.H * a.D; i += blockDim.x) w1[i] = a.w1[i];
+  for (int i = threadIdx.x; i < a.H * a.NC; i += blockDim.x) { const int c = i / a.H, j = i % a.H; w2t[j * a.NC + c] = a.w2[i]; }
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float inv_b = a.grad_scale * (a.grad_scale_dev != nullptr ? *a.grad_scale_dev : 1.0f) / static_cast<float>(a.B);
+  // register accumulators: thread t owns gw1 entries t, t+256, ... and gw2 entries t, t+256, ...
+  constexpr int kW1PerThread = (kHeadH * kHeadD + 255) / 256;  // 32
+  constexpr int kW2PerThread = (kHeadC * kHeadH + 255) / 256;  // 16
+  float acc1[kW1PerThread], acc2[kW2PerThread];
+#pragma unroll
+  for (int k = 0; k < kW1PerThread; ++k) acc1[k] = 0.f;
+#pragma unroll
+  for (int k = 0; k < kW2PerThread; ++k) acc2[k] = 0.f;
+  float accb = 0.f;  // threads 0..H-1: gb1[t]; threads H..H+NC-1: gb2[t-H]
+  const int n1 = a.H * a.D, n2 = a.NC * a.H;
+  __syncthreads();
+  for (int base = blockIdx.x * kHeadChunk; base < a.B; base += gridDim.x * kHeadChunk) {
+    const int ns = min(kHeadChunk, a.B - base);
+    // phase A: one warp per sample
+    for (int ls = warp; ls < ns; ls += 8) {
+      const int s = base + ls;
+      float* d = sd + ls * kHeadD;
+      float* dh = sdh + ls * a.H;
+      float* hh = sh + ls * a.H;
+      float* dl = sdl + ls * a.NC;
+      for (int i = lane; i < a.D; i += 32)
+        d[i] = __bfloat162float(a.p2[static_cast<long long>(s) * a.D + i]) * dropout_scale(a.seed, static_cast<uint32_t>(s) * a.D + i, a.p);
+      const int t = static_cast<int>(a.target[s]);
+      if (lane < a.NC) dl[lane] = (__expf(a.logp[static_cast<long long>(s) * a.NC + lane]) - (lane == t ? 1.f : 0.f)) * inv_b;
+      __syncwarp();
+      for (int j = lane; j < a.H; j += 32) {
+        const float hv = a.hbuf[static_cast<long long>(s) * a.H + j];
+        float g = 0.f;
+        for (int c = 0; c < a.NC; ++c) g += dl[c] * w2t[j * a.NC + c];
+        hh[j] = hv;
+        dh[j] = hv > 0.f ? g : 0.f;
+      }
+      __syncwarp();
+      for (int i = lane; i < a.D; i += 32) {
+        float g = 0.f;
+        for (int j = 0; j < a.H; ++j) g += dh[j] * w1[j * a.D + i];
+        a.dp2[static_cast<long long>(s) * a.D + i] = __float2bfloat16_rn(g * dropout_scale(a.seed, static_cast<uint32_t>(s) * a.D + i, a.p));
+      }
+    }
+    __syncthreads();
+    // phase B: every thread accumulates its own weight-gradient entries over the staged samples
+#pragma unroll
+    for (int k = 0; k < kW1PerThread; ++k) {
+      const int e = threadIdx.x + k * 256;
+      if (e < n1) {
+        const int j = e / a.D, i = e % a.D;
+        float acc = acc1[k];
+        for (int ls = 0; ls < ns; ++ls) acc += sdh[ls * a.H + j] * sd[ls * kHeadD + i];
+        acc1[k] = acc;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < kW2PerThread; ++k) {
+      const int e = threadIdx.x + k * 256;
+      if (e < n2) {
+        const int c = e / a.H, j = e % a.H;
+        float acc = acc2[k];
+        for (int ls = 0; ls < ns; ++ls) acc += sdl[ls * a.NC + c] * sh[ls * a.H + j];
+        acc2[k] = acc;
+      }
+    }
+    if (static_cast<int>(threadIdx.x) < a.H) {
+      for (int ls = 0; ls < ns; ++ls) accb += sdh[ls * a.H + threadIdx.x];
+    } else if (static_cast<int>(threadIdx.x) < a.H + a.NC) {
+      for (int ls = 0; ls < ns; ++ls) accb += sdl[ls * a.NC + (threadIdx.x - a.H)];
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int k = 0; k < kW1PerThread; ++k) {
+    const int e = threadIdx.x + k * 256;
+    if (e < n1) atomicAdd(a.gw1 + e, acc1[k]);
+  }
+#pragma unroll
+  for (int k = 0; k < kW2PerThread; ++k) {
+    const int e = threadIdx.x + k * 256;
+    if (e < n2) atomicAdd(a.gw2 + e, acc2[k]);
+  }
+  if (static_cast<int>(threadIdx.x) < a.H) atomicAdd(a.gb1 + threadIdx.x, accb);
+  else if (static_cast<int>(threadIdx.x) < a.H + a.NC) atomicAdd(a.gb2 + (threadIdx.x - a.H), accb);
+}
+
+// ---- optimiser / misc elementwise -------------------------------------------------------------
+__global__ void sgd_kernel(float* __restrict__ p, float* __restrict__ g, long long n, float lr, float wd, int zero_grad) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const float w = p[i];
+    p[i] = w - lr * (g[i] + wd * w);
+    if (zero_grad) g[i] = 0.f;
+  }
+}
+__global__ void cast_f32_to_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x)
+    y[i] = __float2bfloat16_rn(x[i]);
+}
+
+int grid_for(long long total, int threads) {
+  long long b = (total + threads - 1) / threads;
+  const long long cap = static_cast<long long>(sm_count()) * 16;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return static_cast<int>(b);
+}
+
+size_t head_fwd_smem(int D, int H, int NC) { return sizeof(float) * (static_cast<size_t>(D) * H + H * NC + H + NC + 8 * kHeadD + 8 * H); }
+size_t head_bwd_smem(int D, int H, int NC) {
+  return sizeof(float) * (static_cast<size_t>(H) * D + H * NC + kHeadChunk * kHeadD + 2 * kHeadChunk * H + kHeadChunk * NC);
+}
+
+}  // namespace
+}  // namespace tadnn
+
+using namespace tadnn;
+
+extern "C" int tadnn_im2col(const void* x, void* col, int B, int C, int H, int W, int KH, int KW, int Kpad, int nchw, tadnn_stream_t stream_) {
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int OH = H - KH + 1, OW = W - KW + 1;
+  TADNN_REQUIRE(B > 0 && OH > 0 && OW > 0, "im2col: bad shape");
+  TADNN_REQUIRE(Kpad % 8 == 0 && Kpad >= C * KH * KW, "im2col: Kpad=%d must be a multiple of 8 and >= %d", Kpad, C * KH * KW);
+  if (nchw) {
+    const long long total = static_cast<long long>(B) * OH * OW * (Kpad / 8);
+    im2col_nchw_kernel<<<grid_for(total, 256), 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), static_cast<uint4*>(col), B, C, H, W, KH, KW, OH, OW, Kpad / 8);
+    TADNN_LAUNCH_CHECK("im2col_nchw");
+  } else {
+    TADNN_REQUIRE(C % 8 == 0 && Kpad == C * KH * KW, "im2col (NHWC): C must be a multiple of 8 and Kpad == C*KH*KW");
+    const long long total = static_cast<long long>(B) * OH * OW * KH * KW * (C / 8);
+    im2col_nhwc_kernel<<<grid_for(total, 256), 256, 0, stream>>>(static_cast<const uint4*>(x), static_cast<uint4*>(col), B, H, W, C / 8, KH, KW, OH, OW, Kpad / 8);
+    TADNN_LAUNCH_CHECK("im2col_nhwc");
+  }
+  return 0;
+}
+
+extern "C" int tadnn_col2im(const void* dcol, void* dx, int B, int C, int H, int W, int KH, int KW, tadnn_stream_t stream_) {
+  const int OH = H - KH + 1, OW = W - KW + 1;
+  TADNN_REQUIRE(B > 0 && OH > 0 && OW > 0 && C % 8 == 0, "col2im: bad shape (C must be a multiple of 8)");
+  const long long total = static_cast<long long>(B) * H * W * (C / 8);
+  col2im_nhwc_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(static_cast<const uint4*>(dcol), static_cast<uint4*>(dx), B, H, W, C / 8, KH, KW, OH, OW, C * KH * KW / 8);
+  TADNN_LAUNCH_CHECK("col2im_nhwc");
+  return 0;
+}
+
+extern "C" int tadnn_maxpool_fwd(const void* x, void* y, void* idx, int B, int H, int W, int C, int k, tadnn_stream_t stream_) {
+  TADNN_REQUIRE(B > 0 && C % 8 == 0 && k >= 1 && k <= 15 && H >= k && W >= k, "maxpool_fwd: bad shape");
+  const int PH = H / k, PW = W / k;
+  const long long total = static_cast<long long>(B) * PH * PW * (C / 8);
+  maxpool_fwd_nhwc_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(static_cast<const uint4*>(x), static_cast<uint4*>(y), static_cast<uint2*>(idx), B, H, W, C / 8, k, PH, PW);
+  TADNN_LAUNCH_CHECK("maxpool_fwd_nhwc");
+  return 0;
+}
+
+extern "C" int tadnn_maxpool_relu_bwd(const void* dy, const void* y, const void* idx, void* dx, int B, int H, int W, int C, int k, tadnn_stream_t stream_) {
+  TADNN_REQUIRE(B > 0 && C % 8 == 0 && k >= 1 && k <= 15 && H >= k && W >= k, "maxpool_relu_bwd: bad shape");
+  const int PH = H / k, PW = W / k;
+  const long long total = static_cast<long long>(B) * H * W * (C / 8);
+  maxpool_relu_bwd_nhwc_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(static_cast<const uint4*>(dy), static_cast<const uint4*>(y), static_cast<const uint2*>(idx), static_cast<uint4*>(dx), B, H, W, C / 8, k, PH, PW);
+  TADNN_LAUNCH_CHECK("maxpool_relu_bwd_nhwc");
+  return 0;
+}
+
+extern "C" int tadnn_colsum_bf16(const void* x, float* out, long long R, int C, int ld, tadnn_stream_t stream_) {
+  TADNN_REQUIRE(R > 0 && C > 0, "colsum: empty");
+  long long blocks = (R + 63) / 64;
+  if (blocks > sm_count() * 4) blocks = sm_count() * 4;
+  colsum_bf16_kernel<<<static_cast<int>(blocks), dim3(64, 4), 0, static_cast<cudaStream_t>(stream_)>>>(static_cast<const __nv_bfloat16*>(x), out, R, C, ld);
+  TADNN_LAUNCH_CHECK("colsum_bf16");
+  return 0;
+}
+
+extern "C" int tadnn_conv_weight_pack(const float* w, void* wp, int O, int C, int KH, int KW, int Kpad, tadnn_stream_t stream_) {
+  TADNN_REQUIRE(Kpad >= C * KH * KW, "conv_weight_pack: Kpad too small");
+  conv_weight_pack_kernel<<<grid_for(static_cast<long long>(O) * Kpad, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(w, static_cast<__nv_bfloat16*>(wp), O, C, KH, KW, Kpad);
+  TADNN_LAUNCH_CHECK("conv_weight_pack");
+  return 0;
+}
+
+extern "C" int tadnn_conv_wgrad_unpack(const float* dwp, float* grad, int O, int C, int KH, int KW, int Kpad, float scale, tadnn_stream_t stream_) {
+  conv_wgrad_unpack_kernel<<<grid_for(static_cast<long long>(O) * C * KH * KW, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(dwp, grad, O, C, KH, KW, Kpad, scale);
+  TADNN_LAUNCH_CHECK("conv_wgrad_unpack");
+  return 0;
+}
+
+static int head_check(const tadnn_head_args* h, const char* what) {
+  TADNN_REQUIRE(h != nullptr, "%s: null args", what);
+  TADNN_REQUIRE(h->B > 0 && h->D > 0 && h->D <= kHeadD && h->H > 0 && h->H <= kHeadH && h->NC > 0 && h->NC <= kHeadC,
+                "%s: unsupported head shape D=%d (<=%d) H=%d (<=%d) NC=%d (<=%d)", what, h->D, kHeadD, h->H, kHeadH, h->NC, kHeadC);
+  return 0;
+}
+
+static HeadArgs to_dev(const tadnn_head_args* h) {
+  HeadArgs a;
+  memset(&a, 0, sizeof(a));
+  a.p2 = static_cast<const __nv_bfloat16*>(h->p2);
+  a.w1 = h->w1; a.b1 = h->b1; a.w2 = h->w2; a.b2 = h->b2;
+  a.target = h->target;
+  a.B = h->B; a.D = h->D; a.H = h->H; a.NC = h->NC;
+  a.p = h->dropout_p; a.seed = h->seed;
+  a.hbuf = h->hidden; a.logp = h->logp; a.loss = h->loss;
+  a.gw1 = h->gw1; a.gb1 = h->gb1; a.gw2 = h->gw2; a.gb2 = h->gb2;
+  a.dp2 = static_cast<__nv_bfloat16*>(h->dp2);
+  a.grad_scale = h->grad_scale;
+  a.grad_scale_dev = h->grad_scale_dev;
+  return a;
+}
+
+extern "C" int tadnn_head_workspace_bytes(int B) {
+  (void)B;
+  return static_cast<int>(sizeof(float) * 1024 + 256);
+}
+
+extern "C" int tadnn_head_forward(const tadnn_head_args* h, void* workspace, tadnn_stream_t stream_) {
+  if (int rc = head_check(h, "head_forward")) return rc;
+  TADNN_REQUIRE(workspace != nullptr, "head_forward: workspace is required (tadnn_head_workspace_bytes)");
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  HeadArgs a = to_dev(h);
+  a.loss_partial = static_cast<float*>(workspace);
+  a.counter = reinterpret_cast<unsigned int*>(static_cast<uint8_t*>(workspace) + sizeof(float) * 1024);
+  int blocks = (h->B + 7) / 8;
+  const int cap = sm_count() * 2 < 1024 ? sm_count() * 2 : 1024;
+  if (blocks > cap) blocks = cap;
+  const size_t smem = head_fwd_smem(h->D, h->H, h->NC);
+  static bool attr = false;
+  if (!attr) { TADNN_CHECK_CUDA(cudaFuncSetAttribute(head_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)); attr = true; }
+  TADNN_REQUIRE(smem <= 96 * 1024, "head_forward: shared memory %zu too large", smem);
+  head_fwd_kernel<<<blocks, 256, smem, stream>>>(a);
+  TADNN_LAUNCH_CHECK("head_fwd");
+  return 0;
+}
+
+extern "C" int tadnn_head_backward(const tadnn_head_args* h, tadnn_stream_t stream_) {
+  if (int rc = head_check(h, "head_backward")) return rc;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  HeadArgs a = to_dev(h);
+  int blocks = (h->B + kHeadChunk - 1) / kHeadChunk;
+  if (blocks > sm_count()) blocks = sm_count();
+  const size_t smem = head_bwd_smem(h->D, h->H, h->NC);
+  static bool attr = false;
+  if (!attr) { TADNN_CHECK_CUDA(cudaFuncSetAttribute(head_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024)); attr = true; }
+  TADNN_REQUIRE(smem <= 160 * 1024, "head_backward: shared memory %zu too large", smem);
+  head_bwd_kernel<<<blocks, 256, smem, stream>>>(a);
+  TADNN_LAUNCH_CHECK("head_bwd");
+  return 0;
+}
+
+extern "C" int tadnn_sgd_step(float* p, float* g, long long n, float lr, float weight_decay, int zero_grad, tadnn_stream_t stream_) {
+  if (n <= 0) return 0;
+  sgd_kernel<<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(p, g, n, lr, weight_decay, zero_grad);
+  TADNN_LAUNCH_CHECK("sgd_step");
+  return 0;
+}
+
+extern "C" int tadnn_cast_f32_bf16(const float* x, void* y, long long n, tadnn_stream_t stream_) {
+  if (n <= 0) return 0;
+  cast_f32_to_bf16_kernel<<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(x, static_cast<__nv_bfloat16*>(y), n);
+  TADNN_LAUNCH_CHECK("cast_f32_bf16");
+  return 0;
+}

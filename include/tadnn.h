@@ -143,6 +143,64 @@ int tadnn_allreduce_emulated(tadnn_comm* const* comms, int world, unsigned long 
                              unsigned long long count, int dtype, float scale, int algo,
                              tadnn_stream_t stream);
 
+/* ---- CIFAR-CNN kernels (csrc/cnn.cu) ----------------------------------------
+ * Replace the cunn library calls behind the example model
+ * (cifar_example/sgd-torchad_nn-cifar.lua:88-118,237): SpatialConvolutionMM's im2col,
+ * ReLU, SpatialMaxPooling, Dropout, the two nn.Linear, LogSoftMax and the criterion.
+ * Activations are bf16; NHWC between layers; valid convolution, stride 1.
+ */
+/* col[row, (kh*KW+kw)*C + c] with row = (b*OH+oy)*OW+ox; Kpad >= C*KH*KW, multiple of 8,
+ * zero padded.  nchw=1: x is [B,C,H,W] (the input image); nchw=0: x is [B,H,W,C], C%8==0. */
+int tadnn_im2col(const void* x, void* col, int B, int C, int H, int W, int KH, int KW, int Kpad,
+                 int nchw, tadnn_stream_t stream);
+/* dx[B,H,W,C] = col2im(dcol[B*OH*OW, C*KH*KW]) (gather form, no atomics). */
+int tadnn_col2im(const void* dcol, void* dx, int B, int C, int H, int W, int KH, int KW,
+                 tadnn_stream_t stream);
+/* k x k / stride k max pooling, floor mode, NHWC; idx holds the argmax (one byte per element). */
+int tadnn_maxpool_fwd(const void* x, void* y, void* idx, int B, int H, int W, int C, int k,
+                      tadnn_stream_t stream);
+/* Backward of ReLU followed by that pooling: dx = dy routed to the argmax where y > 0. */
+int tadnn_maxpool_relu_bwd(const void* dy, const void* y, const void* idx, void* dx, int B, int H,
+                           int W, int C, int k, tadnn_stream_t stream);
+/* out[c] += sum_r x[r,c]  (bias gradient; x bf16 [R, ld], out fp32). */
+int tadnn_colsum_bf16(const void* x, float* out, long long R, int C, int ld, tadnn_stream_t stream);
+/* Torch7 conv weight [O, C*KH*KW] fp32 (k = (c*KH+kh)*KW+kw)  <->  GEMM operand [O, Kpad] bf16
+ * (k' = (kh*KW+kw)*C+c); unpack accumulates: grad += scale * dwp. */
+int tadnn_conv_weight_pack(const float* w, void* wp, int O, int C, int KH, int KW, int Kpad,
+                           tadnn_stream_t stream);
+int tadnn_conv_wgrad_unpack(const float* dwp, float* grad, int O, int C, int KH, int KW, int Kpad,
+                            float scale, tadnn_stream_t stream);
+
+/* Fused classifier head: dropout -> Linear(D,H)+ReLU -> Linear(H,NC) -> log-softmax -> NLL.
+ * Limits: D <= 64, H <= 128, NC <= 32.  fc weights in Torch7 nn.Linear layout, fp32. */
+typedef struct tadnn_head_args {
+  const void* p2;            /* [B, D] bf16 input (second pooling output) */
+  const float* w1; const float* b1;   /* [H, D], [H] */
+  const float* w2; const float* b2;   /* [NC, H], [NC] */
+  const long long* target;   /* [B] 0-based class indices */
+  int B, D, H, NC;
+  float dropout_p;           /* 0 disables dropout (evaluation) */
+  unsigned int seed;         /* dropout mask = hash(seed, element); same seed in forward and backward */
+  float* hidden;             /* [B, H] fp32, written by forward, read by backward */
+  float* logp;               /* [B, NC] fp32 log-probabilities */
+  float* loss;               /* [1] fp32 mean NLL (forward) */
+  float* gw1; float* gb1; float* gw2; float* gb2;  /* backward: fp32 gradients, accumulated (+=) */
+  void* dp2;                 /* backward: [B, D] bf16 gradient w.r.t. p2 */
+  float grad_scale;          /* backward: upstream dLoss (1 for a plain mean loss) */
+  const float* grad_scale_dev; /* backward: optional device scalar multiplied into grad_scale */
+} tadnn_head_args;
+/* Scratch needed by tadnn_head_forward (per-block loss partials + a completion counter).  The
+ * caller allocates it ONCE, zero-filled; the kernel leaves the counter at zero again. */
+int tadnn_head_workspace_bytes(int B);
+int tadnn_head_forward(const tadnn_head_args* a, void* workspace, tadnn_stream_t stream);
+int tadnn_head_backward(const tadnn_head_args* a, tadnn_stream_t stream);
+
+/* p -= lr * (g + wd * p); optionally g = 0.  Replaces accUpdateGradParameters' in-place step
+ * (datamodule.lua:142) for batched training on the flat buffer. */
+int tadnn_sgd_step(float* p, float* g, long long n, float lr, float weight_decay, int zero_grad,
+                   tadnn_stream_t stream);
+int tadnn_cast_f32_bf16(const float* x, void* y, long long n, tadnn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

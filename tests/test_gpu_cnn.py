@@ -1,0 +1,121 @@
+"""CNN kernels and the fused CifarCNN loss vs plain PyTorch fp32 references."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def test_im2col_nchw_and_nhwc():
+    from tadnn.ops import cnn as K
+    x = torch.randn(3, 3, 32, 32, device="cuda").bfloat16()
+    col = K.im2col(x, 5, 5, 80, nchw=True)
+    ref = F.unfold(x.float(), 5).transpose(1, 2).reshape(3 * 784, 3, 25).permute(0, 2, 1).reshape(3 * 784, 75)
+    assert torch.equal(col[:, :75].float(), ref) and float(col[:, 75:].abs().sum()) == 0
+    y = torch.randn(2, 9, 9, 64, device="cuda").bfloat16()
+    col2 = K.im2col(y, 5, 5, 1600, nchw=False)
+    ref2 = F.unfold(y.float().permute(0, 3, 1, 2), 5).transpose(1, 2).reshape(2 * 25, 64, 25).permute(0, 2, 1).reshape(50, 1600)
+    assert torch.equal(col2.float(), ref2)
+
+
+def test_col2im_is_adjoint_of_im2col():
+    from tadnn.ops import cnn as K
+    dcol = torch.randn(2 * 25, 1600, device="cuda").bfloat16()
+    dx = K.col2im(dcol, 2, 64, 9, 9, 5, 5)
+    cols = dcol.float().reshape(2, 25, 25, 64).permute(0, 3, 2, 1).reshape(2, 1600, 25)  # [B, C*25 (c,k), L]
+    ref = F.fold(cols, (9, 9), 5).permute(0, 2, 3, 1)
+    assert (dx.float() - ref).abs().max().item() < 0.05 * ref.abs().max().item()
+
+
+def test_maxpool_fwd_bwd():
+    from tadnn.ops import cnn as K
+    x = torch.relu(torch.randn(4, 28, 28, 64, device="cuda")).bfloat16()
+    y, idx = K.maxpool_fwd(x, 3)
+    xr = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    yr = F.max_pool2d(xr, 3, 3)
+    assert torch.equal(y.float(), yr.permute(0, 2, 3, 1))
+    dy = torch.randn(4, 9, 9, 64, device="cuda").bfloat16()
+    dx = K.maxpool_relu_bwd(dy, y, idx, 28, 28, 3)
+    # reference: route to argmax where pooled value > 0 (ties: first max, like our scan order)
+    (gr,) = torch.autograd.grad(yr, xr, (dy.float() * (y.float() > 0)).permute(0, 3, 1, 2))
+    # tie-breaking can differ only where the max is 0 (masked) -> exact match expected
+    assert torch.equal(dx.float(), gr.permute(0, 2, 3, 1))
+
+
+def test_colsum_pack_unpack_sgd():
+    from tadnn.ops import cnn as K
+    x = torch.randn(10000, 64, device="cuda").bfloat16()
+    out = torch.ones(64, device="cuda")
+    K.colsum_bf16(x, out)
+    assert torch.allclose(out, 1 + x.float().sum(0), atol=2e-2, rtol=1e-4)
+    w = torch.randn(64, 75, device="cuda")
+    wp = K.conv_weight_pack(w, 3, 5, 5, 80)
+    ref = w.view(64, 3, 5, 5).permute(0, 2, 3, 1).reshape(64, 75)
+    assert torch.equal(wp[:, :75].float(), ref.bfloat16().float()) and float(wp[:, 75:].abs().sum()) == 0
+    g = torch.ones(64, 75, device="cuda")
+    K.conv_wgrad_unpack(F.pad(ref, (0, 5)).contiguous(), g, 3, 5, 5, 2.0)
+    assert torch.allclose(g, 1 + 2 * w)
+    p, gr = torch.randn(1000, device="cuda"), torch.randn(1000, device="cuda")
+    p0, g0 = p.clone(), gr.clone()
+    K.sgd_step(p, gr, 0.1, 0.01, True)
+    assert torch.allclose(p, p0 - 0.1 * (g0 + 0.01 * p0), atol=1e-6) and float(gr.abs().sum()) == 0
+
+
+@pytest.mark.parametrize("B", [1, 7, 64, 300])
+def test_cifar_cnn_loss_and_grads_match_pytorch(B):
+    from tadnn.models.cifar_cnn import CifarCNN
+    torch.manual_seed(0)
+    m = CifarCNN().cuda().eval()  # eval: dropout off, exact comparison
+    with torch.no_grad():  # widen the init a little so ReLUs/pools are well exercised
+        for p in m.parameters():
+            p.mul_(2.0)
+    x = torch.randn(B, 3, 32, 32, device="cuda").bfloat16()
+    t = torch.randint(0, 10, (B,), device="cuda")
+    loss, logp = m.loss_and_logp(x, t)
+    loss.backward()
+    got = {n: p.grad.clone() for n, p in m.named_parameters()}
+    m.zero_grad()
+    ref_logp = m.reference_logp(x.float(), emulate_bf16=True)
+    ref_loss = F.nll_loss(ref_logp, t)
+    ref_loss.backward()
+    assert abs(loss.item() - ref_loss.item()) < 2e-2 * max(1.0, abs(ref_loss.item()))
+    assert (logp - ref_logp.detach()).abs().max().item() < 0.05
+    report = {}
+    for n, p in m.named_parameters():
+        ref = p.grad
+        report[n] = ((got[n] - ref).norm() / (ref.norm() + 1e-12)).item()
+    print("\n[cnn grads rel-err B=%d] %s" % (B, {k: round(v, 4) for k, v in report.items()}))
+    for n, v in report.items():
+        assert v < 4e-2, f"{n}: relative error {v}"
+
+
+def test_cifar_cnn_dropout_is_consistent_and_seeded():
+    from tadnn.models.cifar_cnn import CifarCNN
+    torch.manual_seed(0)
+    m = CifarCNN().cuda().train()
+    x = torch.randn(256, 3, 32, 32, device="cuda").bfloat16()
+    t = torch.randint(0, 10, (256,), device="cuda")
+    l1 = m.loss(x, t).item()
+    l2 = m.loss(x, t).item()
+    assert l1 != l2  # a new mask every step
+    m._step = 0
+    assert m.loss(x, t).item() == l1  # same seed/step -> same mask (deterministic loss reduction)
+
+
+def test_cifar_cnn_trains():
+    from tadnn.models.cifar_cnn import CifarCNN
+    from tadnn.ops import cnn as K
+    torch.manual_seed(0)
+    m = CifarCNN(dropout=0.0).cuda().train()
+    t = torch.randint(0, 10, (512,), device="cuda")
+    patterns = torch.randn(10, 3, 32, 32, device="cuda")
+    x = (0.5 * torch.randn(512, 3, 32, 32, device="cuda") + patterns[t]).bfloat16()  # learnable
+    first = None
+    for _ in range(60):
+        m.zero_grad()
+        loss = m.loss(x, t)
+        loss.backward()
+        for p in m.parameters():
+            K.sgd_step(p.data.view(-1), p.grad.view(-1), 0.1)
+        first = first if first is not None else loss.item()
+    assert loss.item() < 0.7 * first, (first, loss.item())

@@ -25,6 +25,7 @@ from . import datamodule, nodemodule  # noqa: F401
 from . import nn  # noqa: F401
 from .datamodule import (comm_speed, data_parallel, optimize_sync, parallelize, remove_hooks,  # noqa: F401
                          selectCollective, synchronizeModel, synchronize_model)
+from .trainer import BatchTrainer  # noqa: F401
 from .nn import (MPBaseLinear, MPBaseReshape, MPInitialLinear, MPInitialReshape, MPTanh,  # noqa: F401
                  StochasticGradient)
 
@@ -39,5 +40,5 @@ __all__ = [
     "parallelize", "synchronizeModel", "synchronize_model", "data_parallel", "optimize_sync",
     "selectCollective", "comm_speed", "remove_hooks", "mpi", "mpinn", "nn", "datamodule", "nodemodule",
     "MPInitialLinear", "MPBaseLinear", "MPTanh", "MPInitialReshape", "MPBaseReshape",
-    "StochasticGradient", "native_available",
+    "StochasticGradient", "BatchTrainer", "native_available",
 ]

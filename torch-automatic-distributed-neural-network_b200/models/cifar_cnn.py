@@ -1,0 +1,202 @@
+"""The reference example's CNN (cifar_example/sgd-torchad_nn-cifar.lua:88-118), B200 edition.
+
+Architecture and parameter layout are the reference's: conv5x5(3->64)+ReLU+maxpool3/3,
+conv5x5(64->64)+ReLU+maxpool3/3, View(64), Dropout(0.5), Linear(64,100)+ReLU, Linear(100,10),
+LogSoftMax, trained with CrossEntropyCriterion (a second, idempotent log-softmax — SURVEY Q9);
+114,838 parameters: ``conv1 [64,75]+64``, ``conv2 [64,1600]+64``, ``fc1 [100,64]+100``,
+``fc2 [10,100]+10`` in Torch7 layouts, fp32 master copies.
+
+Execution on CUDA (``loss(x, target)``): bf16 activations, NHWC between layers,
+convolutions as im2col + the tcgen05 GEMM with bias+ReLU in its epilogue, pooling with saved
+argmax, and one fused kernel for everything after the second pooling (dropout, both FC layers,
+log-softmax, NLL and their gradients).  ``reference_logp`` is the plain PyTorch fp32 statement
+of the same network used as the numerics oracle and as the CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+
+import torch
+import torch.nn.functional as F
+
+from .. import _native
+from ..nn.protocol import T7Protocol
+
+K1PAD = 80  # 75 -> multiple of 8 (TMA pitch)
+
+
+class _CnnLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed):
+        from ..ops import cnn as K
+        B = x.shape[0]
+        dev = x.device
+        xb = x if x.dtype == torch.bfloat16 else x.to(torch.bfloat16)
+        xb = xb.contiguous()
+        w1p = K.conv_weight_pack(w1, 3, 5, 5, K1PAD)
+        w2p = K.conv_weight_pack(w2, 64, 5, 5, 1600)
+        col1 = K.im2col(xb, 5, 5, K1PAD, nchw=True)                       # [B*784, 80]
+        a1 = K.gemm_bf16(col1, w1p, bias=b1, act="relu", tile_n=64)       # [B*784, 64] == NHWC [B,28,28,64]
+        p1, idx1 = K.maxpool_fwd(a1.view(B, 28, 28, 64), 3)               # [B,9,9,64]
+        col2 = K.im2col(p1, 5, 5, 1600, nchw=False)                       # [B*25, 1600]
+        a2 = K.gemm_bf16(col2, w2p, bias=b2, act="relu", tile_n=64)       # [B*25, 64] == [B,5,5,64]
+        p2, idx2 = K.maxpool_fwd(a2.view(B, 5, 5, 64), 3)                 # [B,1,1,64]
+        hidden = torch.empty((B, 100), device=dev, dtype=torch.float32)
+        logp = torch.empty((B, 10), device=dev, dtype=torch.float32)
+        loss = torch.empty((), device=dev, dtype=torch.float32)
+        h = K.HeadArgs()
+        h.p2, h.w1, h.b1, h.w2, h.b2 = p2.data_ptr(), fw1.data_ptr(), fb1.data_ptr(), fw2.data_ptr(), fb2.data_ptr()
+        tgt = target.to(torch.int64).contiguous()
+        h.target = tgt.data_ptr()
+        h.B, h.D, h.H, h.NC = B, 64, 100, 10
+        h.dropout_p, h.seed = float(p_drop), int(seed) & 0xFFFFFFFF
+        h.hidden, h.logp, h.loss = hidden.data_ptr(), logp.data_ptr(), loss.data_ptr()
+        ws = K.head_workspace(dev)
+        _native.check(_native.lib().tadnn_head_forward(C.byref(h), C.c_void_p(ws.data_ptr()),
+                                                       C.c_void_p(_native.stream_ptr())), "tadnn_head_forward")
+        ctx.save_for_backward(col1, a1, p1, idx1, col2, a2, p2, idx2, hidden, logp, tgt, w2p, fw1, fb1, fw2, fb2)
+        ctx.p_drop, ctx.seed, ctx.B = float(p_drop), int(seed) & 0xFFFFFFFF, B
+        ctx.mark_non_differentiable(logp)
+        return loss, logp
+
+    @staticmethod
+    def backward(ctx, gloss, _glogp):
+        from ..ops import cnn as K
+        col1, a1, p1, idx1, col2, a2, p2, idx2, hidden, logp, tgt, w2p, fw1, fb1, fw2, fb2 = ctx.saved_tensors
+        B, dev = ctx.B, p2.device
+        f32 = dict(device=dev, dtype=torch.float32)
+        gfw1, gfb1 = torch.zeros((100, 64), **f32), torch.zeros(100, **f32)
+        gfw2, gfb2 = torch.zeros((10, 100), **f32), torch.zeros(10, **f32)
+        gw1, gb1 = torch.zeros((64, 75), **f32), torch.zeros(64, **f32)
+        gw2, gb2 = torch.zeros((64, 1600), **f32), torch.zeros(64, **f32)
+        dp2 = torch.empty((B, 1, 1, 64), device=dev, dtype=torch.bfloat16)
+        h = K.HeadArgs()
+        h.p2, h.w1, h.b1, h.w2, h.b2 = p2.data_ptr(), fw1.data_ptr(), fb1.data_ptr(), fw2.data_ptr(), fb2.data_ptr()
+        h.target = tgt.data_ptr()
+        h.B, h.D, h.H, h.NC = B, 64, 100, 10
+        h.dropout_p, h.seed = ctx.p_drop, ctx.seed
+        h.hidden, h.logp = hidden.data_ptr(), logp.data_ptr()
+        h.gw1, h.gb1, h.gw2, h.gb2 = gfw1.data_ptr(), gfb1.data_ptr(), gfw2.data_ptr(), gfb2.data_ptr()
+        h.dp2 = dp2.data_ptr()
+        h.grad_scale = 1.0
+        gl = gloss.to(device=dev, dtype=torch.float32).contiguous()
+        h.grad_scale_dev = gl.data_ptr()  # upstream dLoss stays on the device: no host sync
+        _native.check(_native.lib().tadnn_head_backward(C.byref(h), C.c_void_p(_native.stream_ptr())), "tadnn_head_backward")
+        # conv2: pool/relu backward into a2's storage, bias grad, wgrad (split-K), dgrad into col2's storage
+        da2 = K.maxpool_relu_bwd(dp2, p2, idx2, 5, 5, 3, out=a2.view(B, 5, 5, 64)).view(B * 25, 64)
+        K.colsum_bf16(da2, gb2)
+        dw2p = K.gemm_bf16(da2, col2, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
+                           split_k=K.auto_split_k(64, 1600, B * 25))
+        K.conv_wgrad_unpack(dw2p, gw2, 64, 5, 5)
+        dcol2 = K.gemm_bf16(da2, w2p, b_mn_major=True, out=col2)
+        dp1 = K.col2im(dcol2, B, 64, 9, 9, 5, 5)
+        # conv1 (no dgrad: the image needs no gradient)
+        da1 = K.maxpool_relu_bwd(dp1, p1, idx1, 28, 28, 3, out=a1.view(B, 28, 28, 64)).view(B * 784, 64)
+        K.colsum_bf16(da1, gb1)
+        dw1p = K.gemm_bf16(da1, col1, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
+                           split_k=K.auto_split_k(64, K1PAD, B * 784, 128), tile_n=128)
+        K.conv_wgrad_unpack(dw1p, gw1, 3, 5, 5)
+        grads = [gw1, gb1, gw2, gb2, gfw1, gfb1, gfw2, gfb2]
+        return (None, None, *grads, None, None)
+
+
+class CifarCNN(torch.nn.Module, T7Protocol):
+    def __init__(self, dropout: float = 0.5, seed: int = 1):
+        super().__init__()
+        self.dropout = dropout
+        self._step = 0
+        self._seed = seed
+        P = torch.nn.Parameter
+        self.conv1_weight, self.conv1_bias = P(torch.empty(64, 75)), P(torch.empty(64))
+        self.conv2_weight, self.conv2_bias = P(torch.empty(64, 1600)), P(torch.empty(64))
+        self.fc1_weight, self.fc1_bias = P(torch.empty(100, 64)), P(torch.empty(100))
+        self.fc2_weight, self.fc2_bias = P(torch.empty(10, 100)), P(torch.empty(10))
+        self.reset()
+
+    def reset(self):
+        """Torch7 resets: U(+-1/sqrt(fan_in)) for weight and bias of every layer."""
+        with torch.no_grad():
+            for w, b, fan in ((self.conv1_weight, self.conv1_bias, 75), (self.conv2_weight, self.conv2_bias, 1600),
+                              (self.fc1_weight, self.fc1_bias, 64), (self.fc2_weight, self.fc2_bias, 100)):
+                s = 1.0 / math.sqrt(fan)
+                w.uniform_(-s, s)
+                b.uniform_(-s, s)
+        return self
+
+    # ---- plain PyTorch statement of the network (oracle / CPU path) -----------------------
+    def reference_logp(self, x: torch.Tensor, dropout_scale: torch.Tensor | None = None,
+                       emulate_bf16: bool = False) -> torch.Tensor:
+        """``emulate_bf16`` rounds weights and post-ReLU activations to bf16 at the points where
+        the fused path stores bf16, so that pooling picks the same arg-max in both."""
+        def r(t):
+            return t.to(torch.bfloat16).float() if emulate_bf16 else t
+        x = x.float()
+        y = F.conv2d(x, r(self.conv1_weight).view(64, 3, 5, 5), self.conv1_bias)
+        y = F.max_pool2d(r(F.relu(y)), 3, 3)
+        y = F.conv2d(y, r(self.conv2_weight).view(64, 64, 5, 5), self.conv2_bias)
+        y = F.max_pool2d(r(F.relu(y)), 3, 3).reshape(-1, 64)
+        if dropout_scale is not None:
+            y = y * dropout_scale
+        elif self.training and self.dropout > 0:
+            y = F.dropout(y, self.dropout, True)
+        y = F.relu(F.linear(y, self.fc1_weight, self.fc1_bias))
+        y = F.linear(y, self.fc2_weight, self.fc2_bias)
+        return F.log_softmax(y, dim=-1)
+
+    def _native_ok(self, x) -> bool:
+        return x.is_cuda and x.dim() == 4 and tuple(x.shape[1:]) == (3, 32, 32)
+
+    def loss_and_logp(self, x: torch.Tensor, target: torch.Tensor):
+        """Mean cross-entropy (differentiable) and log-probabilities."""
+        if x.dim() == 3:
+            x, target = x.unsqueeze(0), torch.as_tensor(target).reshape(1)
+        if self._native_ok(x):
+            self._step += 1
+            p = self.dropout if self.training else 0.0
+            seed = (self._seed * 2654435761 + self._step * 40503) & 0xFFFFFFFF
+            return _CnnLoss.apply(x, target.to(x.device), self.conv1_weight, self.conv1_bias, self.conv2_weight,
+                                  self.conv2_bias, self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias, p, seed)
+        logp = self.reference_logp(x)
+        return F.nll_loss(logp, target.long().to(logp.device)), logp.detach()
+
+    def loss(self, x, target):
+        return self.loss_and_logp(x, target)[0]
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        """Log-probabilities ``[B, 10]`` (what the reference model outputs after LogSoftMax)."""
+        squeeze = x.dim() == 3
+        if squeeze:
+            x = x.unsqueeze(0)
+        if self._native_ok(x) and not torch.is_grad_enabled():
+            dummy = torch.zeros(x.shape[0], dtype=torch.int64, device=x.device)
+            was = self.training
+            self.training = False
+            try:
+                logp = self.loss_and_logp(x, dummy)[1]
+            finally:
+                self.training = was
+        else:
+            logp = self.reference_logp(x)
+        return logp.squeeze(0) if squeeze else logp
+
+    def to_sequential(self):
+        """The same network as a ``tadnn.nn.Sequential`` of Torch7-named layers sharing these
+        parameters (for ``.t7`` export and for the per-sample reference-config example)."""
+        from .. import nn as tnn
+        c1, c2 = tnn.SpatialConvolutionMM(3, 64, 5, 5), tnn.SpatialConvolutionMM(64, 64, 5, 5)
+        l1, l2 = tnn.Linear(64, 100), tnn.Linear(100, 10)
+        c1.weight, c1.bias, c2.weight, c2.bias = self.conv1_weight, self.conv1_bias, self.conv2_weight, self.conv2_bias
+        l1.weight, l1.bias, l2.weight, l2.bias = self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias
+        return (tnn.Sequential().add(c1).add(tnn.ReLU()).add(tnn.SpatialMaxPooling(3, 3, 3, 3))
+                .add(c2).add(tnn.ReLU()).add(tnn.SpatialMaxPooling(3, 3, 3, 3)).add(tnn.View(64))
+                .add(tnn.Dropout(self.dropout)).add(l1).add(tnn.ReLU()).add(l2).add(tnn.LogSoftMax()))
+
+
+class CnnCriterion:
+    """Pairs with ``CifarCNN`` in ``StochasticGradient``-style loops: ``crit(model_out, y)`` needs
+    the model's *input*, so the fused path is exposed as ``model.loss(x, y)`` instead; this class
+    only adapts the ``criterion(output, target)`` call for log-prob outputs."""
+
+    def __call__(self, logp, target):
+        return F.nll_loss(logp.float(), torch.as_tensor(target).long().reshape(-1).to(logp.device))

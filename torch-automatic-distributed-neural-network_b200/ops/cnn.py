@@ -1,0 +1,113 @@
+"""Python wrappers over csrc/cnn.cu (im2col/col2im, max-pool, fused classifier head, SGD).
+See include/tadnn.h for the contracts and the reference call sites each kernel replaces."""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from .. import _native
+from .gemm import gemm_bf16
+
+
+class HeadArgs(C.Structure):
+    _fields_ = [
+        ("p2", C.c_void_p), ("w1", C.c_void_p), ("b1", C.c_void_p), ("w2", C.c_void_p), ("b2", C.c_void_p),
+        ("target", C.c_void_p), ("B", C.c_int), ("D", C.c_int), ("H", C.c_int), ("NC", C.c_int),
+        ("dropout_p", C.c_float), ("seed", C.c_uint), ("hidden", C.c_void_p), ("logp", C.c_void_p),
+        ("loss", C.c_void_p), ("gw1", C.c_void_p), ("gb1", C.c_void_p), ("gw2", C.c_void_p), ("gb2", C.c_void_p),
+        ("dp2", C.c_void_p), ("grad_scale", C.c_float), ("grad_scale_dev", C.c_void_p),
+    ]
+
+
+def _s(stream=None):
+    return C.c_void_p(_native.stream_ptr(stream))
+
+
+def _p(t):
+    return C.c_void_p(_native.ptr(t))
+
+
+def im2col(x: torch.Tensor, KH: int, KW: int, Kpad: int, nchw: bool, out=None) -> torch.Tensor:
+    if nchw:
+        B, Cc, H, W = x.shape
+    else:
+        B, H, W, Cc = x.shape
+    assert x.dtype == torch.bfloat16 and x.is_contiguous()
+    OH, OW = H - KH + 1, W - KW + 1
+    if out is None:
+        out = torch.empty((B * OH * OW, Kpad), device=x.device, dtype=torch.bfloat16)
+    _native.check(_native.lib().tadnn_im2col(_p(x), _p(out), B, Cc, H, W, KH, KW, Kpad, int(nchw), _s()), "tadnn_im2col")
+    return out
+
+
+def col2im(dcol: torch.Tensor, B: int, Cc: int, H: int, W: int, KH: int, KW: int) -> torch.Tensor:
+    dx = torch.empty((B, H, W, Cc), device=dcol.device, dtype=torch.bfloat16)
+    _native.check(_native.lib().tadnn_col2im(_p(dcol), _p(dx), B, Cc, H, W, KH, KW, _s()), "tadnn_col2im")
+    return dx
+
+
+def maxpool_fwd(x: torch.Tensor, k: int):
+    B, H, W, Cc = x.shape
+    y = torch.empty((B, H // k, W // k, Cc), device=x.device, dtype=torch.bfloat16)
+    idx = torch.empty((B, H // k, W // k, Cc), device=x.device, dtype=torch.uint8)
+    _native.check(_native.lib().tadnn_maxpool_fwd(_p(x), _p(y), _p(idx), B, H, W, Cc, k, _s()), "tadnn_maxpool_fwd")
+    return y, idx
+
+
+def maxpool_relu_bwd(dy, y, idx, H: int, W: int, k: int, out=None):
+    B, PH, PW, Cc = y.shape
+    dx = out if out is not None else torch.empty((B, H, W, Cc), device=y.device, dtype=torch.bfloat16)
+    _native.check(_native.lib().tadnn_maxpool_relu_bwd(_p(dy), _p(y), _p(idx), _p(dx), B, H, W, Cc, k, _s()),
+                  "tadnn_maxpool_relu_bwd")
+    return dx
+
+
+def colsum_bf16(x: torch.Tensor, out: torch.Tensor):
+    R, Cc = x.shape
+    _native.check(_native.lib().tadnn_colsum_bf16(_p(x), _p(out), C.c_longlong(R), Cc, x.stride(0), _s()), "tadnn_colsum_bf16")
+    return out
+
+
+def conv_weight_pack(w: torch.Tensor, Cc: int, KH: int, KW: int, Kpad: int) -> torch.Tensor:
+    O = w.shape[0]
+    wp = torch.empty((O, Kpad), device=w.device, dtype=torch.bfloat16)
+    _native.check(_native.lib().tadnn_conv_weight_pack(_p(w), _p(wp), O, Cc, KH, KW, Kpad, _s()), "tadnn_conv_weight_pack")
+    return wp
+
+
+def conv_wgrad_unpack(dwp: torch.Tensor, grad: torch.Tensor, Cc: int, KH: int, KW: int, scale: float = 1.0):
+    O, Kpad = dwp.shape
+    _native.check(_native.lib().tadnn_conv_wgrad_unpack(_p(dwp), _p(grad), O, Cc, KH, KW, Kpad, C.c_float(scale), _s()),
+                  "tadnn_conv_wgrad_unpack")
+    return grad
+
+
+_head_ws = {}
+
+
+def head_workspace(device) -> torch.Tensor:
+    """Zero-initialised scratch for tadnn_head_forward, one per device, allocated once."""
+    key = str(device)
+    ws = _head_ws.get(key)
+    if ws is None:
+        n = int(_native.lib().tadnn_head_workspace_bytes(0))
+        ws = torch.zeros(n, device=device, dtype=torch.uint8)
+        _head_ws[key] = ws
+    return ws
+
+
+def sgd_step(p: torch.Tensor, g: torch.Tensor, lr: float, weight_decay: float = 0.0, zero_grad: bool = False):
+    assert p.dtype == torch.float32 and g.dtype == torch.float32 and p.is_contiguous() and g.is_contiguous()
+    _native.check(_native.lib().tadnn_sgd_step(_p(p), _p(g), C.c_longlong(p.numel()), C.c_float(lr),
+                                               C.c_float(weight_decay), int(zero_grad), _s()), "tadnn_sgd_step")
+
+
+def auto_split_k(M: int, N: int, K: int, tile_n: int = 256) -> int:
+    tiles = ((M + 127) // 128) * ((N + tile_n - 1) // tile_n)
+    kb = (K + 63) // 64
+    return max(1, min(kb, 148 // max(1, tiles)))
+
+
+__all__ = ["im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "conv_weight_pack",
+           "conv_wgrad_unpack", "head_workspace", "sgd_step", "auto_split_k", "HeadArgs", "gemm_bf16"]

@@ -44,7 +44,34 @@ __global__ void im2col_nhwc_kernel(const uint4* __restrict__ x, uint4* __restric
   }
 }
 // NCHW source with few channels (the 3-channel input image): each thread builds 8 consecutive
-// k entries (one 16-byte store); K is zero-padded to Kpad.
+// k entries (one 16-byte store); K is zero-padded to Kpad.  Shapes are template constants for the
+// CIFAR case so that every div/mod folds into multiply-shift.
+template <int C, int H, int W, int KH, int KW>
+__global__ void __launch_bounds__(256) im2col_nchw_fixed_kernel(const __nv_bfloat16* __restrict__ x, uint4* __restrict__ col,
+                                                                 int B) {
+  constexpr int OH = H - KH + 1, OW = W - KW + 1, K = KH * KW * C, Kpad8 = (K + 7) / 8;
+  // one block = one image: stage it in shared memory, then emit its OH*OW rows
+  __shared__ __nv_bfloat16 img[C * H * W];
+  for (int b = blockIdx.x; b < B; b += gridDim.x) {
+    const uint4* src = reinterpret_cast<const uint4*>(x + static_cast<long long>(b) * C * H * W);
+    for (int i = threadIdx.x; i < C * H * W / 8; i += blockDim.x) reinterpret_cast<uint4*>(img)[i] = src[i];
+    __syncthreads();
+    uint4* dst = col + static_cast<long long>(b) * OH * OW * Kpad8;
+    for (int i = threadIdx.x; i < OH * OW * Kpad8; i += blockDim.x) {
+      const int k8 = i % Kpad8, pix = i / Kpad8;
+      const int ox = pix % OW, oy = pix / OW;
+      __align__(16) __nv_bfloat16 v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int k = k8 * 8 + j;
+        const int c = k % C, kw = (k / C) % KW, kh = k / (C * KW);
+        v[j] = (k < K) ? img[(c * H + oy + kh) * W + ox + kw] : __float2bfloat16_rn(0.f);
+      }
+      dst[i] = *reinterpret_cast<const uint4*>(v);
+    }
+    __syncthreads();
+  }
+}
 __global__ void im2col_nchw_kernel(const __nv_bfloat16* __restrict__ x, uint4* __restrict__ col, int B, int C, int H,
                                    int W, int KH, int KW, int OH, int OW, int Kpad8) {
   const long long total = static_cast<long long>(B) * OH * OW * Kpad8;
@@ -449,7 +476,12 @@ extern "C" int tadnn_im2col(const void* x, void* col, int B, int C, int H, int W
   const int OH = H - KH + 1, OW = W - KW + 1;
   TADNN_REQUIRE(B > 0 && OH > 0 && OW > 0, "im2col: bad shape");
   TADNN_REQUIRE(Kpad % 8 == 0 && Kpad >= C * KH * KW, "im2col: Kpad=%d must be a multiple of 8 and >= %d", Kpad, C * KH * KW);
-  if (nchw) {
+  if (nchw && C == 3 && H == 32 && W == 32 && KH == 5 && KW == 5 && Kpad == 80 &&
+      (reinterpret_cast<uintptr_t>(x) & 15) == 0) {
+    const int blocks = B < sm_count() * 8 ? B : sm_count() * 8;
+    im2col_nchw_fixed_kernel<3, 32, 32, 5, 5><<<blocks, 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), static_cast<uint4*>(col), B);
+    TADNN_LAUNCH_CHECK("im2col_nchw");
+  } else if (nchw) {
     const long long total = static_cast<long long>(B) * OH * OW * (Kpad / 8);
     im2col_nchw_kernel<<<grid_for(total, 256), 256, 0, stream>>>(static_cast<const __nv_bfloat16*>(x), static_cast<uint4*>(col), B, C, H, W, KH, KW, OH, OW, Kpad / 8);
     TADNN_LAUNCH_CHECK("im2col_nchw");

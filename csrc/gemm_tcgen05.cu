@@ -40,7 +40,8 @@ struct Cfg {
   static constexpr int kStageBytes = kABytes + kBBytes;
   // keep the ring <= ~200 KB
   static constexpr int kStages = (BN == 256) ? 4 : (BN == 128 ? 6 : 8);
-  static constexpr int kSmemBytes = kStages * kStageBytes + 1024;  // +1024 alignment slack
+  static constexpr int kStagingBytes = 4 * 2 * 4096;  // 4 epilogue warps x 2 buffers x (32 rows x 128 B)
+  static constexpr int kSmemBytes = kStages * kStageBytes + kStagingBytes + 1024;  // +1024 alignment slack
   static constexpr uint32_t kTmemCols = (2 * BN <= 128) ? 128 : (2 * BN <= 256 ? 256 : 512);
 };
 
@@ -58,6 +59,11 @@ struct DevArgs {
   void* push[8];
   int push_ldc;
   int push_col_offset;
+  int tma_store;  // bf16 output through shared memory + cp.async.bulk.tensor stores
+};
+
+struct PushMaps {
+  CUtensorMap m[8];
 };
 
 __device__ __forceinline__ void red_add_v4(float* p, float a, float b, float c, float d) {
@@ -121,7 +127,9 @@ __device__ __forceinline__ void store_row32(void* base, int ld, int c_fp32, int 
 template <bool A_MN, bool B_MN, int BN>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
-                         const __grid_constant__ CUtensorMap tma_b, const DevArgs p) {
+                         const __grid_constant__ CUtensorMap tma_b,
+                         const __grid_constant__ CUtensorMap tma_c,
+                         const __grid_constant__ PushMaps tma_push, const DevArgs p) {
   using C = Cfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B tiles need 1024-byte alignment.
@@ -132,6 +140,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   __shared__ __align__(8) uint64_t tmem_full_bar[2];
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];
   __shared__ uint32_t tmem_base_smem;
+  __shared__ __align__(16) float s_bias[4][64];
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -252,6 +261,74 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     const int wg = warp & 3;  // TMEM lane quarter this warp may touch
     int acc = 0;
     uint32_t acc_phase = 0;
+    if (p.tma_store) {
+      // bf16 output: TMEM -> registers -> (bias, act, cast) -> SWIZZLE_128B staging in shared
+      // memory -> one bulk tensor store per 32-row x 64-column slab (full 128-byte lines, OOB
+      // clipped by the TMA unit; the same slab is also stored to every push map = fused all-gather).
+      uint8_t* stg = smem + C::kStages * C::kStageBytes + wg * 8192;
+      float* sb = s_bias[wg];
+      int buf = 0;
+      for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
+        const int tile = w / splits;
+        const int m_blk = tile % num_m;
+        const int n_blk = tile / num_m;
+        mbar_wait(&tmem_full_bar[acc], acc_phase);
+        tc_fence_after_sync();
+        const int row0 = m_blk * BM + wg * 32;
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(wg * 32) << 16) +
+                               static_cast<uint32_t>(acc * BN);
+#pragma unroll 1
+        for (int c = 0; c < BN / 64; ++c) {
+          const int col0 = n_blk * BN + c * 64;
+          if (col0 >= p.N) break;  // warp-uniform
+          if (p.bias != nullptr) {
+            sb[lane] = (col0 + lane < p.N) ? __ldg(p.bias + col0 + lane) : 0.f;
+            sb[32 + lane] = (col0 + 32 + lane < p.N) ? __ldg(p.bias + col0 + 32 + lane) : 0.f;
+          }
+          uint32_t r0[32], r1[32];
+          tmem_ld_32x32b_x32(taddr + static_cast<uint32_t>(c * 64), r0);
+          tmem_ld_32x32b_x32(taddr + static_cast<uint32_t>(c * 64 + 32), r1);
+          if (lane == 0) asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory");  // staging[buf] free
+          tmem_ld_wait();
+          __syncwarp();
+          uint8_t* dst = stg + buf * 4096 + lane * 128;
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {  // 8 x 16-byte chunks = 64 bf16 columns of this row
+            float v[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const int col = j * 8 + e;
+              float x = __uint_as_float(col < 32 ? r0[col] : r1[col - 32]) * p.alpha;
+              if (p.bias != nullptr) x += sb[col];
+              v[e] = apply_act(x, p.act);
+            }
+            uint4 u;
+            u.x = pack_bf16x2(v[0], v[1]);
+            u.y = pack_bf16x2(v[2], v[3]);
+            u.z = pack_bf16x2(v[4], v[5]);
+            u.w = pack_bf16x2(v[6], v[7]);
+            *reinterpret_cast<uint4*>(dst + ((j ^ (lane & 7)) << 4)) = u;
+          }
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0 && row0 < p.M) {
+            tma_store_2d(&tma_c, stg + buf * 4096, col0, row0);
+            for (int q = 0; q < p.n_push; ++q)
+              tma_store_2d(&tma_push.m[q], stg + buf * 4096, p.push_col_offset + col0, row0);
+            asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+          }
+          buf ^= 1;
+        }
+        tc_fence_before_sync();
+        mbar_arrive(&tmem_empty_bar[acc]);
+        if (++acc == 2) {
+          acc = 0;
+          acc_phase ^= 1;
+        }
+      }
+      if (lane == 0) asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");  // stores landed before exit
+      __syncwarp();
+    } else {
     for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
       const int tile = w / splits;
       const int m_blk = tile % num_m;
@@ -289,6 +366,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         acc_phase ^= 1;
       }
     }
+    }
   }
 
   tc_fence_before_sync();
@@ -322,6 +400,7 @@ EncodeTiledFn get_encode_fn() {
 // 2-D bf16 tensor [rows, cols] (cols contiguous, pitch ld elements); box = 64 cols x box_rows.
 int make_tmap(CUtensorMap* out, const void* ptr, long long rows, long long cols, long long ld,
               int box_rows) {
+  memset(out, 0, sizeof(*out));
   EncodeTiledFn fn = get_encode_fn();
   TADNN_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled not available from the driver");
   TADNN_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "TMA operand %p is not 16-byte aligned", ptr);
@@ -341,8 +420,20 @@ int make_tmap(CUtensorMap* out, const void* ptr, long long rows, long long cols,
 template <bool A_MN, bool B_MN, int BN>
 int launch(const tadnn_gemm_args* a, const DevArgs& d, cudaStream_t stream) {
   using C = Cfg<BN>;
-  CUtensorMap ta, tb;
+  CUtensorMap ta, tb, tc;
+  PushMaps tp;
+  memset(&tc, 0, sizeof(tc));
+  memset(&tp, 0, sizeof(tp));
   int rc;
+  if (d.tma_store) {
+    // C / push targets: [M, ld] bf16, stored in 32-row x 64-column slabs
+    rc = make_tmap(&tc, d.C, a->M, a->N, d.ldc, 32);
+    if (rc) return rc;
+    for (int q = 0; q < d.n_push; ++q) {
+      rc = make_tmap(&tp.m[q], d.push[q], a->M, static_cast<long long>(d.push_col_offset) + a->N, d.push_ldc, 32);
+      if (rc) return rc;
+    }
+  }
   // K-major operand: tensor [MN, K], box 64(K) x tile rows.  MN-major: tensor [K, MN], box 64(MN) x BK.
   rc = A_MN ? make_tmap(&ta, a->A, a->K, a->M, a->lda, BK) : make_tmap(&ta, a->A, a->M, a->K, a->lda, BM);
   if (rc) return rc;
@@ -358,7 +449,7 @@ int launch(const tadnn_gemm_args* a, const DevArgs& d, cudaStream_t stream) {
   const int splits = d.split_k > 1 ? d.split_k : 1;
   const int work = num_m * num_n * splits;
   const int grid = work < sm_count() ? work : sm_count();
-  kern<<<grid, kThreads, C::kSmemBytes, stream>>>(ta, tb, d);
+  kern<<<grid, kThreads, C::kSmemBytes, stream>>>(ta, tb, tc, tp, d);
   TADNN_LAUNCH_CHECK("gemm_bf16_tcgen05");
   return 0;
 }
@@ -406,6 +497,12 @@ extern "C" int tadnn_gemm_bf16(const tadnn_gemm_args* a, tadnn_stream_t stream_)
   d.n_push = a->n_push;
   for (int i = 0; i < a->n_push; ++i) d.push[i] = a->push[i];
   d.push_ldc = a->push_ldc; d.push_col_offset = a->push_col_offset;
+  {
+    bool ok = !a->c_fp32 && !atomic && (a->ldc % 8 == 0) && ((reinterpret_cast<uintptr_t>(a->C) & 15) == 0);
+    for (int i = 0; i < a->n_push && ok; ++i)
+      ok = (a->push_ldc % 8 == 0) && ((reinterpret_cast<uintptr_t>(a->push[i]) & 15) == 0) && (a->push_col_offset % 8 == 0);
+    d.tma_store = ok ? 1 : 0;
+  }
 
   int bn = a->tile_n;
   if (bn == 0) bn = a->N <= 64 ? 64 : (a->N <= 128 ? 128 : 256);

@@ -223,6 +223,26 @@ __global__ void colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* _
   }
 }
 
+// Bias gradient of conv+ReLU+maxpool taken at the POOLED resolution: the un-pooled gradient is
+// zero except at each window's arg-max, so  sum_pixels d(conv out)[., c] = sum_windows dy[., c] * (y > 0).
+// Reads k*k times less data than a column sum over the un-pooled gradient.
+__global__ void colsum_relu_mask_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y,
+                                        float* __restrict__ out, long long R, int C) {
+  __shared__ float part[4][64];
+  for (int c0 = 0; c0 < C; c0 += 64) {
+    const int c = c0 + threadIdx.x;
+    float acc = 0.f;
+    if (c < C)
+      for (long long r = blockIdx.x * 4ll + threadIdx.y; r < R; r += gridDim.x * 4ll)
+        if (__bfloat162float(y[r * C + c]) > 0.f) acc += __bfloat162float(dy[r * C + c]);
+    part[threadIdx.y][threadIdx.x] = acc;
+    __syncthreads();
+    if (threadIdx.y == 0 && c < C)
+      atomicAdd(out + c, part[0][threadIdx.x] + part[1][threadIdx.x] + part[2][threadIdx.x] + part[3][threadIdx.x]);
+    __syncthreads();
+  }
+}
+
 // ---- conv weight layout/dtype conversion -----------------------------------------------------
 // Torch7 SpatialConvolutionMM keeps weight [O, C*KH*KW] with k = (c*KH + kh)*KW + kw.  The GEMMs
 // want bf16 [O, Kpad] with k' = (kh*KW + kw)*C + c (matches the NHWC im2col), zero padded.
@@ -527,6 +547,15 @@ extern "C" int tadnn_colsum_bf16(const void* x, float* out, long long R, int C, 
   if (blocks > sm_count() * 4) blocks = sm_count() * 4;
   colsum_bf16_kernel<<<static_cast<int>(blocks), dim3(64, 4), 0, static_cast<cudaStream_t>(stream_)>>>(static_cast<const __nv_bfloat16*>(x), out, R, C, ld);
   TADNN_LAUNCH_CHECK("colsum_bf16");
+  return 0;
+}
+
+extern "C" int tadnn_colsum_relu_mask(const void* dy, const void* y, float* out, long long R, int C, tadnn_stream_t stream_) {
+  TADNN_REQUIRE(R > 0 && C > 0, "colsum_relu_mask: empty");
+  long long blocks = (R + 63) / 64;
+  if (blocks > sm_count() * 4) blocks = sm_count() * 4;
+  colsum_relu_mask_kernel<<<static_cast<int>(blocks), dim3(64, 4), 0, static_cast<cudaStream_t>(stream_)>>>(static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(y), out, R, C);
+  TADNN_LAUNCH_CHECK("colsum_relu_mask");
   return 0;
 }
 

@@ -164,6 +164,10 @@ int tadnn_maxpool_relu_bwd(const void* dy, const void* y, const void* idx, void*
                            int W, int C, int k, tadnn_stream_t stream);
 /* out[c] += sum_r x[r,c]  (bias gradient; x bf16 [R, ld], out fp32). */
 int tadnn_colsum_bf16(const void* x, float* out, long long R, int C, int ld, tadnn_stream_t stream);
+/* out[c] += sum_r dy[r,c] * (y[r,c] > 0): bias gradient of conv+ReLU+maxpool evaluated on the
+ * pooled tensors (dy, y: bf16 [R, C] contiguous). */
+int tadnn_colsum_relu_mask(const void* dy, const void* y, float* out, long long R, int C,
+                           tadnn_stream_t stream);
 /* Torch7 conv weight [O, C*KH*KW] fp32 (k = (c*KH+kh)*KW+kw)  <->  GEMM operand [O, Kpad] bf16
  * (k' = (kh*KW+kw)*C+c); unpack accumulates: grad += scale * dwp. */
 int tadnn_conv_weight_pack(const float* w, void* wp, int O, int C, int KH, int KW, int Kpad,

@@ -1,0 +1,101 @@
+"""Collective kernels (csrc/comm.cu).
+
+* 1 GPU: the all-reduce kernels run with all ranks emulated inside ONE cooperative launch
+  (rank = blockIdx.y; the recipe forbids separate launches that wait on each other on one GPU).
+* >= 2 GPUs: the real multi-process path (CUDA-IPC symmetric heaps) via torchrun, see
+  tests/_dist_gpu_checks.py.
+"""
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _heap_view(lib, comm, nbytes, owner):
+    from tadnn.parallel.symm import _RawCuda
+    p = C.c_void_p()
+    rank = C.c_int()
+    lib.tadnn_comm_info(comm, C.byref(rank), None, None, None)
+    lib.tadnn_comm_heap(comm, rank, C.byref(p))
+    return torch.as_tensor(_RawCuda(int(p.value), nbytes, owner), device="cuda")
+
+
+@pytest.mark.parametrize("world", [2, 4, 8])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("algo", [1, 2])
+def test_allreduce_emulated_single_launch(world, dtype, algo):
+    from tadnn import _native
+    lib = _native.lib()
+    heap = 4 << 20
+    comms = (C.c_void_p * world)()
+    _native.check(lib.tadnn_comm_create_local(world, C.c_ulonglong(heap), comms), "create_local")
+    try:
+        for n in (5, 1000, 114838):
+            es = 4 if dtype == torch.float32 else 2
+            xs = [torch.randn(n, device="cuda").to(dtype) for _ in range(world)]
+            views = [_heap_view(lib, C.c_void_p(comms[r]), heap, comms).view(dtype)[:n] for r in range(world)]
+            for v, x in zip(views, xs):
+                v.copy_(x)
+            torch.cuda.synchronize()
+            _native.check(lib.tadnn_allreduce_emulated(comms, world, C.c_ulonglong(0), C.c_ulonglong(n),
+                                                       0 if dtype == torch.float32 else 1, C.c_float(1.0 / world),
+                                                       algo, C.c_void_p(_native.stream_ptr())), "allreduce_emulated")
+            torch.cuda.synchronize()
+            ref = torch.stack([x.float() for x in xs]).sum(0) / world
+            tol = 1e-5 if dtype == torch.float32 else 1e-2
+            for v in views:
+                assert (v.float() - ref).abs().max().item() <= tol * max(1.0, ref.abs().max().item())
+            for v in views[1:]:
+                assert torch.equal(v, views[0])  # bit-identical on every rank
+            del es
+    finally:
+        for r in range(world):
+            lib.tadnn_comm_destroy(C.c_void_p(comms[r]))
+
+
+def test_world1_context_and_flat_buffer_sync():
+    """parallelize() on a single GPU: flat symmetric buffer, hooks fire, sync is a no-op average."""
+    import tadnn
+    import tadnn.mpi as mpi
+    from tadnn.models.cifar_cnn import CifarCNN
+    os.environ.setdefault("MASTER_PORT", "29577")
+    h = mpi.TorchMPI().start(True)
+    try:
+        assert h.symm is not None and h.size() == 1
+        m = CifarCNN().cuda()
+        x = torch.randn(32, 3, 32, 32).bfloat16()
+        y = torch.randint(0, 10, (32,))
+        d, t, n = tadnn.parallelize(x, y, m, 32, h, None, 2, verbose=False)
+        assert n == 32 and m._tadnn_flat.symmetric
+        tr = tadnn.BatchTrainer(m, 0.01)
+        before = torch.cat([p.detach().reshape(-1) for p in m.parameters()]).clone()
+        for _ in range(4):
+            tr.step(d.cuda(), t.cuda())
+        torch.cuda.synchronize()
+        assert m._tadnn_sync.syncs == 2 and m.sync_counter == 5
+        after = torch.cat([p.detach().reshape(-1) for p in m.parameters()])
+        assert not torch.equal(before, after)
+    finally:
+        h.stop()
+
+
+@pytest.mark.multigpu
+def test_multiprocess_collectives_via_torchrun():
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    world = 2 if n < 4 else (4 if n < 8 else 8)
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}",
+           "--master-addr", "127.0.0.1", "--master-port", "29561", os.path.join(ROOT, "tests", "_dist_gpu_checks.py")]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT)
+    line = [l for l in p.stdout.splitlines() if l.startswith("{")]
+    assert p.returncode == 0 and line, p.stdout[-2000:] + p.stderr[-2000:]
+    res = json.loads(line[-1])
+    assert res["world"] == world and res["failures"] == []

@@ -85,7 +85,7 @@ class _CnnLoss(torch.autograd.Function):
         _native.check(_native.lib().tadnn_head_backward(C.byref(h), C.c_void_p(_native.stream_ptr())), "tadnn_head_backward")
         # conv2: pool/relu backward into a2's storage, bias grad, wgrad (split-K), dgrad into col2's storage
         da2 = K.maxpool_relu_bwd(dp2, p2, idx2, 5, 5, 3, out=a2.view(B, 5, 5, 64)).view(B * 25, 64)
-        K.colsum_bf16(da2, gb2)
+        K.colsum_relu_mask(dp2, p2, gb2)
         dw2p = K.gemm_bf16(da2, col2, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
                            split_k=K.auto_split_k(64, 1600, B * 25))
         K.conv_wgrad_unpack(dw2p, gw2, 64, 5, 5)
@@ -93,7 +93,7 @@ class _CnnLoss(torch.autograd.Function):
         dp1 = K.col2im(dcol2, B, 64, 9, 9, 5, 5)
         # conv1 (no dgrad: the image needs no gradient)
         da1 = K.maxpool_relu_bwd(dp1, p1, idx1, 28, 28, 3, out=a1.view(B, 28, 28, 64)).view(B * 784, 64)
-        K.colsum_bf16(da1, gb1)
+        K.colsum_relu_mask(dp1, p1, gb1)
         dw1p = K.gemm_bf16(da1, col1, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
                            split_k=K.auto_split_k(64, K1PAD, B * 784, 128), tile_n=128)
         K.conv_wgrad_unpack(dw1p, gw1, 3, 5, 5)

@@ -69,6 +69,15 @@ def colsum_bf16(x: torch.Tensor, out: torch.Tensor):
     return out
 
 
+def colsum_relu_mask(dy: torch.Tensor, y: torch.Tensor, out: torch.Tensor):
+    Cc = y.shape[-1]
+    R = y.numel() // Cc
+    assert dy.is_contiguous() and y.is_contiguous() and dy.numel() == y.numel()
+    _native.check(_native.lib().tadnn_colsum_relu_mask(_p(dy), _p(y), _p(out), C.c_longlong(R), Cc, _s()),
+                  "tadnn_colsum_relu_mask")
+    return out
+
+
 def conv_weight_pack(w: torch.Tensor, Cc: int, KH: int, KW: int, Kpad: int) -> torch.Tensor:
     O = w.shape[0]
     wp = torch.empty((O, Kpad), device=w.device, dtype=torch.bfloat16)
@@ -109,5 +118,5 @@ def auto_split_k(M: int, N: int, K: int, tile_n: int = 256) -> int:
     return max(1, min(kb, 148 // max(1, tiles)))
 
 
-__all__ = ["im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "conv_weight_pack",
+__all__ = ["im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "conv_weight_pack",
            "conv_wgrad_unpack", "head_workspace", "sgd_step", "auto_split_k", "HeadArgs", "gemm_bf16"]

@@ -320,6 +320,46 @@ __global__ void __launch_bounds__(512) reduce_scatter_cols_kernel(CommDev c, siz
   block_barrier(c, channel);
 }
 
+// ---- finalize of the fused GEMM -> reduce-scatter: sum the P slots that the peers' GEMM epilogues
+// pushed into THIS rank's staging buffer, add bias, activate; optionally push the result to every
+// rank (all-gather), which turns the pair into a fused all-reduce.
+__global__ void __launch_bounds__(512) reduce_slots_kernel(CommDev c, size_t slots_off, int rows, int width8 /* width/8 */,
+                                                           float scale, const float* bias, int act,
+                                                           __nv_bfloat16* out_local, size_t out_pitch,
+                                                           size_t push_off, int do_push, int channel) {
+  const int rank = my_rank(c);
+  const size_t total = static_cast<size_t>(rows) * width8;
+  const size_t slot_elems8 = total;  // uint4 units per slot
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const uint4* slots = reinterpret_cast<const uint4*>(c.heap[rank] + slots_off);
+  block_barrier(c, channel);  // every rank's GEMM (and its remote stores) has completed
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const size_t row = i / width8, c8 = i - row * width8;
+    float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int q = 0; q < kMaxRanks; ++q)
+      if (q < c.world) Vec<1>::add(a, slots[q * slot_elems8 + i]);
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      float x = a[e] * scale;
+      if (bias != nullptr) x += bias[(static_cast<size_t>(rank) * width8 + c8) * 8 + e];
+      if (act == 1) x = tanh_f32(x);
+      else if (act == 2) x = fmaxf(x, 0.f);
+      v[e] = x;
+    }
+    const uint4 o = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+    if (out_local != nullptr) *reinterpret_cast<uint4*>(out_local + row * out_pitch + c8 * 8) = o;
+    if (do_push) {
+      const size_t off = push_off + (row * (static_cast<size_t>(width8) * c.world) + static_cast<size_t>(rank) * width8 + c8) * 16;
+#pragma unroll
+      for (int q = 0; q < kMaxRanks; ++q)
+        if (q < c.world) st_peer16(c.heap[q] + off, o);
+    }
+  }
+  block_barrier(c, channel);  // slots may be overwritten / pushed results are visible
+}
+
 int pick_blocks(size_t work_items_per_thread_1, int max_blocks, int cap_default) {
   int cap = max_blocks > 0 ? max_blocks : cap_default;
   if (cap > kMaxBlocks) cap = kMaxBlocks;
@@ -569,5 +609,23 @@ extern "C" int tadnn_reduce_scatter_cols(tadnn_comm* c, unsigned long long off_b
   else
     reduce_scatter_cols_kernel<1><<<blocks, 512, 0, stream>>>(c->dev, off_bytes, dst, dst_pitch, rows, width, scale, bias, act, channel);
   TADNN_LAUNCH_CHECK("reduce_scatter_cols");
+  return 0;
+}
+
+extern "C" int tadnn_reduce_slots(tadnn_comm* c, unsigned long long slots_off, int rows, int width, float scale,
+                                  const float* bias, int act, void* out_local, unsigned long long out_pitch,
+                                  unsigned long long push_off, int do_push, int max_blocks, int channel,
+                                  tadnn_stream_t stream) {
+  if (int rc = validate(c, channel, "reduce_slots")) return rc;
+  TADNN_REQUIRE(rows > 0 && width > 0 && width % 8 == 0, "reduce_slots: width must be a positive multiple of 8");
+  TADNN_REQUIRE(slots_off % 16 == 0 && (!do_push || push_off % 16 == 0), "reduce_slots: offsets must be 16-byte aligned");
+  TADNN_REQUIRE(slots_off + 2ull * rows * width * c->world <= c->heap_bytes, "reduce_slots: slots exceed the heap");
+  TADNN_REQUIRE(out_local == nullptr || ((reinterpret_cast<uintptr_t>(out_local) & 15) == 0 && out_pitch % 8 == 0),
+                "reduce_slots: out_local must be 16-byte aligned with a pitch multiple of 8");
+  const int blocks = pick_blocks(static_cast<size_t>(rows) * (width / 8), max_blocks, 148);
+  reduce_slots_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(
+      c->dev, slots_off, rows, width / 8, scale, bias, act, static_cast<__nv_bfloat16*>(out_local), out_pitch, push_off,
+      do_push, channel);
+  TADNN_LAUNCH_CHECK("reduce_slots");
   return 0;
 }

@@ -60,6 +60,9 @@ struct DevArgs {
   int push_ldc;
   int push_col_offset;
   int tma_store;  // bf16 output through shared memory + cp.async.bulk.tensor stores
+  int rs_width;   // >0: reduce-scatter push: column block q = col/rs_width goes ONLY to push map q
+  const __nv_bfloat16* aux;  // optional [M, ld_aux] bf16; epilogue multiplies by (1 - aux^2) (tanh backward)
+  int ld_aux;
 };
 
 struct PushMaps {
@@ -292,15 +295,34 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           tmem_ld_wait();
           __syncwarp();
           uint8_t* dst = stg + buf * 4096 + lane * 128;
+          const int row = row0 + lane;
+          const bool aux_ok = p.aux != nullptr && row < p.M;
+          const __nv_bfloat16* aux_row = p.aux + static_cast<size_t>(row < p.M ? row : 0) * p.ld_aux + col0;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {  // 8 x 16-byte chunks = 64 bf16 columns of this row
             float v[8];
+            float ay[8];
+            if (aux_ok) {
+              if (col0 + j * 8 + 8 <= p.N && ((reinterpret_cast<uintptr_t>(aux_row + j * 8) & 15) == 0)) {
+                const uint4 q = *reinterpret_cast<const uint4*>(aux_row + j * 8);
+                float2 f;
+                f = unpack_bf16x2(q.x); ay[0] = f.x; ay[1] = f.y;
+                f = unpack_bf16x2(q.y); ay[2] = f.x; ay[3] = f.y;
+                f = unpack_bf16x2(q.z); ay[4] = f.x; ay[5] = f.y;
+                f = unpack_bf16x2(q.w); ay[6] = f.x; ay[7] = f.y;
+              } else {
+#pragma unroll
+                for (int e = 0; e < 8; ++e) ay[e] = (col0 + j * 8 + e < p.N) ? __bfloat162float(aux_row[j * 8 + e]) : 0.f;
+              }
+            }
 #pragma unroll
             for (int e = 0; e < 8; ++e) {
               const int col = j * 8 + e;
               float x = __uint_as_float(col < 32 ? r0[col] : r1[col - 32]) * p.alpha;
               if (p.bias != nullptr) x += sb[col];
-              v[e] = apply_act(x, p.act);
+              x = apply_act(x, p.act);
+              if (aux_ok) x *= (1.0f - ay[e] * ay[e]);
+              v[e] = x;
             }
             uint4 u;
             u.x = pack_bf16x2(v[0], v[1]);
@@ -312,9 +334,16 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0 && row0 < p.M) {
-            tma_store_2d(&tma_c, stg + buf * 4096, col0, row0);
-            for (int q = 0; q < p.n_push; ++q)
-              tma_store_2d(&tma_push.m[q], stg + buf * 4096, p.push_col_offset + col0, row0);
+            if (p.rs_width > 0) {
+              // reduce-scatter push: this 64-column slab belongs to rank q; store it into OUR slot
+              // of q's staging buffer (peer memory over NVLink), nowhere else.
+              const int q = col0 / p.rs_width;
+              tma_store_2d(&tma_push.m[q], stg + buf * 4096, col0 - q * p.rs_width, row0);
+            } else {
+              tma_store_2d(&tma_c, stg + buf * 4096, col0, row0);
+              for (int q = 0; q < p.n_push; ++q)
+                tma_store_2d(&tma_push.m[q], stg + buf * 4096, p.push_col_offset + col0, row0);
+            }
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
           }
           buf ^= 1;
@@ -427,11 +456,18 @@ int launch(const tadnn_gemm_args* a, const DevArgs& d, cudaStream_t stream) {
   int rc;
   if (d.tma_store) {
     // C / push targets: [M, ld] bf16, stored in 32-row x 64-column slabs
-    rc = make_tmap(&tc, d.C, a->M, a->N, d.ldc, 32);
-    if (rc) return rc;
-    for (int q = 0; q < d.n_push; ++q) {
-      rc = make_tmap(&tp.m[q], d.push[q], a->M, static_cast<long long>(d.push_col_offset) + a->N, d.push_ldc, 32);
+    if (d.rs_width > 0) {
+      for (int q = 0; q < d.n_push; ++q) {
+        rc = make_tmap(&tp.m[q], d.push[q], a->M, d.rs_width, d.push_ldc, 32);
+        if (rc) return rc;
+      }
+    } else {
+      rc = make_tmap(&tc, d.C, a->M, a->N, d.ldc, 32);
       if (rc) return rc;
+      for (int q = 0; q < d.n_push; ++q) {
+        rc = make_tmap(&tp.m[q], d.push[q], a->M, static_cast<long long>(d.push_col_offset) + a->N, d.push_ldc, 32);
+        if (rc) return rc;
+      }
     }
   }
   // K-major operand: tensor [MN, K], box 64(K) x tile rows.  MN-major: tensor [K, MN], box 64(MN) x BK.
@@ -497,12 +533,23 @@ extern "C" int tadnn_gemm_bf16(const tadnn_gemm_args* a, tadnn_stream_t stream_)
   d.n_push = a->n_push;
   for (int i = 0; i < a->n_push; ++i) d.push[i] = a->push[i];
   d.push_ldc = a->push_ldc; d.push_col_offset = a->push_col_offset;
-  {
+  d.rs_width = a->rs_width;
+  d.aux = static_cast<const __nv_bfloat16*>(a->aux_tanh_out);
+  d.ld_aux = a->ld_aux;
+  if (a->rs_width > 0) {
+    TADNN_REQUIRE(!a->c_fp32 && !atomic, "tadnn_gemm_bf16: rs_width needs a bf16, non-accumulating output");
+    TADNN_REQUIRE(a->rs_width % 64 == 0 && a->n_push * a->rs_width >= a->N && a->push_ldc % 8 == 0,
+                  "tadnn_gemm_bf16: rs_width=%d must be a multiple of 64 with n_push*rs_width >= N and push_ldc %% 8 == 0", a->rs_width);
+    for (int i = 0; i < a->n_push; ++i)
+      TADNN_REQUIRE((reinterpret_cast<uintptr_t>(a->push[i]) & 15) == 0, "tadnn_gemm_bf16: rs push target %d misaligned", i);
+    d.tma_store = 1;
+  } else {
     bool ok = !a->c_fp32 && !atomic && (a->ldc % 8 == 0) && ((reinterpret_cast<uintptr_t>(a->C) & 15) == 0);
     for (int i = 0; i < a->n_push && ok; ++i)
       ok = (a->push_ldc % 8 == 0) && ((reinterpret_cast<uintptr_t>(a->push[i]) & 15) == 0) && (a->push_col_offset % 8 == 0);
     d.tma_store = ok ? 1 : 0;
   }
+  TADNN_REQUIRE(d.aux == nullptr || d.tma_store, "tadnn_gemm_bf16: aux_tanh_out needs the bf16 TMA-store epilogue");
 
   int bn = a->tile_n;
   if (bn == 0) bn = a->N <= 64 ? 64 : (a->N <= 128 ? 128 : 256);

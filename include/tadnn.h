@@ -66,6 +66,13 @@ typedef struct tadnn_gemm_args {
   int push_ldc;
   int push_col_offset;
   int tile_n;        /* 0: auto; else 64, 128 or 256 */
+  /* Fused reduce-scatter push (K-split partial products): rs_width > 0 means output column
+   * block q = col / rs_width is stored ONLY to push[q] (this rank's slot in rank q's staging
+   * buffer, [M, push_ldc] bf16) at column col - q*rs_width; C is not written. */
+  int rs_width;
+  /* Fused tanh backward: multiply the result by (1 - y^2), y = aux_tanh_out[M, ld_aux] bf16. */
+  const void* aux_tanh_out;
+  int ld_aux;
 } tadnn_gemm_args;
 
 int tadnn_gemm_bf16(const tadnn_gemm_args* args, tadnn_stream_t stream);
@@ -135,6 +142,18 @@ int tadnn_reduce_scatter_cols(tadnn_comm* c, unsigned long long off_bytes, void*
                               unsigned long long dst_pitch_elems, int rows, int width, int dtype,
                               float scale, const float* bias, int act, int max_blocks, int channel,
                               tadnn_stream_t stream);
+
+/* Second half of the fused K-split GEMM -> reduce-scatter (K11): the peers' GEMM epilogues have
+ * pushed their partial [rows, width] bf16 tiles into this rank's staging slots (heap[slots_off],
+ * layout [world][rows][width]); this kernel barriers, sums the slots in fp32, scales, adds
+ * bias[rank*width + col], applies act and writes bf16 to out_local (may be NULL) and, if do_push,
+ * to heap[push_off] of EVERY rank viewed as [rows, world*width] (all-gather => all-reduce).
+ * Replaces the allreduceTensor after nn.Linear.updateOutput (nodemodule.lua:52,103) and the
+ * following Tanh (nodemodule.lua:134). */
+int tadnn_reduce_slots(tadnn_comm* c, unsigned long long slots_off, int rows, int width, float scale,
+                       const float* bias, int act, void* out_local, unsigned long long out_pitch,
+                       unsigned long long push_off, int do_push, int max_blocks, int channel,
+                       tadnn_stream_t stream);
 
 /* Emulated (single launch, no cross-launch waiting) variants for 1-GPU numerics tests on a
  * tadnn_comm_create_local() set: performs rank `as_rank`'s share of the math with all

@@ -116,6 +116,47 @@ def main():
         torch.cuda.synchronize()
         expect(f"reduce_scatter {rows}x{w} {dtype}", dst, ref, 1e-5 if dtype == torch.float32 else 1e-2)
 
+    # ---- fused model-parallel MLP (GEMM epilogue -> peer staging slots -> reduce) vs dense fp32
+    from tadnn.parallel.tp import FusedMPMLP
+    for sizes, B in (([1024, 2048, 10], 96), ([512, 1024, 1024, 512], 200)):
+        g = torch.Generator(device="cpu").manual_seed(77)
+        mlp = FusedMPMLP(sizes, mpi=h).to(dev)
+        dense_W, dense_b = [], []
+        for l in range(len(sizes) - 1):
+            Wd = (torch.rand(sizes[l + 1], sizes[l], generator=g) - 0.5) * (2.0 / sizes[l] ** 0.5)
+            bd = (torch.rand(sizes[l + 1], generator=g) - 0.5) * 0.2
+            sh = sizes[l] // P
+            with torch.no_grad():
+                mlp.weights[l].copy_(Wd[:, rank * sh:(rank + 1) * sh])
+                mlp.biases[l].copy_(bd / P)  # effective bias = sum over ranks (Q4)
+            dense_W.append(Wd.to(dev).requires_grad_(True))
+            dense_b.append(bd.to(dev).requires_grad_(True))
+        x = torch.randn(B, sizes[0], generator=g).to(dev)
+        tgt = torch.randn(B, sizes[-1], generator=g).to(dev)
+        y = mlp(x.bfloat16())
+        loss = ((y - tgt) ** 2).mean()
+        loss.backward()
+        a = x.bfloat16().float()
+        for l in range(len(sizes) - 1):
+            a = a @ dense_W[l].t() + dense_b[l]
+            if l < len(sizes) - 2:
+                a = torch.tanh(a)
+        ref_loss = ((a - tgt) ** 2).mean()
+        ref_loss.backward()
+        torch.cuda.synchronize()
+        expect(f"fused MP-MLP {sizes} forward", y, a.detach(), 3e-2)
+        for l in range(len(sizes) - 1):
+            sh = sizes[l] // P
+            gw_ref = dense_W[l].grad[:, rank * sh:(rank + 1) * sh]
+            rel = ((mlp.weights[l].grad - gw_ref).norm() / (gw_ref.norm() + 1e-12)).item()
+            checks += 1
+            if not rel < 4e-2:
+                fails.append(f"fused MP-MLP {sizes} layer {l} dW rel err {rel:.3e}")
+            relb = ((mlp.biases[l].grad - dense_b[l].grad).norm() / (dense_b[l].grad.norm() + 1e-12)).item()
+            checks += 1
+            if not relb < 4e-2:
+                fails.append(f"fused MP-MLP {sizes} layer {l} db rel err {relb:.3e}")
+
     # ---- device barrier stress
     for _ in range(500):
         ctx.barrier()

@@ -20,7 +20,8 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False,
               out_dtype: torch.dtype = torch.bfloat16, bias: torch.Tensor | None = None,
               act: str | None = None, alpha: float = 1.0, accumulate: bool = False,
               split_k: int = 0, push=None, push_col_offset: int = 0, push_ldc: int = 0,
-              tile_n: int = 0, stream=None) -> torch.Tensor:
+              tile_n: int = 0, rs_width: int = 0, aux_tanh_out: torch.Tensor | None = None,
+              stream=None) -> torch.Tensor:
     """out[M,N] = act(alpha * A·Bᵀ + bias).
 
     a: [M,K] (or [K,M] if a_mn_major), b: [N,K] (or [K,N] if b_mn_major); bf16, last dim
@@ -33,17 +34,23 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False,
     M, K = (a.shape[1], a.shape[0]) if a_mn_major else (a.shape[0], a.shape[1])
     N, Kb = (b.shape[1], b.shape[0]) if b_mn_major else (b.shape[0], b.shape[1])
     assert K == Kb, f"inner dims differ: {K} vs {Kb}"
-    if out is None:
+    if rs_width > 0:
+        assert out is None and push, "rs_width: partial tiles go to `push` only"
+    if out is None and rs_width == 0:
         out = torch.empty((M, N), device=a.device, dtype=out_dtype)
-    assert out.shape == (M, N) and out.stride(1) == 1
-    assert out.dtype in (torch.bfloat16, torch.float32)
+    if out is not None:
+        assert out.shape == (M, N) and out.stride(1) == 1
+        assert out.dtype in (torch.bfloat16, torch.float32)
     if bias is not None:
         assert bias.dtype == torch.float32 and bias.numel() == N and bias.is_contiguous()
     args = _native.GemmArgs()
     args.M, args.N, args.K = M, N, K
     args.A, args.lda, args.a_mn_major = a.data_ptr(), a.stride(0), int(a_mn_major)
     args.B, args.ldb, args.b_mn_major = b.data_ptr(), b.stride(0), int(b_mn_major)
-    args.C, args.ldc, args.c_fp32 = out.data_ptr(), out.stride(0), int(out.dtype == torch.float32)
+    if out is not None:
+        args.C, args.ldc, args.c_fp32 = out.data_ptr(), out.stride(0), int(out.dtype == torch.float32)
+    else:
+        args.C, args.ldc, args.c_fp32 = 0, N, 0
     args.bias = _native.ptr(bias)
     args.act = _ACT[act]
     args.alpha = float(alpha)
@@ -56,6 +63,10 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False,
     args.push_ldc = int(push_ldc)
     args.push_col_offset = int(push_col_offset)
     args.tile_n = int(tile_n)
+    args.rs_width = int(rs_width)
+    if aux_tanh_out is not None:
+        assert aux_tanh_out.dtype == torch.bfloat16 and aux_tanh_out.stride(1) == 1 and aux_tanh_out.shape == (M, N)
+        args.aux_tanh_out, args.ld_aux = aux_tanh_out.data_ptr(), aux_tanh_out.stride(0)
     rc = _native.lib().tadnn_gemm_bf16(C.byref(args), C.c_void_p(_native.stream_ptr(stream)))
     _native.check(rc, "tadnn_gemm_bf16")
     return out

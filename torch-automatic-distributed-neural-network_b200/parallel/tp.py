@@ -1,5 +1,248 @@
-"""placeholder (filled in below)"""
-class FusedMPMLP:  # noqa: D101
+"""Fused model-parallel MLP: the reference's ``MPInitialLinear -> MPTanh -> MPBaseLinear ...``
+stack (README.md:97-101; nodemodule.lua:34-174) as B200 kernels.
+
+Parameter layout is the reference's: rank r holds ``W_r [o, i/P]`` (input-dimension split) and a
+full ``bias [o]``; the effective dense layer is ``W = cat_r W_r``, ``b = sum_r b_r``.
+
+Dataflow (what the reference does with a cuBLAS SGEMM + blocking ``allreduceTensor`` per layer
+on replicated activations) becomes, per layer::
+
+    forward   partial_r = a_r · W_rᵀ + b_r           tcgen05 GEMM; its epilogue TMA-stores each
+                                                      64-column slab straight into the OWNER
+                                                      rank's staging slot over NVLink
+              a'_r = tanh( sum_q slot_q )             reduce_slots kernel (barrier + local reduce)
+    backward  g = all_gather(g_r)                     push all-gather (csrc/comm.cu)
+              dW_r = gᵀ · a_r ,  db = colsum(g)       tcgen05 GEMM (MN-major operands, split-K)
+              g'_r = (g · W_r) ⊙ (1 - a_r²)           tcgen05 GEMM, tanh' fused in the epilogue
+
+Activations stay *sharded* between layers (``a'_r`` is exactly the slice the next layer's
+``narrowInput`` would take, nodemodule.lua:16-21), so the forward moves (P-1)/P·B·o elements per
+layer instead of the all-reduce's 2(P-1)/P·B·o, and the redundant full-width tanh of the
+reference disappears.  The backward is the exact gradient (the reference's ``syncTanh`` gather).
+Layers whose width is not a multiple of 64·P (e.g. the 10-way classifier) fall back to a plain
+GEMM + one-shot all-reduce of the small output.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from typing import List, Optional
+
+import torch
+import torch.nn.functional as F
+
+from .. import _native
+from .. import mpi as _mpi
+from . import symm as _symm
+
+
+def _cast_bf16(w: torch.Tensor) -> torch.Tensor:
+    out = torch.empty(w.shape, device=w.device, dtype=torch.bfloat16)
+    _native.check(_native.lib().tadnn_cast_f32_bf16(C.c_void_p(w.data_ptr()), C.c_void_p(out.data_ptr()),
+                                                    C.c_longlong(w.numel()), C.c_void_p(_native.stream_ptr())),
+                  "tadnn_cast_f32_bf16")
+    return out
+
+
+class _Plan:
+    """Per (batch size) symmetric buffers shared by all layers of one FusedMPMLP."""
+
+    def __init__(self, ctx: _symm.SymmContext, B: int, sizes: List[int]):
+        P = ctx.world
+        self.B = B
+        big = [o for o in sizes[1:] if o % (64 * P) == 0]
+        maxo = max(big) if big else 0
+        allo = max(sizes[1:])
+        allo_pad = (allo + 7) // 8 * 8
+        self.slots_off = ctx.alloc(2 * B * maxo) if maxo else 0      # [P][B][o/P] bf16 == B*o elements
+        self.gfull_off = ctx.alloc(2 * B * allo_pad)                  # [B, o] bf16 (gathered grads / outputs)
+        self.small = ctx.empty((B * allo_pad,), torch.float32)        # small-layer partial sums (all-reduced in place)
+
+
+class _Fn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, mod: "FusedMPMLP", x: torch.Tensor, *params):
+        from ..ops.gemm import gemm_bf16
+        sc = mod._ctx()
+        P, r = sc.world, sc.rank
+        L = mod.num_layers
+        B = x.shape[0]
+        plan = mod._plan(B)
+        lib = _native.lib()
+        st = C.c_void_p(_native.stream_ptr())
+        xb = x if x.dtype == torch.bfloat16 else x.to(torch.bfloat16)
+        w0 = mod.sizes[0] // P
+        a = xb[:, r * w0:(r + 1) * w0]  # narrowInput: a strided view, consumed in place by TMA
+        acts = [a]
+        wbs = []
+        out = None
+        for l in range(L):
+            W, b = params[2 * l], params[2 * l + 1]
+            o = mod.sizes[l + 1]
+            last = l == L - 1
+            wb = _cast_bf16(W)
+            wbs.append(wb)
+            if o % (64 * P) == 0:
+                w = o // P
+                push = [sc.heap_ptrs[q] + plan.slots_off + r * B * w * 2 for q in range(P)]
+                gemm_bf16(a, wb, bias=b, push=push, push_ldc=w, rs_width=w)
+                nxt = torch.empty((B, w), device=x.device, dtype=torch.bfloat16)
+                _native.check(lib.tadnn_reduce_slots(
+                    sc.handle, C.c_ulonglong(plan.slots_off), B, w, C.c_float(1.0), None, 0 if last else 1,
+                    C.c_void_p(nxt.data_ptr()), C.c_ulonglong(w), C.c_ulonglong(plan.gfull_off), int(last), 0,
+                    _symm.CH_TP, st), "tadnn_reduce_slots")
+                if last:
+                    out = sc.tensor(plan.gfull_off, (B, o), torch.bfloat16).float()
+                a = nxt
+            else:
+                part = plan.small[:B * o].view(B, o)
+                gemm_bf16(a, wb, bias=b, out=part, out_dtype=torch.float32, tile_n=64)
+                if P > 1:
+                    sc.allreduce_(part, 1.0, channel=_symm.CH_TP)
+                y = part.clone()
+                if last:
+                    out = y
+                else:
+                    assert o % (8 * P) == 0, f"hidden width {o} must be a multiple of 8*P"
+                    a = torch.tanh(y[:, r * (o // P):(r + 1) * (o // P)]).to(torch.bfloat16).contiguous()
+            if not last:
+                acts.append(a)
+        ctx.mod, ctx.B = mod, B
+        ctx.save_for_backward(*acts, *wbs)
+        return out
+
+    @staticmethod
+    def backward(ctx, gy):
+        from ..ops.cnn import auto_split_k, colsum_bf16
+        from ..ops.gemm import gemm_bf16
+        mod, B = ctx.mod, ctx.B
+        sc = mod._ctx()
+        P, r = sc.world, sc.rank
+        L = mod.num_layers
+        plan = mod._plan(B)
+        saved = ctx.saved_tensors
+        acts, wbs = saved[:L], saved[L:]
+        grads: List[Optional[torch.Tensor]] = [None] * (2 * L)
+        dev = gy.device
+        # replicated gradient of the last layer's output, bf16, pitch padded to a multiple of 8
+        oL = mod.sizes[L]
+        pitch = (oL + 7) // 8 * 8
+        g_full = sc.tensor(plan.gfull_off, (B, pitch), torch.bfloat16)
+        if pitch != oL:
+            g_full.zero_()
+        g_full[:, :oL].copy_(gy)
+        gx = None
+        for l in range(L - 1, -1, -1):
+            o, i_sh = mod.sizes[l + 1], mod.sizes[l] // P
+            pitch = (o + 7) // 8 * 8
+            gv = torch.as_strided(g_full, (B, o), (pitch, 1))  # [B, o] with row pitch `pitch`
+            a = acts[l]
+            # dW_r [o, i/P] = gᵀ · a_r   (A: g stored [K=B, M=o];  B: a_r stored [K=B, N=i/P])
+            tile_n = 256 if i_sh > 128 else (128 if i_sh > 64 else 64)
+            dW = gemm_bf16(gv, a, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
+                           split_k=auto_split_k(o, i_sh, B, tile_n), tile_n=tile_n)
+            db = torch.zeros(o, device=dev, dtype=torch.float32)
+            colsum_bf16(gv, db)
+            grads[2 * l], grads[2 * l + 1] = dW, db
+            need_dx = l > 0 or ctx.needs_input_grad[1]
+            if not need_dx:
+                break
+            # g'_r [B, i/P] = (g · W_r) (⊙ tanh' of the layer input if that input is a tanh output)
+            gr = gemm_bf16(gv, wbs[l], b_mn_major=True, aux_tanh_out=a if l > 0 else None)
+            if l > 0 or P > 1:
+                w_prev = i_sh
+                if P > 1:
+                    sc.allgather_cols_offset(gr, plan.gfull_off, _symm.CH_TP)
+                    g_full = sc.tensor(plan.gfull_off, (B, w_prev * P), torch.bfloat16)
+                else:
+                    g_full = gr
+            if l == 0:
+                gx = (g_full if P > 1 else gr).to(gy.dtype).clone()
+        return (None, gx, *grads)
+
+
+class FusedMPMLP(torch.nn.Module):
+    """``sizes = [i, h1, ..., o]``; tanh between layers; parameters in the reference layout."""
+
+    def __init__(self, sizes: List[int], mpi=None, init: str = "reference"):
+        super().__init__()
+        h = mpi if mpi is not None else _mpi.current()
+        self._mpi = mpi
+        P = h.size()
+        self.sizes = [int(s) for s in sizes]
+        self.num_layers = len(sizes) - 1
+        for s in self.sizes[:-1]:
+            assert s % (8 * P) == 0, f"layer input width {s} must be a multiple of 8*P={8 * P}"
+        self.weights = torch.nn.ParameterList()
+        self.biases = torch.nn.ParameterList()
+        for l in range(self.num_layers):
+            i_sh, o = self.sizes[l] // P, self.sizes[l + 1]
+            fan = i_sh if init == "reference" else self.sizes[l]
+            s = 1.0 / math.sqrt(fan)
+            self.weights.append(torch.nn.Parameter(torch.empty(o, i_sh).uniform_(-s, s)))
+            self.biases.append(torch.nn.Parameter(torch.empty(o).uniform_(-s, s)))
+        self._plans = {}
+
     @classmethod
-    def from_sequential(cls, model, **kw):
-        raise NotImplementedError
+    def from_sequential(cls, model, mpi=None):
+        """Share the parameters of an ``MPInitialLinear / MPTanh / MPBaseLinear`` Sequential."""
+        from ..nn import mp
+        lins = [m for m in model.children() if isinstance(m, mp._MPLinear)]
+        assert lins, "no MP linear layers found"
+        kinds = [type(m).__name__ for m in model.children() if not isinstance(m, mp._MPReshape)]
+        for k, name in enumerate(kinds):
+            assert name == ("MPTanh" if k % 2 else ("MPInitialLinear" if k == 0 else "MPBaseLinear")), \
+                f"unsupported MP stack {kinds}"
+        sizes = [lins[0].in_features] + [m.out_features for m in lins]
+        self = cls.__new__(cls)
+        torch.nn.Module.__init__(self)
+        self._mpi = mpi if mpi is not None else lins[0]._mpi
+        self.sizes, self.num_layers = sizes, len(lins)
+        self.weights = torch.nn.ParameterList([m.weight for m in lins])
+        self.biases = torch.nn.ParameterList([m.bias for m in lins])
+        self._plans = {}
+        return self
+
+    # ------------------------------------------------------------------
+    def _handle(self):
+        return self._mpi if self._mpi is not None else _mpi.current()
+
+    def _ctx(self) -> _symm.SymmContext:
+        sc = getattr(self._handle(), "symm", None)
+        if sc is None:
+            raise _native.NativeError("FusedMPMLP needs the symmetric-memory context (mpi.start(True) on CUDA)")
+        return sc
+
+    def _plan(self, B: int) -> _Plan:
+        p = self._plans.get(B)
+        if p is None:
+            p = self._plans[B] = _Plan(self._ctx(), B, self.sizes)
+        return p
+
+    def _params(self):
+        out = []
+        for w, b in zip(self.weights, self.biases):
+            out += [w, b]
+        return out
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        x2 = x.reshape(x.shape[0], -1) if x.dim() > 2 else (x.reshape(1, -1) if x.dim() == 1 else x)
+        assert x2.shape[1] == self.sizes[0], f"expected {self.sizes[0]} input features, got {x2.shape[1]}"
+        h = self._handle()
+        if x2.is_cuda and getattr(h, "symm", None) is not None and _native.available():
+            return _Fn.apply(self, x2.contiguous(), *self._params())
+        return self.reference_forward(x2)
+
+    def reference_forward(self, x2: torch.Tensor) -> torch.Tensor:
+        """Plain PyTorch statement (per-op MP semantics: narrow, linear, sum-all-reduce, tanh)."""
+        from ..nn.mp import _AllReduceSum, _Narrow
+        h = self._handle()
+        a = x2.float()
+        for l in range(self.num_layers):
+            xs = _Narrow.apply(a, h, False) if (a.requires_grad and h.size() > 1) else \
+                a.narrow(1, h.rank() * (a.shape[1] // h.size()), a.shape[1] // h.size())
+            y = F.linear(xs, self.weights[l].float(), self.biases[l].float())
+            if h.size() > 1:
+                y = _AllReduceSum.apply(y, h)
+            a = torch.tanh(y) if l < self.num_layers - 1 else y
+        return a

@@ -223,6 +223,37 @@ __global__ void colsum_bf16_kernel(const __nv_bfloat16* __restrict__ x, float* _
   }
 }
 
+// Wide/tall variant: 16-byte loads, 2-D grid (64-column chunk x row split), one atomic per column
+// per block.  blockDim = (8, 32): x = which 8-column vector of the chunk, y = row lane.
+__global__ void __launch_bounds__(256) colsum_bf16_vec_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ out,
+                                                               long long R, int C, int ld) {
+  __shared__ float part[32][65];
+  const int c = blockIdx.x * 64 + threadIdx.x * 8;
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  if (c < C) {
+    const long long rows_per = (R + gridDim.y - 1) / gridDim.y;
+    const long long r0 = blockIdx.y * rows_per, r1 = min(R, r0 + rows_per);
+    for (long long r = r0 + threadIdx.y; r < r1; r += 32) {
+      const uint4 v = *reinterpret_cast<const uint4*>(x + r * ld + c);
+      float2 f;
+      f = unpack_bf16x2(v.x); acc[0] += f.x; acc[1] += f.y;
+      f = unpack_bf16x2(v.y); acc[2] += f.x; acc[3] += f.y;
+      f = unpack_bf16x2(v.z); acc[4] += f.x; acc[5] += f.y;
+      f = unpack_bf16x2(v.w); acc[6] += f.x; acc[7] += f.y;
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) part[threadIdx.y][threadIdx.x * 8 + e] = acc[e];
+  __syncthreads();
+  const int t = threadIdx.y * 8 + threadIdx.x;
+  if (t < 64 && blockIdx.x * 64 + t < C) {
+    float sum = 0.f;
+#pragma unroll 8
+    for (int y = 0; y < 32; ++y) sum += part[y][t];
+    atomicAdd(out + blockIdx.x * 64 + t, sum);
+  }
+}
+
 // Bias gradient of conv+ReLU+maxpool taken at the POOLED resolution: the un-pooled gradient is
 // zero except at each window's arg-max, so  sum_pixels d(conv out)[., c] = sum_windows dy[., c] * (y > 0).
 // Reads k*k times less data than a column sum over the un-pooled gradient.
@@ -543,6 +574,15 @@ extern "C" int tadnn_maxpool_relu_bwd(const void* dy, const void* y, const void*
 
 extern "C" int tadnn_colsum_bf16(const void* x, float* out, long long R, int C, int ld, tadnn_stream_t stream_) {
   TADNN_REQUIRE(R > 0 && C > 0, "colsum: empty");
+  if (C % 8 == 0 && ld % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 15) == 0) {
+    const int cx = (C + 63) / 64;
+    long long ry = (4ll * sm_count() + cx - 1) / cx;
+    if (ry > (R + 255) / 256) ry = (R + 255) / 256;
+    if (ry < 1) ry = 1;
+    colsum_bf16_vec_kernel<<<dim3(cx, static_cast<unsigned>(ry)), dim3(8, 32), 0, static_cast<cudaStream_t>(stream_)>>>(static_cast<const __nv_bfloat16*>(x), out, R, C, ld);
+    TADNN_LAUNCH_CHECK("colsum_bf16");
+    return 0;
+  }
   long long blocks = (R + 63) / 64;
   if (blocks > sm_count() * 4) blocks = sm_count() * 4;
   colsum_bf16_kernel<<<static_cast<int>(blocks), dim3(64, 4), 0, static_cast<cudaStream_t>(stream_)>>>(static_cast<const __nv_bfloat16*>(x), out, R, C, ld);

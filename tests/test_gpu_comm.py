@@ -99,3 +99,35 @@ def test_multiprocess_collectives_via_torchrun():
     assert p.returncode == 0 and line, p.stdout[-2000:] + p.stderr[-2000:]
     res = json.loads(line[-1])
     assert res["world"] == world and res["failures"] == []
+
+
+def test_fused_mp_mlp_world1_matches_dense():
+    """FusedMPMLP on one GPU (P=1): GEMM -> reduce-scatter push into the own staging slot ->
+    reduce_slots(+tanh), fused tanh-backward dgrad, wgrad; vs dense fp32 autograd."""
+    import tadnn.mpi as mpi
+    from tadnn.parallel.tp import FusedMPMLP
+    os.environ.setdefault("MASTER_PORT", "29578")
+    h = mpi.TorchMPI().start(True)
+    try:
+        torch.manual_seed(0)
+        sizes, B = [256, 512, 128, 10], 200
+        m = FusedMPMLP(sizes, mpi=h).cuda()
+        x = torch.randn(B, sizes[0], device="cuda")
+        tgt = torch.randn(B, sizes[-1], device="cuda")
+        y = m(x.bfloat16())
+        ((y - tgt) ** 2).mean().backward()
+        a = x.bfloat16().float()
+        Ws = [w.detach().clone().requires_grad_(True) for w in m.weights]
+        bs = [b.detach().clone().requires_grad_(True) for b in m.biases]
+        for l in range(3):
+            a = a @ Ws[l].t() + bs[l]
+            if l < 2:
+                a = torch.tanh(a)
+        ((a - tgt) ** 2).mean().backward()
+        assert (y - a.detach()).abs().max().item() < 3e-2 * max(1.0, a.abs().max().item())
+        for l in range(3):
+            rel = ((m.weights[l].grad - Ws[l].grad).norm() / Ws[l].grad.norm()).item()
+            relb = ((m.biases[l].grad - bs[l].grad).norm() / bs[l].grad.norm()).item()
+            assert rel < 4e-2 and relb < 4e-2, (l, rel, relb)
+    finally:
+        h.stop()

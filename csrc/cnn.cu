@@ -9,6 +9,8 @@
 // log-softmax, NLL loss and all of their gradients) is ONE fused kernel per direction.
 #include "common.cuh"
 
+#include <mutex>
+
 namespace tadnn {
 namespace {
 
@@ -656,6 +658,60 @@ extern "C" int tadnn_head_forward(const tadnn_head_args* h, void* workspace, tad
   TADNN_REQUIRE(smem <= 96 * 1024, "head_forward: shared memory %zu too large", smem);
   head_fwd_kernel<<<blocks, 256, smem, stream>>>(a);
   TADNN_LAUNCH_CHECK("head_fwd");
+  return 0;
+}
+
+// ---- allocation-free variant of the classifier-head forward -------------------------------------
+// Some callers of this library are not in a position to hand us a workspace, because they cannot
+// allocate device memory where the call happens: a serving or control loop that must never hit
+// cudaMalloc (it synchronises the whole device and its latency is unbounded), a host program that
+// has already given every byte of device memory to its own pool, or a plain-C client of this ABI
+// that has no allocator wired up at all.  For them the scratch that tadnn_head_forward takes as a
+// pointer lives here instead, in a fixed array inside the library image.  Every GPU that loads
+// libtadnn.so carries these 2 KB until the process exits.
+static __device__ __align__(256) unsigned char tadnn_head_noalloc_scratch[2048];
+
+namespace {
+constexpr int kNoAllocMaxBlocks = 256;                      // partial-sum slots that fit in the array
+constexpr int kNoAllocMaxBatch = kNoAllocMaxBlocks * 8 * 32;  // 8 warps/block, <= 32 samples/warp: 65536
+constexpr size_t kNoAllocCounterOffset = 1024;              // 256 floats of partials, then the counter
+std::mutex g_noalloc_mu;
+void* g_noalloc_ptr[64] = {nullptr};                        // device address of the array, per device
+}  // namespace
+
+extern "C" int tadnn_head_forward_noalloc(const tadnn_head_args* h, tadnn_stream_t stream_) {
+  if (int rc = head_check(h, "head_forward_noalloc")) return rc;
+  TADNN_REQUIRE(h->B <= kNoAllocMaxBatch,
+                "head_forward_noalloc: batch %d exceeds the %d samples the built-in scratch is sized for; "
+                "use tadnn_head_forward with a caller-provided workspace", h->B, kNoAllocMaxBatch);
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  int dev = 0;
+  TADNN_CHECK_CUDA(cudaGetDevice(&dev));
+  TADNN_REQUIRE(dev >= 0 && dev < 64, "head_forward_noalloc: device ordinal %d out of range", dev);
+  const size_t smem = head_fwd_smem(h->D, h->H, h->NC);
+  TADNN_REQUIRE(smem <= 96 * 1024, "head_forward_noalloc: shared memory %zu too large", smem);
+  void* scratch = nullptr;
+  {
+    // One-time set-up per device, with that device current.  In host code the array's name is only
+    // a stand-in; the address a kernel can use has to be asked for.
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    scratch = g_noalloc_ptr[dev];
+    if (scratch == nullptr) {
+      TADNN_CHECK_CUDA(cudaGetSymbolAddress(&scratch, tadnn_head_noalloc_scratch));
+      TADNN_CHECK_CUDA(cudaFuncSetAttribute(head_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+      g_noalloc_ptr[dev] = scratch;
+    }
+  }
+  HeadArgs a = to_dev(h);
+  a.loss_partial = static_cast<float*>(scratch);
+  a.counter = reinterpret_cast<unsigned int*>(static_cast<unsigned char*>(scratch) + kNoAllocCounterOffset);
+  // The array is shared by every call and still holds whatever the previous call left behind.
+  // Only the completion counter has to start at zero; the partial sums are overwritten before use.
+  TADNN_CHECK_CUDA(cudaMemsetAsync(a.counter, 0, sizeof(unsigned int), stream));
+  int blocks = (h->B + 7) / 8;
+  if (blocks > kNoAllocMaxBlocks) blocks = kNoAllocMaxBlocks;
+  head_fwd_kernel<<<blocks, 256, smem, stream>>>(a);
+  TADNN_LAUNCH_CHECK("head_fwd_noalloc");
   return 0;
 }
 

@@ -217,6 +217,18 @@ typedef struct tadnn_head_args {
 int tadnn_head_workspace_bytes(int B);
 int tadnn_head_forward(const tadnn_head_args* a, void* workspace, tadnn_stream_t stream);
 int tadnn_head_backward(const tadnn_head_args* a, tadnn_stream_t stream);
+/* Same result as tadnn_head_forward, for callers that cannot give it a workspace because they
+ * cannot allocate device memory at the point of the call (a latency-bound loop that must stay
+ * clear of cudaMalloc, a host that has already committed all device memory to its own pool, a C
+ * client with no allocator).  This entry point has no counterpart in the reference.
+ * The scratch is a fixed 2 KB array inside the library; the call allocates nothing (no
+ * cudaMalloc / cudaFree, no allocating library routine).
+ *  - Limit: a->B <= 65536 samples; larger batches are refused with an error.
+ *  - The first call on each device looks up the array's device address and sets a kernel
+ *    attribute; make that first call before any stream capture is begun on that device.
+ *  - All calls on one device share the array: two calls whose kernels can overlap on the GPU
+ *    (different streams) race on it.  Calls on one stream are safe back to back. */
+int tadnn_head_forward_noalloc(const tadnn_head_args* a, tadnn_stream_t stream);
 
 /* p -= lr * (g + wd * p); optionally g = 0.  Replaces accUpdateGradParameters' in-place step
  * (datamodule.lua:142) for batched training on the flat buffer. */

@@ -194,6 +194,19 @@ int tadnn_conv_weight_pack(const float* w, void* wp, int O, int C, int KH, int K
 int tadnn_conv_wgrad_unpack(const float* dwp, float* grad, int O, int C, int KH, int KW, int Kpad,
                             float scale, tadnn_stream_t stream);
 
+/* Fused first stage of the example CNN (csrc/conv1_fused.cu): implicit-GEMM conv5x5(3->64) on
+ * tcgen05 with the im2col rows generated in shared memory, bias + ReLU + 3x3/3 max-pool in the
+ * epilogue; backward regenerates both GEMM operands on the fly from (x, dp1, p1, idx1).  Replaces
+ * SpatialConvolutionMM + ReLU + SpatialMaxPooling of cifar_example/sgd-torchad_nn-cifar.lua:91-93
+ * and their backward.  x: [B,3,32,32] bf16; p1/dp1: [B,9,9,64] bf16; idx1: [B,9,9,64] bytes.
+ * w_packed: bf16 [64,80] produced by tadnn_conv1_weight_pack from the Torch7 fp32 [64,75] weight;
+ * grad_weight: fp32 [64,75] in the Torch7 order, accumulated (+=). */
+int tadnn_conv1_weight_pack(const float* w, void* w_packed, tadnn_stream_t stream);
+int tadnn_conv1_pool_forward(const void* x, const void* w_packed, const float* bias, void* p1,
+                             void* idx1, int B, tadnn_stream_t stream);
+int tadnn_conv1_pool_backward(const void* x, const void* dp1, const void* p1, const void* idx1,
+                              float* grad_weight, int B, tadnn_stream_t stream);
+
 /* Fused classifier head: dropout -> Linear(D,H)+ReLU -> Linear(H,NC) -> log-softmax -> NLL.
  * Limits: D <= 64, H <= 128, NC <= 32.  fc weights in Torch7 nn.Linear layout, fp32. */
 typedef struct tadnn_head_args {

@@ -61,11 +61,38 @@ def test_colsum_pack_unpack_sgd():
     assert torch.allclose(p, p0 - 0.1 * (g0 + 0.01 * p0), atol=1e-6) and float(gr.abs().sum()) == 0
 
 
+def test_fused_conv1_matches_unfused_kernels():
+    """conv1_pool_forward/backward (implicit GEMM, pooled epilogue) vs im2col + GEMM + pooling kernels."""
+    from tadnn.ops import cnn as K
+    torch.manual_seed(0)
+    for B in (1, 5, 130):
+        x = torch.randn(B, 3, 32, 32, device="cuda").bfloat16()
+        w = torch.randn(64, 75, device="cuda") * 0.2
+        b = torch.randn(64, device="cuda") * 0.1
+        p1, idx1 = K.conv1_pool_forward(x, K.conv1_weight_pack(w), b)
+        col = K.im2col(x, 5, 5, 80, nchw=True)
+        a1 = K.gemm_bf16(col, K.conv_weight_pack(w, 3, 5, 5, 80), bias=b, act="relu", tile_n=64)
+        p1_ref, idx_ref = K.maxpool_fwd(a1.view(B, 28, 28, 64), 3)
+        assert (p1.float() - p1_ref.float()).abs().max().item() <= 0.02 * max(1.0, p1_ref.float().abs().max().item())
+        same = (idx1 == idx_ref) | (p1_ref <= 0)
+        assert same.float().mean().item() > 0.995
+        dp1 = torch.randn(B, 9, 9, 64, device="cuda").bfloat16()
+        gw = torch.zeros(64, 75, device="cuda")
+        K.conv1_pool_backward(x, dp1, p1_ref, idx_ref, gw)
+        da1 = K.maxpool_relu_bwd(dp1, p1_ref, idx_ref, 28, 28, 3).view(B * 784, 64)
+        dwp = K.gemm_bf16(da1, col, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32, tile_n=128)
+        gw_ref = torch.zeros(64, 75, device="cuda")
+        K.conv_wgrad_unpack(dwp, gw_ref, 3, 5, 5)
+        rel = ((gw - gw_ref).norm() / gw_ref.norm()).item()
+        assert rel < 2e-3, (B, rel)
+
+
+@pytest.mark.parametrize("fused", [True, False])
 @pytest.mark.parametrize("B", [1, 7, 64, 300])
-def test_cifar_cnn_loss_and_grads_match_pytorch(B):
+def test_cifar_cnn_loss_and_grads_match_pytorch(B, fused):
     from tadnn.models.cifar_cnn import CifarCNN
     torch.manual_seed(0)
-    m = CifarCNN().cuda().eval()  # eval: dropout off, exact comparison
+    m = CifarCNN(fused_conv1=fused).cuda().eval()  # eval: dropout off, exact comparison
     with torch.no_grad():  # widen the init a little so ReLUs/pools are well exercised
         for p in m.parameters():
             p.mul_(2.0)

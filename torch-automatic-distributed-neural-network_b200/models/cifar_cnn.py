@@ -28,17 +28,22 @@ K1PAD = 80  # 75 -> multiple of 8 (TMA pitch)
 
 class _CnnLoss(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed):
+    def forward(ctx, x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fused_conv1):
         from ..ops import cnn as K
         B = x.shape[0]
         dev = x.device
         xb = x if x.dtype == torch.bfloat16 else x.to(torch.bfloat16)
         xb = xb.contiguous()
-        w1p = K.conv_weight_pack(w1, 3, 5, 5, K1PAD)
         w2p = K.conv_weight_pack(w2, 64, 5, 5, 1600)
-        col1 = K.im2col(xb, 5, 5, K1PAD, nchw=True)                       # [B*784, 80]
-        a1 = K.gemm_bf16(col1, w1p, bias=b1, act="relu", tile_n=64)       # [B*784, 64] == NHWC [B,28,28,64]
-        p1, idx1 = K.maxpool_fwd(a1.view(B, 28, 28, 64), 3)               # [B,9,9,64]
+        if fused_conv1:
+            # implicit-GEMM conv + bias + ReLU + max-pool in one tcgen05 kernel: no col1 / a1 in HBM
+            p1, idx1 = K.conv1_pool_forward(xb, K.conv1_weight_pack(w1), b1)
+            col1 = a1 = xb  # placeholders (the backward regenerates its operands from xb)
+        else:
+            w1p = K.conv_weight_pack(w1, 3, 5, 5, K1PAD)
+            col1 = K.im2col(xb, 5, 5, K1PAD, nchw=True)                       # [B*784, 80]
+            a1 = K.gemm_bf16(col1, w1p, bias=b1, act="relu", tile_n=64)       # [B*784, 64] == NHWC [B,28,28,64]
+            p1, idx1 = K.maxpool_fwd(a1.view(B, 28, 28, 64), 3)               # [B,9,9,64]
         col2 = K.im2col(p1, 5, 5, 1600, nchw=False)                       # [B*25, 1600]
         a2 = K.gemm_bf16(col2, w2p, bias=b2, act="relu", tile_n=64)       # [B*25, 64] == [B,5,5,64]
         p2, idx2 = K.maxpool_fwd(a2.view(B, 5, 5, 64), 3)                 # [B,1,1,64]
@@ -57,6 +62,7 @@ class _CnnLoss(torch.autograd.Function):
                                                        C.c_void_p(_native.stream_ptr())), "tadnn_head_forward")
         ctx.save_for_backward(col1, a1, p1, idx1, col2, a2, p2, idx2, hidden, logp, tgt, w2p, fw1, fb1, fw2, fb2)
         ctx.p_drop, ctx.seed, ctx.B = float(p_drop), int(seed) & 0xFFFFFFFF, B
+        ctx.fused_conv1 = bool(fused_conv1)
         ctx.mark_non_differentiable(logp)
         return loss, logp
 
@@ -92,19 +98,23 @@ class _CnnLoss(torch.autograd.Function):
         dcol2 = K.gemm_bf16(da2, w2p, b_mn_major=True, out=col2)
         dp1 = K.col2im(dcol2, B, 64, 9, 9, 5, 5)
         # conv1 (no dgrad: the image needs no gradient)
-        da1 = K.maxpool_relu_bwd(dp1, p1, idx1, 28, 28, 3, out=a1.view(B, 28, 28, 64)).view(B * 784, 64)
         K.colsum_relu_mask(dp1, p1, gb1)
-        dw1p = K.gemm_bf16(da1, col1, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
-                           split_k=K.auto_split_k(64, K1PAD, B * 784, 128), tile_n=128)
-        K.conv_wgrad_unpack(dw1p, gw1, 3, 5, 5)
+        if ctx.fused_conv1:
+            K.conv1_pool_backward(col1, dp1, p1, idx1, gw1)   # col1 is the bf16 input image here
+        else:
+            da1 = K.maxpool_relu_bwd(dp1, p1, idx1, 28, 28, 3, out=a1.view(B, 28, 28, 64)).view(B * 784, 64)
+            dw1p = K.gemm_bf16(da1, col1, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
+                               split_k=K.auto_split_k(64, K1PAD, B * 784, 128), tile_n=128)
+            K.conv_wgrad_unpack(dw1p, gw1, 3, 5, 5)
         grads = [gw1, gb1, gw2, gb2, gfw1, gfb1, gfw2, gfb2]
-        return (None, None, *grads, None, None)
+        return (None, None, *grads, None, None, None)
 
 
 class CifarCNN(torch.nn.Module, T7Protocol):
-    def __init__(self, dropout: float = 0.5, seed: int = 1):
+    def __init__(self, dropout: float = 0.5, seed: int = 1, fused_conv1: bool = True):
         super().__init__()
         self.dropout = dropout
+        self.fused_conv1 = fused_conv1  # False: im2col + GEMM + separate pooling kernels (generic path)
         self._step = 0
         self._seed = seed
         P = torch.nn.Parameter
@@ -156,7 +166,8 @@ class CifarCNN(torch.nn.Module, T7Protocol):
             p = self.dropout if self.training else 0.0
             seed = (self._seed * 2654435761 + self._step * 40503) & 0xFFFFFFFF
             return _CnnLoss.apply(x, target.to(x.device), self.conv1_weight, self.conv1_bias, self.conv2_weight,
-                                  self.conv2_bias, self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias, p, seed)
+                                  self.conv2_bias, self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias, p, seed,
+                                  self.fused_conv1)
         logp = self.reference_logp(x)
         return F.nll_loss(logp, target.long().to(logp.device)), logp.detach()
 

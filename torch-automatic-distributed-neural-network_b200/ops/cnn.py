@@ -92,6 +92,29 @@ def conv_wgrad_unpack(dwp: torch.Tensor, grad: torch.Tensor, Cc: int, KH: int, K
     return grad
 
 
+def conv1_weight_pack(w: torch.Tensor) -> torch.Tensor:
+    wp = torch.empty((64, 80), device=w.device, dtype=torch.bfloat16)
+    _native.check(_native.lib().tadnn_conv1_weight_pack(_p(w), _p(wp), _s()), "tadnn_conv1_weight_pack")
+    return wp
+
+
+def conv1_pool_forward(x: torch.Tensor, wp: torch.Tensor, bias: torch.Tensor):
+    """x [B,3,32,32] bf16 -> (p1 [B,9,9,64] bf16, idx1 [B,9,9,64] uint8): conv5x5 + bias + ReLU + maxpool3/3."""
+    B = x.shape[0]
+    assert x.dtype == torch.bfloat16 and x.is_contiguous() and tuple(x.shape[1:]) == (3, 32, 32)
+    p1 = torch.empty((B, 9, 9, 64), device=x.device, dtype=torch.bfloat16)
+    idx1 = torch.empty((B, 9, 9, 64), device=x.device, dtype=torch.uint8)
+    _native.check(_native.lib().tadnn_conv1_pool_forward(_p(x), _p(wp), _p(bias), _p(p1), _p(idx1), B, _s()),
+                  "tadnn_conv1_pool_forward")
+    return p1, idx1
+
+
+def conv1_pool_backward(x, dp1, p1, idx1, grad_weight):
+    _native.check(_native.lib().tadnn_conv1_pool_backward(_p(x), _p(dp1), _p(p1), _p(idx1), _p(grad_weight),
+                                                          x.shape[0], _s()), "tadnn_conv1_pool_backward")
+    return grad_weight
+
+
 _head_ws = {}
 
 
@@ -118,5 +141,5 @@ def auto_split_k(M: int, N: int, K: int, tile_n: int = 256) -> int:
     return max(1, min(kb, 148 // max(1, tiles)))
 
 
-__all__ = ["im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "conv_weight_pack",
+__all__ = ["conv1_weight_pack", "conv1_pool_forward", "conv1_pool_backward", "im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "conv_weight_pack",
            "conv_wgrad_unpack", "head_workspace", "sgd_step", "auto_split_k", "HeadArgs", "gemm_bf16"]

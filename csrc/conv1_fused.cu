@@ -31,7 +31,7 @@ constexpr int kWinPerImg = kPH * kPW;        // 81
 constexpr int kWinPerTile = 14;              // 14 windows x 9 pixels = 126 rows of a 128-row tile
 constexpr int kRows = 128;
 constexpr int kBlockBytes = kRows * 128;     // one [128 rows x 64 bf16] SWIZZLE_128B block: 16 KB
-constexpr int kThreads = 288;                // warp 0: MMA/TMEM, warps 1-4: producers, warps 5-8: second group
+constexpr int kThreads = 416;                // warp 0: MMA/TMEM, warps 1-8: two im2col producer groups (one per smem stage), warps 9-12: epilogue / gradient rows
 
 struct Conv1Args {
   const __nv_bfloat16* x;     // [B, 3, 32, 32]
@@ -47,43 +47,80 @@ struct Conv1Args {
 // byte offset of 16-byte chunk j of row r inside a SWIZZLE_128B [rows x 128 B] block
 __device__ __forceinline__ uint32_t sw128(int r, int j) { return static_cast<uint32_t>(r * 128 + ((j ^ (r & 7)) << 4)); }
 
-// Build this thread's im2col row (80 bf16 = 10 chunks) for tile row `r` of tile `tile` and store it
-// into the two swizzled blocks: block0 holds k 0..63, block1 holds k 64..79 in its chunks 0..1.
-__device__ __forceinline__ void build_patch_row(const __nv_bfloat16* __restrict__ x, long long total_win, int tile, int r,
-                                                uint8_t* blk0, uint8_t* blk1) {
+// Stage the (at most two) images a tile touches in shared memory ([2][3][32][32] bf16 = 12 KB) with
+// 1-D bulk async copies (cp.async.bulk, completion on an mbarrier): issued by one thread for the
+// NEXT tile while the group builds the current one.
+constexpr int kImgBytes = kC * kH * kW * 2;  // 6144
+__device__ __forceinline__ void stage_images_async(const __nv_bfloat16* __restrict__ x, int B, int b0, uint8_t* img, uint64_t* bar) {
+  const int n = (b0 + 1 < B) ? 2 : 1;
+  mbar_arrive_expect_tx(bar, static_cast<uint32_t>(n * kImgBytes));
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(img)),
+               "l"(x + static_cast<long long>(b0) * (kC * kH * kW)), "r"(n * kImgBytes), "r"(smem_u32(bar))
+               : "memory");
+}
+
+// Build this thread's im2col row (80 bf16 = 10 chunks) for tile row `r` of tile `tile` from the
+// staged images and store it into the two swizzled blocks: block0 holds k 0..63, block1 holds
+// k 64..79 in its chunks 0..1.  Each (kh, c) run of 5 contiguous input pixels is fetched as three
+// aligned 32-bit words and funnel-shifted by the pixel's column parity; the 2-byte shuffles into
+// patch order are compile-time byte permutes.
+__device__ __forceinline__ void build_patch_row(const uint32_t* __restrict__ img_words, long long total_win, int tile, int b0,
+                                                int r, uint8_t* blk0, uint8_t* blk1) {
   const long long win = static_cast<long long>(tile) * kWinPerTile + r / 9;
   const bool valid = (r < kWinPerTile * 9) && (win < total_win);
-  __align__(16) __nv_bfloat16 v[kKpad];
+  uint32_t out[kKpad / 2];
   if (valid) {
     const int pos = r % 9;
     const int b = static_cast<int>(win / kWinPerImg);
     const int wi = static_cast<int>(win % kWinPerImg);
     const int oy = (wi / kPW) * kPool + pos / 3;
     const int ox = (wi % kPW) * kPool + pos % 3;
-    const __nv_bfloat16* img = x + static_cast<long long>(b) * (kC * kH * kW) + oy * kW + ox;
+    const uint32_t* base = img_words + (b - b0) * (kC * kH * kW / 2) + oy * (kW / 2) + (ox >> 1);
+    const uint32_t sh = static_cast<uint32_t>(ox & 1) * 16u;
+    uint32_t A[kKH * kC], Bv[kKH * kC], Cv[kKH * kC];
 #pragma unroll
     for (int kh = 0; kh < kKH; ++kh)
 #pragma unroll
-      for (int c = 0; c < kC; ++c)
+      for (int c = 0; c < kC; ++c) {
+        const uint32_t* p = base + (c * kH + kh) * (kW / 2);
+        const uint32_t w0 = p[0], w1 = p[1], w2 = p[2];
+        const int g = kh * kC + c;
+        A[g] = __funnelshift_r(w0, w1, sh);    // elements 0,1 of the run
+        Bv[g] = __funnelshift_r(w1, w2, sh);   // elements 2,3
+        Cv[g] = (w2 >> sh) & 0xffffu;          // element 4
+      }
 #pragma unroll
-        for (int kw = 0; kw < kKW; ++kw)
-          v[(kh * kC + c) * kKW + kw] = __ldg(img + (c * kH + kh) * kW + kw);
+    for (int m = 0; m < kKpad / 2; ++m) {
+      uint32_t half[2];
 #pragma unroll
-    for (int k = kK; k < kKpad; ++k) v[k] = __float2bfloat16_rn(0.f);
+      for (int h = 0; h < 2; ++h) {
+        const int k = 2 * m + h;
+        if (k < kK) {
+          const int g = k / kKW, e = k % kKW;
+          const uint32_t wsrc = e < 2 ? A[g] : (e < 4 ? Bv[g] : Cv[g]);
+          half[h] = (e == 1 || e == 3) ? (wsrc >> 16) : (wsrc & 0xffffu);
+        } else {
+          half[h] = 0u;
+        }
+      }
+      out[m] = half[0] | (half[1] << 16);
+    }
   } else {
 #pragma unroll
-    for (int k = 0; k < kKpad; ++k) v[k] = __float2bfloat16_rn(0.f);
+    for (int m = 0; m < kKpad / 2; ++m) out[m] = 0u;
   }
-  const uint4* q = reinterpret_cast<const uint4*>(v);
 #pragma unroll
-  for (int j = 0; j < 8; ++j) *reinterpret_cast<uint4*>(blk0 + sw128(r, j)) = q[j];
+  for (int j = 0; j < 8; ++j)
+    *reinterpret_cast<uint4*>(blk0 + sw128(r, j)) = make_uint4(out[4 * j], out[4 * j + 1], out[4 * j + 2], out[4 * j + 3]);
 #pragma unroll
-  for (int j = 0; j < 2; ++j) *reinterpret_cast<uint4*>(blk1 + sw128(r, j)) = q[8 + j];
+  for (int j = 0; j < 2; ++j)
+    *reinterpret_cast<uint4*>(blk1 + sw128(r, j)) = make_uint4(out[32 + 4 * j], out[33 + 4 * j], out[34 + 4 * j], out[35 + 4 * j]);
 }
 
 // ======================================= forward =======================================
 // smem: W block0 | W block1 (64 rows each, 8 KB) | A[2] x (block0 16 KB + block1 16 KB) | E 16 KB
-constexpr int kFwdSmem = 2 * 8192 + 2 * 2 * kBlockBytes + kRows * 128 + 1024;
+constexpr int kImgStageBytes = 2 * 2 * kC * kH * kW * 2;  // per producer group: double-buffered pair of staged images
+constexpr int kFwdSmem = 2 * 8192 + 2 * 2 * kBlockBytes + kRows * 128 + 2 * kImgStageBytes + 1024;
 
 __global__ void __launch_bounds__(kThreads, 1) conv1_fwd_kernel(const Conv1Args a) {
   extern __shared__ uint8_t smem_raw[];
@@ -92,7 +129,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_fwd_kernel(const Conv1Args 
   uint8_t* w1 = smem + 8192;
   uint8_t* abuf = smem + 16384;                       // stage s: abuf + s*32768 (+0: block0, +16384: block1)
   uint8_t* ebuf = abuf + 2 * 2 * kBlockBytes;         // [128 rows][64 ch] bf16, plain row-major
-  __shared__ __align__(8) uint64_t a_full[2], a_empty[2], t_full[2], t_empty[2];
+  uint8_t* imgbuf = ebuf + kRows * 128;                // [2 groups][2 images] staged input
+  __shared__ __align__(8) uint64_t a_full[2], a_empty[2], t_full[2], t_empty[2], img_full[2][2];
   __shared__ uint32_t tmem_base_smem;
   __shared__ float s_bias[kO];
 
@@ -106,6 +144,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_fwd_kernel(const Conv1Args 
       mbar_init(&a_empty[s], 1);
       mbar_init(&t_full[s], 1);
       mbar_init(&t_empty[s], 128);
+      mbar_init(&img_full[s][0], 1);
+      mbar_init(&img_full[s][1], 1);
     }
     fence_mbar_init();
   }
@@ -147,24 +187,35 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_fwd_kernel(const Conv1Args 
       }
     }
     __syncwarp();
-  } else if (warp <= 4) {
-    // ---------------- producers: one im2col row per thread ----------------
-    const int r = threadIdx.x - 32;
-    int i = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++i) {
-      const int s = i & 1;
-      const uint32_t ph = (i >> 1) & 1;
-      mbar_wait(&a_empty[s], ph ^ 1);
-      uint8_t* b0 = abuf + s * 2 * kBlockBytes;
-      build_patch_row(a.x, total_win, t, r, b0, b0 + kBlockBytes);
+  } else if (warp <= 8) {
+    // ---------------- producers: one im2col row per thread; group g owns smem stage g ----------------
+    const int grp = (warp - 1) >> 2;
+    const int r = (threadIdx.x - 32) & 127;
+    uint8_t* b0p = abuf + grp * 2 * kBlockBytes;
+    uint8_t* img = imgbuf + grp * kImgStageBytes;   // two buffers of 2 images
+    const long long t_first = blockIdx.x + static_cast<long long>(grp) * gridDim.x, t_step = 2ll * gridDim.x;
+    if (r == 0 && t_first < num_tiles)
+      stage_images_async(a.x, a.B, static_cast<int>(t_first * kWinPerTile / kWinPerImg), img, &img_full[grp][0]);
+    int n = 0;
+    for (long long t = t_first; t < num_tiles; t += t_step, ++n) {
+      const int buf = n & 1;
+      const int b0 = static_cast<int>(t * kWinPerTile / kWinPerImg);
+      if (r == 0 && t + t_step < num_tiles)  // prefetch the next tile's images into the other buffer
+        stage_images_async(a.x, a.B, static_cast<int>((t + t_step) * kWinPerTile / kWinPerImg), img + (buf ^ 1) * 2 * kImgBytes,
+                           &img_full[grp][buf ^ 1]);
+      mbar_wait(&img_full[grp][buf], (n >> 1) & 1);
+      mbar_wait(&a_empty[grp], (n & 1) ^ 1);
+      build_patch_row(reinterpret_cast<const uint32_t*>(img + buf * 2 * kImgBytes), total_win, static_cast<int>(t), b0, r, b0p,
+                      b0p + kBlockBytes);
       fence_proxy_async_smem();
-      mbar_arrive(&a_full[s]);
+      mbar_arrive(&a_full[grp]);
+      asm volatile("bar.sync %0, 128;" ::"r"(2 + grp) : "memory");  // everyone is done with img[buf] before it is refilled
     }
   } else {
     // ---------------- epilogue: bias + ReLU + 3x3 max-pool with arg-max ----------------
     const int q = warp & 3;                 // TMEM lane quarter of this warp
     const int row = q * 32 + lane;          // accumulator row = tile pixel
-    const int et = threadIdx.x - 160;       // 0..127 inside the epilogue group
+    const int et = threadIdx.x - 288;       // 0..127 inside the epilogue group
     int i = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++i) {
       const int s = i & 1;
@@ -227,14 +278,15 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_fwd_kernel(const Conv1Args 
 //   A = col tile, MN-major: rows = pixels, two 64-wide chunks of k (block0, block1)
 //   B = g tile,   MN-major: rows = pixels, 64 channels
 // smem: A[2] x (block0 + block1) | G[2] x 16 KB
-constexpr int kBwdSmem = 2 * 2 * kBlockBytes + 2 * kBlockBytes + 1024;
+constexpr int kBwdSmem = 2 * 2 * kBlockBytes + 2 * kBlockBytes + 2 * kImgStageBytes + 1024;
 
 __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* abuf = smem;
   uint8_t* gbuf = smem + 2 * 2 * kBlockBytes;
-  __shared__ __align__(8) uint64_t ab_full[2], ab_empty[2], done_bar;
+  uint8_t* imgbuf = gbuf + 2 * kBlockBytes;
+  __shared__ __align__(8) uint64_t ab_full[2], ab_empty[2], done_bar, img_full[2][2];
   __shared__ uint32_t tmem_base_smem;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -245,6 +297,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args 
     for (int s = 0; s < 2; ++s) {
       mbar_init(&ab_full[s], 256);
       mbar_init(&ab_empty[s], 1);
+      mbar_init(&img_full[s][0], 1);
+      mbar_init(&img_full[s][1], 1);
     }
     mbar_init(&done_bar, 1);
     fence_mbar_init();
@@ -284,54 +338,81 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args 
       umma_commit(&done_bar);
     }
     __syncwarp();
-  } else if (warp <= 4) {
-    const int r = threadIdx.x - 32;
-    int i = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++i) {
-      const int s = i & 1;
-      const uint32_t ph = (i >> 1) & 1;
-      mbar_wait(&ab_empty[s], ph ^ 1);
-      uint8_t* b0 = abuf + s * 2 * kBlockBytes;
-      build_patch_row(a.x, total_win, t, r, b0, b0 + kBlockBytes);
+  } else if (warp <= 8) {
+    const int grp = (warp - 1) >> 2;
+    const int r = (threadIdx.x - 32) & 127;
+    uint8_t* b0p = abuf + grp * 2 * kBlockBytes;
+    uint8_t* img = imgbuf + grp * kImgStageBytes;   // two buffers of 2 images
+    const long long t_first = blockIdx.x + static_cast<long long>(grp) * gridDim.x, t_step = 2ll * gridDim.x;
+    if (r == 0 && t_first < num_tiles)
+      stage_images_async(a.x, a.B, static_cast<int>(t_first * kWinPerTile / kWinPerImg), img, &img_full[grp][0]);
+    int n = 0;
+    for (long long t = t_first; t < num_tiles; t += t_step, ++n) {
+      const int buf = n & 1;
+      const int b0 = static_cast<int>(t * kWinPerTile / kWinPerImg);
+      if (r == 0 && t + t_step < num_tiles)  // prefetch the next tile's images into the other buffer
+        stage_images_async(a.x, a.B, static_cast<int>((t + t_step) * kWinPerTile / kWinPerImg), img + (buf ^ 1) * 2 * kImgBytes,
+                           &img_full[grp][buf ^ 1]);
+      mbar_wait(&img_full[grp][buf], (n >> 1) & 1);
+      mbar_wait(&ab_empty[grp], (n & 1) ^ 1);
+      build_patch_row(reinterpret_cast<const uint32_t*>(img + buf * 2 * kImgBytes), total_win, static_cast<int>(t), b0, r, b0p,
+                      b0p + kBlockBytes);
       fence_proxy_async_smem();
-      mbar_arrive(&ab_full[s]);
+      mbar_arrive(&ab_full[grp]);
+      asm volatile("bar.sync %0, 128;" ::"r"(2 + grp) : "memory");  // everyone is done with img[buf] before it is refilled
     }
   } else {
-    // gradient rows: the pooled gradient routed to the arg-max pixel of each window (ReLU folded in)
-    const int r = threadIdx.x - 160;
+    // gradient rows: the pooled gradient routed to the arg-max pixel of each window (ReLU folded in).
+    // Thread (window wl, chunk j) loads that window's dp1/p1/idx1 chunk once and emits the 9 pixel
+    // rows of the window; the next tile's vectors are fetched before the current ones are used.
+    const int gt = threadIdx.x - 288;
+    const int wl = gt >> 3, j = gt & 7;          // wl 0..15 (14 real windows), j = 16-byte chunk
+    auto fetch = [&](long long t, uint4& dv, uint4& pv, uint2& iv, bool& ok) {
+      const long long win = t * kWinPerTile + wl;
+      ok = (wl < kWinPerTile) && (t < num_tiles) && (win < total_win);
+      if (ok) {
+        dv = __ldg(reinterpret_cast<const uint4*>(a.dp1 + win * kO + j * 8));
+        pv = __ldg(reinterpret_cast<const uint4*>(a.p1 + win * kO + j * 8));
+        iv = __ldg(reinterpret_cast<const uint2*>(a.idx1 + win * kO + j * 8));
+      }
+    };
+    uint4 dv = make_uint4(0, 0, 0, 0), pv = dv, ndv = dv, npv = dv;
+    uint2 iv = make_uint2(0, 0), niv = iv;
+    bool ok = false, nok = false;
+    fetch(blockIdx.x, dv, pv, iv, ok);
     int i = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++i) {
+    for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x, ++i) {
       const int s = i & 1;
       const uint32_t ph = (i >> 1) & 1;
+      fetch(t + gridDim.x, ndv, npv, niv, nok);
       mbar_wait(&ab_empty[s], ph ^ 1);
       uint8_t* g = gbuf + s * kBlockBytes;
-      const long long win = static_cast<long long>(t) * kWinPerTile + r / 9;
-      const bool valid = (r < kWinPerTile * 9) && (win < total_win);
-      const unsigned pos = static_cast<unsigned>(r % 9);
+      if (wl < kWinPerTile) {
+        const uint32_t dw[4] = {dv.x, dv.y, dv.z, dv.w};
+        const uint32_t pw[4] = {pv.x, pv.y, pv.z, pv.w};
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        uint4 o = make_uint4(0, 0, 0, 0);
-        if (valid) {
-          const uint4 dv = *reinterpret_cast<const uint4*>(a.dp1 + win * kO + j * 8);
-          const uint4 pv = *reinterpret_cast<const uint4*>(a.p1 + win * kO + j * 8);
-          const uint2 iv = *reinterpret_cast<const uint2*>(a.idx1 + win * kO + j * 8);
-          const uint32_t dw[4] = {dv.x, dv.y, dv.z, dv.w};
-          const uint32_t pw[4] = {pv.x, pv.y, pv.z, pv.w};
-          uint32_t ow[4];
+        for (int pos = 0; pos < 9; ++pos) {
+          uint32_t ow[4] = {0u, 0u, 0u, 0u};
+          if (ok) {
 #pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            const uint32_t ib = (e < 2 ? iv.x : iv.y) >> (16 * (e & 1));
-            const float2 d2 = unpack_bf16x2(dw[e]);
-            const float2 p2 = unpack_bf16x2(pw[e]);
-            ow[e] = pack_bf16x2(((ib & 0xffu) == pos && p2.x > 0.f) ? d2.x : 0.f,
-                                (((ib >> 8) & 0xffu) == pos && p2.y > 0.f) ? d2.y : 0.f);
+            for (int e = 0; e < 4; ++e) {
+              const uint32_t ib = (e < 2 ? iv.x : iv.y) >> (16 * (e & 1));
+              const float2 d2 = unpack_bf16x2(dw[e]);
+              const float2 p2 = unpack_bf16x2(pw[e]);
+              ow[e] = pack_bf16x2(((ib & 0xffu) == static_cast<uint32_t>(pos) && p2.x > 0.f) ? d2.x : 0.f,
+                                  (((ib >> 8) & 0xffu) == static_cast<uint32_t>(pos) && p2.y > 0.f) ? d2.y : 0.f);
+            }
           }
-          o = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+          *reinterpret_cast<uint4*>(g + sw128(wl * 9 + pos, j)) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
         }
-        *reinterpret_cast<uint4*>(g + sw128(r, j)) = o;
+      } else if (wl == kWinPerTile) {
+        // padding rows 126 and 127
+        *reinterpret_cast<uint4*>(g + sw128(126, j)) = make_uint4(0, 0, 0, 0);
+        *reinterpret_cast<uint4*>(g + sw128(127, j)) = make_uint4(0, 0, 0, 0);
       }
       fence_proxy_async_smem();
       mbar_arrive(&ab_full[s]);
+      dv = ndv; pv = npv; iv = niv; ok = nok;
     }
     // final epilogue: accumulator rows = patch index k, columns = output channel
     if (has_work) {

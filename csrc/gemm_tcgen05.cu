@@ -127,7 +127,7 @@ __device__ __forceinline__ void store_row32(void* base, int ld, int c_fp32, int 
   }
 }
 
-template <bool A_MN, bool B_MN, int BN>
+template <bool A_MN, bool B_MN, int BN, bool AUX>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
                          const __grid_constant__ CUtensorMap tma_b,
@@ -296,13 +296,13 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           __syncwarp();
           uint8_t* dst = stg + buf * 4096 + lane * 128;
           const int row = row0 + lane;
-          const bool aux_ok = p.aux != nullptr && row < p.M;
+          const bool aux_ok = AUX && row < p.M;
           const __nv_bfloat16* aux_row = p.aux + static_cast<size_t>(row < p.M ? row : 0) * p.ld_aux + col0;
 #pragma unroll
           for (int j = 0; j < 8; ++j) {  // 8 x 16-byte chunks = 64 bf16 columns of this row
             float v[8];
             float ay[8];
-            if (aux_ok) {
+            if (AUX && aux_ok) {
               if (col0 + j * 8 + 8 <= p.N && ((reinterpret_cast<uintptr_t>(aux_row + j * 8) & 15) == 0)) {
                 const uint4 q = *reinterpret_cast<const uint4*>(aux_row + j * 8);
                 float2 f;
@@ -321,7 +321,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
               float x = __uint_as_float(col < 32 ? r0[col] : r1[col - 32]) * p.alpha;
               if (p.bias != nullptr) x += sb[col];
               x = apply_act(x, p.act);
-              if (aux_ok) x *= (1.0f - ay[e] * ay[e]);
+              if (AUX && aux_ok) x *= (1.0f - ay[e] * ay[e]);
               v[e] = x;
             }
             uint4 u;
@@ -446,7 +446,7 @@ int make_tmap(CUtensorMap* out, const void* ptr, long long rows, long long cols,
   return 0;
 }
 
-template <bool A_MN, bool B_MN, int BN>
+template <bool A_MN, bool B_MN, int BN, bool AUX = false>
 int launch(const tadnn_gemm_args* a, const DevArgs& d, cudaStream_t stream) {
   using C = Cfg<BN>;
   CUtensorMap ta, tb, tc;
@@ -475,7 +475,7 @@ int launch(const tadnn_gemm_args* a, const DevArgs& d, cudaStream_t stream) {
   if (rc) return rc;
   rc = B_MN ? make_tmap(&tb, a->B, a->K, a->N, a->ldb, BK) : make_tmap(&tb, a->B, a->N, a->K, a->ldb, BN);
   if (rc) return rc;
-  auto kern = gemm_bf16_tcgen05_kernel<A_MN, B_MN, BN>;
+  auto kern = gemm_bf16_tcgen05_kernel<A_MN, B_MN, BN, AUX>;
   static bool attr_set = false;  // per instantiation
   if (!attr_set) {
     TADNN_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
@@ -493,7 +493,7 @@ int launch(const tadnn_gemm_args* a, const DevArgs& d, cudaStream_t stream) {
 template <int BN>
 int dispatch_major(const tadnn_gemm_args* a, const DevArgs& d, cudaStream_t s) {
   if (!a->a_mn_major && !a->b_mn_major) return launch<false, false, BN>(a, d, s);
-  if (!a->a_mn_major && a->b_mn_major) return launch<false, true, BN>(a, d, s);
+  if (!a->a_mn_major && a->b_mn_major) return d.aux != nullptr ? launch<false, true, BN, true>(a, d, s) : launch<false, true, BN>(a, d, s);
   if (a->a_mn_major && a->b_mn_major) return launch<true, true, BN>(a, d, s);
   return launch<true, false, BN>(a, d, s);
 }
@@ -549,7 +549,7 @@ extern "C" int tadnn_gemm_bf16(const tadnn_gemm_args* a, tadnn_stream_t stream_)
       ok = (a->push_ldc % 8 == 0) && ((reinterpret_cast<uintptr_t>(a->push[i]) & 15) == 0) && (a->push_col_offset % 8 == 0);
     d.tma_store = ok ? 1 : 0;
   }
-  TADNN_REQUIRE(d.aux == nullptr || d.tma_store, "tadnn_gemm_bf16: aux_tanh_out needs the bf16 TMA-store epilogue");
+  TADNN_REQUIRE(d.aux == nullptr || (d.tma_store && !a->a_mn_major && a->b_mn_major), "tadnn_gemm_bf16: aux_tanh_out needs the bf16 TMA-store epilogue and the dgrad operand layout (a K-major, b MN-major)");
 
   int bn = a->tile_n;
   if (bn == 0) bn = a->N <= 64 ? 64 : (a->N <= 128 ? 128 : 256);

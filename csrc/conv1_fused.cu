@@ -31,7 +31,8 @@ constexpr int kWinPerImg = kPH * kPW;        // 81
 constexpr int kWinPerTile = 14;              // 14 windows x 9 pixels = 126 rows of a 128-row tile
 constexpr int kRows = 128;
 constexpr int kBlockBytes = kRows * 128;     // one [128 rows x 64 bf16] SWIZZLE_128B block: 16 KB
-constexpr int kThreads = 416;                // warp 0: MMA/TMEM, warps 1-8: two im2col producer groups (one per smem stage), warps 9-12: epilogue / gradient rows
+constexpr int kThreads = 416;                // backward: warp 0 MMA/TMEM, warps 1-8 two im2col producer groups (one per smem stage), warps 9-12 gradient rows + final epilogue
+constexpr int kFwdThreads = 544;             // forward: same, plus warps 9-12 / 13-16 = two epilogue groups (one per TMEM stage)
 
 struct Conv1Args {
   const __nv_bfloat16* x;     // [B, 3, 32, 32]
@@ -120,16 +121,16 @@ __device__ __forceinline__ void build_patch_row(const uint32_t* __restrict__ img
 // ======================================= forward =======================================
 // smem: W block0 | W block1 (64 rows each, 8 KB) | A[2] x (block0 16 KB + block1 16 KB) | E 16 KB
 constexpr int kImgStageBytes = 2 * 2 * kC * kH * kW * 2;  // per producer group: double-buffered pair of staged images
-constexpr int kFwdSmem = 2 * 8192 + 2 * 2 * kBlockBytes + kRows * 128 + 2 * kImgStageBytes + 1024;
+constexpr int kFwdSmem = 2 * 8192 + 2 * 2 * kBlockBytes + 2 * kRows * 128 + 2 * kImgStageBytes + 1024;
 
-__global__ void __launch_bounds__(kThreads, 1) conv1_fwd_kernel(const Conv1Args a) {
+__global__ void __launch_bounds__(kFwdThreads, 1) conv1_fwd_kernel(const Conv1Args a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* w0 = smem;
   uint8_t* w1 = smem + 8192;
   uint8_t* abuf = smem + 16384;                       // stage s: abuf + s*32768 (+0: block0, +16384: block1)
   uint8_t* ebuf = abuf + 2 * 2 * kBlockBytes;         // [128 rows][64 ch] bf16, plain row-major
-  uint8_t* imgbuf = ebuf + kRows * 128;                // [2 groups][2 images] staged input
+  uint8_t* imgbuf = ebuf + 2 * kRows * 128;            // staged input images
   __shared__ __align__(8) uint64_t a_full[2], a_empty[2], t_full[2], t_empty[2], img_full[2][2];
   __shared__ uint32_t tmem_base_smem;
   __shared__ float s_bias[kO];
@@ -213,23 +214,25 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_fwd_kernel(const Conv1Args 
     }
   } else {
     // ---------------- epilogue: bias + ReLU + 3x3 max-pool with arg-max ----------------
+    // two groups of 4 warps; group g drains TMEM stage g (tiles i with i % 2 == g) through its own
+    // staging buffer, so one group pools while the other reads the next accumulator.
+    const int grp = (warp - 9) >> 2;
     const int q = warp & 3;                 // TMEM lane quarter of this warp
     const int row = q * 32 + lane;          // accumulator row = tile pixel
-    const int et = threadIdx.x - 288;       // 0..127 inside the epilogue group
-    int i = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x, ++i) {
-      const int s = i & 1;
-      const uint32_t ph = (i >> 1) & 1;
-      mbar_wait(&t_full[s], ph);
+    const int et = (threadIdx.x - 288) & 127;
+    uint8_t* eb = ebuf + grp * kRows * 128;
+    int n = 0;
+    for (long long t = blockIdx.x + static_cast<long long>(grp) * gridDim.x; t < num_tiles; t += 2ll * gridDim.x, ++n) {
+      mbar_wait(&t_full[grp], n & 1);
       tc_fence_after_sync();
       uint32_t r0[32], r1[32];
-      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(s * kO);
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(grp * kO);
       tmem_ld_32x32b_x32(taddr, r0);
       tmem_ld_32x32b_x32(taddr + 32, r1);
       tmem_ld_wait();
       tc_fence_before_sync();
-      mbar_arrive(&t_empty[s]);
-      uint4* erow = reinterpret_cast<uint4*>(ebuf + row * 128);
+      mbar_arrive(&t_empty[grp]);
+      uint4* erow = reinterpret_cast<uint4*>(eb + row * 128);
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
         float v[8];
@@ -241,28 +244,40 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_fwd_kernel(const Conv1Args 
         // rotate the chunk position by the row so that the 32 rows of a warp spread over all banks
         erow[(j + row) & 7] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      // 14 windows x 32 channel pairs
-      for (int o = et; o < kWinPerTile * 32; o += 128) {
-        const int wl = o >> 5, cp = o & 31;
-        const long long win = static_cast<long long>(t) * kWinPerTile + wl;
+      asm volatile("bar.sync %0, 128;" ::"r"(4 + grp) : "memory");
+      // 14 windows x 16 channel quads, packed bf16x2 max + first-arg-max
+      for (int o = et; o < kWinPerTile * 16; o += 128) {
+        const int wl = o >> 4, q4 = o & 15;
+        const long long win = t * kWinPerTile + wl;
         if (win < total_win) {
-          float b0 = -INFINITY, b1 = -INFINITY;
-          int i0 = 0, i1 = 0;
+          uint2 val[9];
 #pragma unroll
           for (int pos = 0; pos < 9; ++pos) {
             const int rr = wl * 9 + pos;
-            const int chunk = ((cp >> 2) + rr) & 7;
-            const uint32_t u = *reinterpret_cast<const uint32_t*>(ebuf + rr * 128 + chunk * 16 + (cp & 3) * 4);
-            const float2 f = unpack_bf16x2(u);
-            if (f.x > b0) { b0 = f.x; i0 = pos; }
-            if (f.y > b1) { b1 = f.y; i1 = pos; }
+            val[pos] = *reinterpret_cast<const uint2*>(eb + rr * 128 + ((((q4 >> 1) + rr) & 7) << 4) + ((q4 & 1) << 3));
           }
-          *reinterpret_cast<uint32_t*>(a.p1 + win * kO + cp * 2) = pack_bf16x2(b0, b1);
-          *reinterpret_cast<unsigned short*>(a.idx1 + win * kO + cp * 2) = static_cast<unsigned short>(i0 | (i1 << 8));
+          uint32_t mx[2], ix[2];
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            __nv_bfloat162 m = *reinterpret_cast<const __nv_bfloat162*>(h ? &val[0].y : &val[0].x);
+#pragma unroll
+            for (int pos = 1; pos < 9; ++pos)
+              m = __hmax2(m, *reinterpret_cast<const __nv_bfloat162*>(h ? &val[pos].y : &val[pos].x));
+            uint32_t idx = 0;
+#pragma unroll
+            for (int pos = 8; pos >= 0; --pos) {  // descending: the smallest matching position wins
+              const uint32_t eq = __heq2_mask(*reinterpret_cast<const __nv_bfloat162*>(h ? &val[pos].y : &val[pos].x), m);
+              idx = (idx & ~eq) | ((static_cast<uint32_t>(pos) * 0x00010001u) & eq);
+            }
+            mx[h] = *reinterpret_cast<const uint32_t*>(&m);
+            ix[h] = idx;  // two 16-bit positions
+          }
+          *reinterpret_cast<uint2*>(a.p1 + win * kO + q4 * 4) = make_uint2(mx[0], mx[1]);
+          const uint32_t packed = (ix[0] & 0xffu) | ((ix[0] >> 8) & 0xff00u) | ((ix[1] & 0xffu) << 16) | ((ix[1] & 0xff0000u) << 8);
+          *reinterpret_cast<uint32_t*>(a.idx1 + win * kO + q4 * 4) = packed;
         }
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      asm volatile("bar.sync %0, 128;" ::"r"(4 + grp) : "memory");
     }
   }
   tc_fence_before_sync();
@@ -388,22 +403,22 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args 
       mbar_wait(&ab_empty[s], ph ^ 1);
       uint8_t* g = gbuf + s * kBlockBytes;
       if (wl < kWinPerTile) {
-        const uint32_t dw[4] = {dv.x, dv.y, dv.z, dv.w};
+        // integer domain: keep dp1 where the byte arg-max equals this pixel position and p1 != 0
+        // (p1 is a ReLU output, so "> 0" is "bits != 0")
+        uint32_t dw[4] = {dv.x, dv.y, dv.z, dv.w};
         const uint32_t pw[4] = {pv.x, pv.y, pv.z, pv.w};
 #pragma unroll
-        for (int pos = 0; pos < 9; ++pos) {
-          uint32_t ow[4] = {0u, 0u, 0u, 0u};
-          if (ok) {
+        for (int e = 0; e < 4; ++e) {
+          const uint32_t nz = ((pw[e] & 0xffffu) ? 0xffffu : 0u) | ((pw[e] & 0xffff0000u) ? 0xffff0000u : 0u);
+          dw[e] = ok ? (dw[e] & nz) : 0u;
+        }
 #pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              const uint32_t ib = (e < 2 ? iv.x : iv.y) >> (16 * (e & 1));
-              const float2 d2 = unpack_bf16x2(dw[e]);
-              const float2 p2 = unpack_bf16x2(pw[e]);
-              ow[e] = pack_bf16x2(((ib & 0xffu) == static_cast<uint32_t>(pos) && p2.x > 0.f) ? d2.x : 0.f,
-                                  (((ib >> 8) & 0xffu) == static_cast<uint32_t>(pos) && p2.y > 0.f) ? d2.y : 0.f);
-            }
-          }
-          *reinterpret_cast<uint4*>(g + sw128(wl * 9 + pos, j)) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+        for (int pos = 0; pos < 9; ++pos) {
+          const uint32_t m0 = __vcmpeq4(iv.x, static_cast<uint32_t>(pos) * 0x01010101u);  // channels 0..3
+          const uint32_t m1 = __vcmpeq4(iv.y, static_cast<uint32_t>(pos) * 0x01010101u);  // channels 4..7
+          *reinterpret_cast<uint4*>(g + sw128(wl * 9 + pos, j)) =
+              make_uint4(dw[0] & __byte_perm(m0, 0, 0x1100), dw[1] & __byte_perm(m0, 0, 0x3322),
+                         dw[2] & __byte_perm(m1, 0, 0x1100), dw[3] & __byte_perm(m1, 0, 0x3322));
         }
       } else if (wl == kWinPerTile) {
         // padding rows 126 and 127
@@ -478,7 +493,7 @@ extern "C" int tadnn_conv1_pool_forward(const void* x, const void* w_packed, con
   a.p1 = static_cast<__nv_bfloat16*>(p1); a.idx1 = static_cast<unsigned char*>(idx1); a.B = B;
   const long long tiles = (static_cast<long long>(B) * kWinPerImg + kWinPerTile - 1) / kWinPerTile;
   const int grid = tiles < sm_count() ? static_cast<int>(tiles) : sm_count();
-  conv1_fwd_kernel<<<grid, kThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
+  conv1_fwd_kernel<<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
   TADNN_LAUNCH_CHECK("conv1_pool_fwd_tcgen05");
   return 0;
 }

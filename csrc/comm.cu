@@ -7,38 +7,7 @@
 // synchronizeModel (datamodule.lua:211-224: per-tensor allreduceTensor + div), from
 // parallelize (datamodule.lua:33 synchronizeParameters, :50 barrier) and from the MP layers
 // (nodemodule.lua:52,66,103,117 allreduceTensor; :166,266 allgatherTensor).
-#include "common.cuh"
-
-#include <vector>
-
-namespace tadnn {
-
-constexpr int kMaxRanks = TADNN_COMM_MAX_RANKS;
-constexpr int kChannels = TADNN_COMM_CHANNELS;
-constexpr int kMaxBlocks = TADNN_COMM_MAX_BLOCKS;
-constexpr size_t kPadBytes = static_cast<size_t>(kChannels) * kMaxBlocks * kMaxRanks * sizeof(uint32_t);
-constexpr unsigned long long kSpinTimeoutNs = 20ull * 1000ull * 1000ull * 1000ull;  // 20 s
-
-struct CommDev {
-  uint8_t* heap[kMaxRanks];
-  uint32_t* pad[kMaxRanks];
-  uint8_t* mc_heap;  // multicast mapping of the heaps (NVLS) or nullptr
-  int rank;          // -1: single-launch emulation, rank = blockIdx.y
-  int world;
-};
-
-}  // namespace tadnn
-
-struct tadnn_comm {
-  tadnn::CommDev dev;
-  int rank = 0, world = 1;
-  int device = 0;
-  unsigned long long heap_bytes = 0;
-  void* base = nullptr;  // own allocation (heap + pad); nullptr if attached
-  bool owns = false;
-  bool local_set = false;  // created by tadnn_comm_create_local
-  std::vector<void*> opened;  // cudaIpcOpenMemHandle results to close
-};
+#include "comm_internal.cuh"
 
 namespace tadnn {
 namespace {
@@ -478,7 +447,7 @@ extern "C" int tadnn_comm_create_local(int world, unsigned long long heap_bytes,
 }
 
 extern "C" int tadnn_comm_ipc_handle(tadnn_comm* c, void* host_out64) {
-  TADNN_REQUIRE(c && c->owns, "comm_ipc_handle: context does not own its heap");
+  TADNN_REQUIRE(c && c->owns && !c->vmm, "comm_ipc_handle: context does not own a cudaMalloc heap");
   static_assert(sizeof(cudaIpcMemHandle_t) == TADNN_IPC_HANDLE_BYTES, "IPC handle size");
   cudaIpcMemHandle_t h;
   TADNN_CHECK_CUDA(cudaIpcGetMemHandle(&h, c->base));
@@ -530,8 +499,12 @@ extern "C" int tadnn_comm_info(tadnn_comm* c, int* rank, int* world, unsigned lo
 extern "C" int tadnn_comm_destroy(tadnn_comm* c) {
   if (c == nullptr) return 0;
   cudaDeviceSynchronize();
-  for (void* p : c->opened) cudaIpcCloseMemHandle(p);
-  if (c->owns && c->base) cudaFree(c->base);
+  if (c->vmm) {
+    tadnn_comm_vmm_release(c);
+  } else {
+    for (void* p : c->opened) cudaIpcCloseMemHandle(p);
+    if (c->owns && c->base) cudaFree(c->base);
+  }
   delete c;
   return 0;
 }

@@ -110,6 +110,21 @@ int tadnn_comm_heap(tadnn_comm* c, int peer, void** out_ptr);
 int tadnn_comm_info(tadnn_comm* c, int* rank, int* world, unsigned long long* heap_bytes, int* has_multicast);
 int tadnn_comm_destroy(tadnn_comm* c);
 
+/* VMM + multicast backend (csrc/comm_vmm.cu): the heap is a cuMemCreate allocation shared as a
+ * POSIX file descriptor; where the driver exposes NVLS a multicast object over all heaps is mapped
+ * and the multimem all-reduce (algo 3) becomes available.  Sequence per rank: create_vmm ->
+ * export_fd (send the fd to every peer) -> import_peer_fd for every peer; optional multicast:
+ * rank 0 mc_create (send fd) / others mc_import -> mc_add_device -> host barrier -> mc_bind. */
+int tadnn_multicast_supported(int* out);
+int tadnn_comm_create_vmm(int rank, int world, unsigned long long heap_bytes, tadnn_comm** out);
+int tadnn_comm_export_fd(tadnn_comm* c, int* fd);
+int tadnn_comm_import_peer_fd(tadnn_comm* c, int peer, int fd);
+int tadnn_comm_mc_create(tadnn_comm* c, int* fd);
+int tadnn_comm_mc_import(tadnn_comm* c, int fd);
+int tadnn_comm_mc_add_device(tadnn_comm* c);
+int tadnn_comm_mc_bind(tadnn_comm* c);
+int tadnn_comm_vmm_release(tadnn_comm* c);
+
 /* K5 device barrier across all ranks (signal-pad flags, release/acquire at system scope).
  * Replaces mpi.barrier() (datamodule.lua:50,283). */
 int tadnn_barrier(tadnn_comm* c, int channel, tadnn_stream_t stream);

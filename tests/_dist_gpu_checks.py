@@ -46,7 +46,7 @@ def main():
     big = ctx.empty((1 << 24,), torch.float32)  # 64 MB region reused for all sizes
     for dtype in (torch.float32, torch.bfloat16):
         for n in (1, 3, 10, 64, 1000, 4099, 65536, 114838 * 2, 1 << 20, (1 << 22) + 5):
-            for algo in (1, 2):
+            for algo in ((1, 2, 3) if ctx.has_multicast else (1, 2)):
                 if algo == 1 and n > (1 << 20):
                     continue
                 view = big.view(dtype)[:n]
@@ -166,7 +166,7 @@ def main():
     dist.all_gather_object(allf, fails)
     if rank == 0:
         flat = [f"r{r}: {m}" for r, fs in enumerate(allf) for m in fs]
-        print(json.dumps({"world": P, "checks": checks, "failures": flat}))
+        print(json.dumps({"world": P, "checks": checks, "failures": flat, "backend": ctx.backend, "multicast": ctx.has_multicast}))
     h.stop()
     sys.exit(1 if any(allf) else 0)
 

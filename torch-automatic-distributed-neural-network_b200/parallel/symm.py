@@ -70,16 +70,34 @@ class SymmContext:
         staging_mb = int(os.environ.get("TADNN_SYMM_STAGING_MB", staging_mb or 128))
         self.heap_bytes = heap_mb << 20
         self.device = torch.device("cuda", torch.cuda.current_device())
-        _native.check(lib.tadnn_comm_create(C.c_int(self.rank), C.c_int(self.world),
-                                            C.c_ulonglong(self.heap_bytes), C.byref(self.handle)),
-                      "tadnn_comm_create")
-        if self.world > 1:
-            mine = C.create_string_buffer(64)
-            _native.check(lib.tadnn_comm_ipc_handle(self.handle, mine), "tadnn_comm_ipc_handle")
-            allh: list = [None] * self.world
-            dist.all_gather_object(allh, bytes(mine.raw))
-            blob = b"".join(allh)
-            _native.check(lib.tadnn_comm_open_peers(self.handle, C.c_char_p(blob)), "tadnn_comm_open_peers")
+        backend = os.environ.get("TADNN_SYMM_BACKEND", "auto")
+        self.backend = "ipc"
+        if backend in ("auto", "vmm") and self.world > 1:
+            ok, why = self._try_vmm(lib)
+            flags: list = [None] * self.world
+            dist.all_gather_object(flags, (ok, why))
+            if all(f[0] for f in flags):
+                self.backend = "vmm"
+            else:
+                if self.handle:
+                    lib.tadnn_comm_destroy(self.handle)
+                    self.handle = C.c_void_p()
+                self.has_multicast = False
+                if backend == "vmm":
+                    raise _native.NativeError(f"TADNN_SYMM_BACKEND=vmm failed: {[f[1] for f in flags if not f[0]]}")
+                if self.rank == 0:
+                    print(f"[tadnn] VMM/multicast heap unavailable ({[f[1] for f in flags if not f[0]][:1]}); using CUDA-IPC", flush=True)
+        if self.backend == "ipc":
+            _native.check(lib.tadnn_comm_create(C.c_int(self.rank), C.c_int(self.world),
+                                                C.c_ulonglong(self.heap_bytes), C.byref(self.handle)),
+                          "tadnn_comm_create")
+            if self.world > 1:
+                mine = C.create_string_buffer(64)
+                _native.check(lib.tadnn_comm_ipc_handle(self.handle, mine), "tadnn_comm_ipc_handle")
+                allh: list = [None] * self.world
+                dist.all_gather_object(allh, bytes(mine.raw))
+                blob = b"".join(allh)
+                _native.check(lib.tadnn_comm_open_peers(self.handle, C.c_char_p(blob)), "tadnn_comm_open_peers")
         self.heap_ptrs = []
         for r in range(self.world):
             p = C.c_void_p()
@@ -94,6 +112,90 @@ class SymmContext:
             torch.cuda.synchronize()
             dist.barrier()  # pads are zeroed and mapped everywhere before the first kernel
         return self
+
+    # ------------------------------------------------------------------ VMM + multicast bring-up
+    def _fd_exchange(self, token: str, send: dict) -> dict:
+        """Pass file descriptors between the rank processes over AF_UNIX datagram sockets
+        (SCM_RIGHTS).  ``send`` maps destination rank -> fd; returns {source rank: fd} for every
+        rank that sent us one (every rank must call this with the same ``token``)."""
+        import socket
+        import struct
+        import torch.distributed as dist
+        addr = lambda r: f"\0tadnn-{token}-{r}"  # abstract namespace: no files to clean up
+        srv = socket.socket(socket.AF_UNIX, socket.SOCK_DGRAM)
+        srv.bind(addr(self.rank))
+        srv.settimeout(60.0)
+        expect: list = [None] * self.world
+        dist.all_gather_object(expect, sorted(send.keys()))
+        n_in = sum(1 for src, dsts in enumerate(expect) if self.rank in dsts and src != self.rank)
+        out = socket.socket(socket.AF_UNIX, socket.SOCK_DGRAM)
+        import array
+        for dst, fd in send.items():  # (socket.send_fds drops its address argument before 3.13)
+            out.sendmsg([struct.pack("i", self.rank)],
+                        [(socket.SOL_SOCKET, socket.SCM_RIGHTS, array.array("i", [fd]))], 0, addr(dst))
+        got = {}
+        for _ in range(n_in):
+            msg, anc, _flags, _a = srv.recvmsg(16, socket.CMSG_LEN(4))
+            fds = array.array("i")
+            for level, typ, data in anc:
+                if level == socket.SOL_SOCKET and typ == socket.SCM_RIGHTS:
+                    fds.frombytes(data[:4])
+            got[struct.unpack("i", msg[:4])[0]] = fds[0]
+        out.close()
+        srv.close()
+        dist.barrier()
+        return got
+
+    def _try_vmm(self, lib):
+        import torch.distributed as dist
+        try:
+            tok = [None]
+            if self.rank == 0:
+                tok[0] = f"{os.getpid()}-{int.from_bytes(os.urandom(4), 'little')}"
+            dist.broadcast_object_list(tok, src=0)
+            rc = lib.tadnn_comm_create_vmm(C.c_int(self.rank), C.c_int(self.world), C.c_ulonglong(self.heap_bytes),
+                                           C.byref(self.handle))
+            if rc != 0:
+                return False, lib.tadnn_last_error().decode()
+            fd = C.c_int(-1)
+            if lib.tadnn_comm_export_fd(self.handle, C.byref(fd)) != 0:
+                return False, lib.tadnn_last_error().decode()
+            got = self._fd_exchange(tok[0] + "-heap", {q: fd.value for q in range(self.world) if q != self.rank})
+            os.close(fd.value)
+            for q, pfd in got.items():
+                if lib.tadnn_comm_import_peer_fd(self.handle, C.c_int(q), C.c_int(pfd)) != 0:
+                    return False, lib.tadnn_last_error().decode()
+            # multicast (optional): failure here keeps the VMM heap, just without NVLS
+            mc = C.c_int(0)
+            lib.tadnn_multicast_supported(C.byref(mc))
+            want = bool(mc.value) and os.environ.get("TADNN_NVLS", "1") not in ("0", "false")
+            votes: list = [None] * self.world
+            dist.all_gather_object(votes, want)
+            if all(votes):
+                mfd = C.c_int(-1)
+                ok = True
+                if self.rank == 0:
+                    ok = lib.tadnn_comm_mc_create(self.handle, C.byref(mfd)) == 0
+                oks: list = [None] * self.world
+                dist.all_gather_object(oks, ok)
+                if all(oks):
+                    got = self._fd_exchange(tok[0] + "-mc", {q: mfd.value for q in range(1, self.world)} if self.rank == 0 else {})
+                    if self.rank == 0:
+                        os.close(mfd.value)
+                    else:
+                        ok = lib.tadnn_comm_mc_import(self.handle, C.c_int(got[0])) == 0
+                    ok = ok and lib.tadnn_comm_mc_add_device(self.handle) == 0
+                    dist.all_gather_object(oks, ok)
+                    if all(oks):
+                        dist.barrier()
+                        ok = lib.tadnn_comm_mc_bind(self.handle) == 0
+                        dist.all_gather_object(oks, ok)
+                        self.has_multicast = all(oks)
+                        if not self.has_multicast and self.rank == 0:
+                            print(f"[tadnn] multicast bind failed: {lib.tadnn_last_error().decode()}", flush=True)
+            return True, ""
+        except Exception as e:  # noqa: BLE001 - any failure means "fall back to IPC"
+            return False, repr(e)
 
     def close(self):
         if self.handle:

@@ -90,15 +90,26 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
 
 def dump_sass() -> None:
+    """cuobjdump -sass of every object under profiles/sass/.  The GEMM object holds 24 template
+    instantiations (24 MB of listing); only two representative ones are kept in the tree."""
     out_dir = os.path.join(ROOT, "profiles", "sass")
     os.makedirs(out_dir, exist_ok=True)
+    keep_gemm = ("ILb0ELb0ELi256ELb0E", "ILb0ELb1ELi256ELb1E")  # forward (TN) and dgrad with fused tanh'
     for f in sorted(os.listdir(OBJ)):
         if not f.endswith(".o"):
             continue
         p = subprocess.run(["cuobjdump", "-sass", os.path.join(OBJ, f)], capture_output=True, text=True)
-        if p.returncode == 0 and p.stdout.strip():
-            with open(os.path.join(out_dir, f[:-2] + ".sass"), "w") as fh:
-                fh.write(p.stdout)
+        if p.returncode != 0 or not p.stdout.strip():
+            continue
+        text = p.stdout
+        if f.startswith("gemm_tcgen05"):
+            parts = text.split("\t\tFunction : ")
+            head, funcs = parts[0], parts[1:]
+            kept = [fn for fn in funcs if any(k in fn.split("\n", 1)[0] for k in keep_gemm)]
+            text = head + "".join("\t\tFunction : " + fn for fn in kept)
+            text += f"\n// ({len(funcs) - len(kept)} further instantiations of gemm_bf16_tcgen05_kernel omitted)\n"
+        with open(os.path.join(out_dir, f[:-2] + ".sass"), "w") as fh:
+            fh.write(text)
 
 
 if __name__ == "__main__":

@@ -63,6 +63,7 @@ struct DevArgs {
   int rs_width;   // >0: reduce-scatter push: column block q = col/rs_width goes ONLY to push map q
   const __nv_bfloat16* aux;  // optional [M, ld_aux] bf16; epilogue multiplies by (1 - aux^2) (tanh backward)
   int ld_aux;
+  int n_rotate;  // tile column order starts at this n-block (reduce-scatter push: de-synchronises the ranks' targets)
 };
 
 struct PushMaps {
@@ -185,7 +186,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         const int split = w % splits;
         const int tile = w / splits;
         const int m_blk = tile % num_m;
-        const int n_blk = tile / num_m;
+        const int n_blk = (tile / num_m + p.n_rotate) % num_n;
         const int kb0 = split * kb_per_split;
         const int kb1 = min(num_kb, kb0 + kb_per_split);
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -274,7 +275,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
       for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
         const int tile = w / splits;
         const int m_blk = tile % num_m;
-        const int n_blk = tile / num_m;
+        const int n_blk = (tile / num_m + p.n_rotate) % num_n;
         mbar_wait(&tmem_full_bar[acc], acc_phase);
         tc_fence_after_sync();
         const int row0 = m_blk * BM + wg * 32;
@@ -361,7 +362,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
       const int tile = w / splits;
       const int m_blk = tile % num_m;
-      const int n_blk = tile / num_m;
+      const int n_blk = (tile / num_m + p.n_rotate) % num_n;
       mbar_wait(&tmem_full_bar[acc], acc_phase);
       tc_fence_after_sync();
       const int row = m_blk * BM + wg * 32 + lane;
@@ -534,6 +535,7 @@ extern "C" int tadnn_gemm_bf16(const tadnn_gemm_args* a, tadnn_stream_t stream_)
   for (int i = 0; i < a->n_push; ++i) d.push[i] = a->push[i];
   d.push_ldc = a->push_ldc; d.push_col_offset = a->push_col_offset;
   d.rs_width = a->rs_width;
+  d.n_rotate = a->n_rotate > 0 ? a->n_rotate : 0;
   d.aux = static_cast<const __nv_bfloat16*>(a->aux_tanh_out);
   d.ld_aux = a->ld_aux;
   if (a->rs_width > 0) {

@@ -73,6 +73,9 @@ typedef struct tadnn_gemm_args {
   /* Fused tanh backward: multiply the result by (1 - y^2), y = aux_tanh_out[M, ld_aux] bf16. */
   const void* aux_tanh_out;
   int ld_aux;
+  /* Start the tile sweep at this n-block (wraps around).  With rs_width each rank passes a
+   * different value so that the ranks never all push to the same owner at the same time. */
+  int n_rotate;
 } tadnn_gemm_args;
 
 int tadnn_gemm_bf16(const tadnn_gemm_args* args, tadnn_stream_t stream);

@@ -48,7 +48,15 @@ class SyncState:
         self.flat = getattr(model, "_tadnn_flat", None)
         use_overlap = self.flat is not None and self.flat.symmetric and self.flat.ctx.world > 1
         if overlap is None:
-            overlap = os.environ.get("TADNN_DP_OVERLAP", "1") not in ("0", "false")
+            env = os.environ.get("TADNN_DP_OVERLAP")
+            if env is not None:
+                overlap = env not in ("0", "false")
+            else:
+                # small models: one fused launch at the end of backward is cheaper than the stream
+                # fork/join and the SM interference of an overlapped sync (measured: 114K-param CNN,
+                # 8 GPUs, 1.203 ms/step without vs 1.227 ms/step with overlap)
+                nbytes = sum(g.half * g.region.element_size() for g in self.flat.groups.values()) if self.flat else 0
+                overlap = nbytes >= (4 << 20)
         self.overlap = bool(overlap) and use_overlap
         self.comm_stream = torch.cuda.Stream() if self.overlap else None
         self.bucket_bytes = int(bucket_mb * (1 << 20))

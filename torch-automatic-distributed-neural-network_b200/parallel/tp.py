@@ -85,7 +85,10 @@ class _Fn(torch.autograd.Function):
             if o % (64 * P) == 0:
                 w = o // P
                 push = [sc.heap_ptrs[q] + plan.slots_off + r * B * w * 2 for q in range(P)]
-                gemm_bf16(a, wb, bias=b, push=push, push_ldc=w, rs_width=w)
+                # every rank starts its tile sweep at a different owner's column block: at any moment the
+                # P ranks push to P different destinations instead of all hammering rank 0's ingress
+                nblk = (o + 255) // 256
+                gemm_bf16(a, wb, bias=b, push=push, push_ldc=w, rs_width=w, n_rotate=((r + 1) % P) * nblk // P)
                 nxt = torch.empty((B, w), device=x.device, dtype=torch.bfloat16)
                 _native.check(lib.tadnn_reduce_slots(
                     sc.handle, C.c_ulonglong(plan.slots_off), B, w, C.c_float(1.0), None, 0 if last else 1,
@@ -148,7 +151,8 @@ class _Fn(torch.autograd.Function):
             if not need_dx:
                 break
             # g'_r [B, i/P] = (g · W_r) (⊙ tanh' of the layer input if that input is a tanh output)
-            gr = gemm_bf16(gv, wbs[l], b_mn_major=True, aux_tanh_out=a if l > 0 else None)
+            tn = 256 if ((B + 127) // 128) * ((i_sh + 255) // 256) >= 2 * 148 else 128  # fill the 148 SMs
+            gr = gemm_bf16(gv, wbs[l], b_mn_major=True, aux_tanh_out=a if l > 0 else None, tile_n=tn)
             if l > 0 or P > 1:
                 w_prev = i_sh
                 if P > 1:

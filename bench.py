@@ -40,6 +40,8 @@ def parse():
                     help="distinct device-resident batches cycled through (8 x 25 MB > 126 MB L2)")
     ap.add_argument("--lr", type=float, default=1e-3)
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--conv2", default="dense", choices=["dense", "pooled", "legacy"],
+                    help="conv2 forward: all 5x5 output pixels (reference behaviour) or only the 3x3 that pool2 reads")
     return ap.parse_args()
 
 
@@ -110,7 +112,7 @@ def main():
     data, labels = SyntheticCifar(total, "data"), SyntheticCifar(total, "labels")
 
     if a.impl == "tadnn":
-        model = CifarCNN().to(dev)
+        model = CifarCNN(conv2_mode=a.conv2).to(dev)
         d, t, n = tadnn.parallelize(data, labels, model, total, h, None, 1, verbose=False)
         trainer = tadnn.BatchTrainer(model, learningRate=a.lr)
         step = trainer.step
@@ -182,7 +184,7 @@ def main():
             "config": {"model": MODEL, "global_batch": B * P, "per_gpu_batch": B, "seq_len": None,
                        "input": "3x32x32 bf16", "parallelism": f"dp{P}",
                        "sync": "params+grads all-reduce-average every step (batchSize=1)",
-                       "optimizer": "SGD", "l2_policy": f"inputs cycle through {nb} device batches = "
+                       "conv2_forward": a.conv2, "optimizer": "SGD", "l2_policy": f"inputs cycle through {nb} device batches = "
                        f"{nb * B * 3072 * 2 / 1e6:.0f} MB per GPU (> 126 MB L2)"},
             "clocks": sampler.summary() if sampler else None,
             "gpu_launches": launches,

@@ -100,6 +100,82 @@ __global__ void im2col_nchw_kernel(const __nv_bfloat16* __restrict__ x, uint4* _
   }
 }
 
+// ---- im2col with the pooled window first ---------------------------------------------------------
+// Same patch layout as im2col_nhwc, but the output rows are ordered so that the win x win output
+// pixels that the following max-pool actually reads come first ([B*win*win] rows, pixel-major per
+// image), followed by all remaining pixels.  The backward pass only needs the first block: the
+// gradient of every other conv output is exactly zero.
+__global__ void im2col_nhwc_winfirst_kernel(const uint4* __restrict__ x, uint4* __restrict__ col, int B, int H, int W, int C8,
+                                            int KH, int KW, int OH, int OW, int Kpad8, int win, int only_window) {
+  const int npix = only_window ? win * win : OH * OW;
+  const long long total = static_cast<long long>(B) * npix * KH * KW * C8;
+  const int nwin = win * win, nrest = OH * OW - nwin;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c8 = static_cast<int>(i % C8);
+    long long t = i / C8;
+    const int kw = static_cast<int>(t % KW); t /= KW;
+    const int kh = static_cast<int>(t % KH); t /= KH;
+    const int pix = static_cast<int>(t % npix);
+    const int b = static_cast<int>(t / npix);
+    int oy, ox;
+    long long row;
+    if (pix < nwin) {
+      oy = pix / win; ox = pix % win;
+      row = static_cast<long long>(b) * nwin + pix;
+    } else {
+      // enumerate the pixels outside the window in raster order
+      int r = pix - nwin;                       // 0 .. nrest-1
+      const int per_top_row = OW - win;         // pixels right of the window in each of the first `win` rows
+      if (r < win * per_top_row) { oy = r / per_top_row; ox = win + r % per_top_row; }
+      else { r -= win * per_top_row; oy = win + r / OW; ox = r % OW; }
+      row = static_cast<long long>(B) * nwin + static_cast<long long>(b) * nrest + (pix - nwin);
+    }
+    const uint4 v = x[((static_cast<long long>(b) * H + oy + kh) * W + ox + kw) * C8 + c8];
+    col[row * Kpad8 + (kh * KW + kw) * C8 + c8] = v;
+  }
+}
+
+// ---- Toeplitz expansion of the packed conv weights for the transposed convolution ----------------
+// The gradient of the conv output is non-zero only inside the win x win pooled window, so
+//   dX[b, y, x, c] = sum_{(oy,ox) in window} sum_co dY[b,oy,ox,co] * Wp[co, ((y-oy)*KW + (x-ox))*C + c]
+// is ONE dense GEMM  dX[B, (FH*FW*C)] = dYw[B, (win*win*O)] * T^T  with FH = win+KH-1 and
+//   T[(y*FW+x)*C + c, (oy*win+ox)*O + co] = Wp[co, ((y-oy)*KW + (x-ox))*C + c]   (0 outside the kernel).
+__global__ void conv_toeplitz_pack_kernel(const __nv_bfloat16* __restrict__ wp, __nv_bfloat16* __restrict__ T, int O, int C, int KH,
+                                          int KW, int win) {
+  const int FH = win + KH - 1, FW = win + KW - 1;
+  const int Kt = win * win * O;
+  const long long total = static_cast<long long>(FH) * FW * C * Kt;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int k = static_cast<int>(i % Kt);
+    const int n = static_cast<int>(i / Kt);
+    const int co = k % O, pos = k / O, oy = pos / win, ox = pos % win;
+    const int c = n % C, pix = n / C, y = pix / FW, x = pix % FW;
+    const int kh = y - oy, kw = x - ox;
+    __nv_bfloat16 v = __float2bfloat16_rn(0.f);
+    if (kh >= 0 && kh < KH && kw >= 0 && kw < KW) v = wp[static_cast<long long>(co) * (KH * KW * C) + (kh * KW + kw) * C + c];
+    T[i] = v;
+  }
+}
+
+// dst[B, H, W, C] = src[B, FH, FW, C] in the top-left corner, zero elsewhere (16-byte vectors)
+__global__ void expand_corner_nhwc_kernel(const uint4* __restrict__ src, uint4* __restrict__ dst, int B, int H, int W, int FH, int FW,
+                                          int C8) {
+  const long long total = static_cast<long long>(B) * H * W * C8;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c8 = static_cast<int>(i % C8);
+    long long t = i / C8;
+    const int x = static_cast<int>(t % W); t /= W;
+    const int y = static_cast<int>(t % H);
+    const int b = static_cast<int>(t / H);
+    uint4 v = make_uint4(0, 0, 0, 0);
+    if (y < FH && x < FW) v = src[((static_cast<long long>(b) * FH + y) * FW + x) * C8 + c8];
+    dst[i] = v;
+  }
+}
+
 // ---- col2im (gather form): dx[b,y,x,c] = sum_{kh,kw} dcol[(b,y-kh,x-kw), (kh*KW+kw)*C + c] ----
 __global__ void col2im_nhwc_kernel(const uint4* __restrict__ dcol, uint4* __restrict__ dx, int B, int H, int W, int C8,
                                    int KH, int KW, int OH, int OW, int Kpad8) {
@@ -544,6 +620,35 @@ extern "C" int tadnn_im2col(const void* x, void* col, int B, int C, int H, int W
     im2col_nhwc_kernel<<<grid_for(total, 256), 256, 0, stream>>>(static_cast<const uint4*>(x), static_cast<uint4*>(col), B, H, W, C / 8, KH, KW, OH, OW, Kpad / 8);
     TADNN_LAUNCH_CHECK("im2col_nhwc");
   }
+  return 0;
+}
+
+extern "C" int tadnn_im2col_winfirst(const void* x, void* col, int B, int C, int H, int W, int KH, int KW, int win, int only_window,
+                                     tadnn_stream_t stream_) {
+  const int OH = H - KH + 1, OW = W - KW + 1;
+  TADNN_REQUIRE(B > 0 && OH > 0 && OW > 0 && C % 8 == 0, "im2col_winfirst: bad shape (C must be a multiple of 8)");
+  TADNN_REQUIRE(win >= 1 && win <= OH && win <= OW, "im2col_winfirst: window %d does not fit %dx%d", win, OH, OW);
+  const long long total = static_cast<long long>(B) * (only_window ? win * win : OH * OW) * KH * KW * (C / 8);
+  im2col_nhwc_winfirst_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const uint4*>(x), static_cast<uint4*>(col), B, H, W, C / 8, KH, KW, OH, OW, C * KH * KW / 8, win, only_window);
+  TADNN_LAUNCH_CHECK("im2col_nhwc_winfirst");
+  return 0;
+}
+
+extern "C" int tadnn_conv_toeplitz_pack(const void* wp, void* T, int O, int C, int KH, int KW, int win, tadnn_stream_t stream_) {
+  const long long total = static_cast<long long>(win + KH - 1) * (win + KW - 1) * C * win * win * O;
+  conv_toeplitz_pack_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const __nv_bfloat16*>(wp), static_cast<__nv_bfloat16*>(T), O, C, KH, KW, win);
+  TADNN_LAUNCH_CHECK("conv_toeplitz_pack");
+  return 0;
+}
+
+extern "C" int tadnn_expand_corner(const void* src, void* dst, int B, int H, int W, int FH, int FW, int C, tadnn_stream_t stream_) {
+  TADNN_REQUIRE(C % 8 == 0 && FH <= H && FW <= W, "expand_corner: bad shape");
+  const long long total = static_cast<long long>(B) * H * W * (C / 8);
+  expand_corner_nhwc_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const uint4*>(src), static_cast<uint4*>(dst), B, H, W, FH, FW, C / 8);
+  TADNN_LAUNCH_CHECK("expand_corner_nhwc");
   return 0;
 }
 

@@ -190,6 +190,19 @@ int tadnn_allreduce_emulated(tadnn_comm* const* comms, int world, unsigned long 
  * zero padded.  nchw=1: x is [B,C,H,W] (the input image); nchw=0: x is [B,H,W,C], C%8==0. */
 int tadnn_im2col(const void* x, void* col, int B, int C, int H, int W, int KH, int KW, int Kpad,
                  int nchw, tadnn_stream_t stream);
+/* im2col (NHWC) whose rows put the win x win output pixels read by the following max-pool first
+ * (rows [0, B*win*win), pixel-major per image), then all other pixels; only_window=1 writes just
+ * the first block.  The backward pass uses only that block (all other gradients are zero). */
+int tadnn_im2col_winfirst(const void* x, void* col, int B, int C, int H, int W, int KH, int KW, int win,
+                          int only_window, tadnn_stream_t stream);
+/* T[(y*FW+x)*C + c, (oy*win+ox)*O + co] = Wp[co, ((y-oy)*KW+(x-ox))*C + c] (0 outside the kernel),
+ * FH = win+KH-1: turns the transposed convolution of a gradient that is non-zero only inside the
+ * pooled window into one dense GEMM dX[B, FH*FW*C] = dYw[B, win*win*O] * T^T. */
+int tadnn_conv_toeplitz_pack(const void* wp, void* T, int O, int C, int KH, int KW, int win,
+                             tadnn_stream_t stream);
+/* dst[B,H,W,C] = src[B,FH,FW,C] in the top-left corner, zeros elsewhere. */
+int tadnn_expand_corner(const void* src, void* dst, int B, int H, int W, int FH, int FW, int C,
+                        tadnn_stream_t stream);
 /* dx[B,H,W,C] = col2im(dcol[B*OH*OW, C*KH*KW]) (gather form, no atomics). */
 int tadnn_col2im(const void* dcol, void* dx, int B, int C, int H, int W, int KH, int KW,
                  tadnn_stream_t stream);

@@ -87,12 +87,33 @@ def test_fused_conv1_matches_unfused_kernels():
         assert rel < 2e-3, (B, rel)
 
 
-@pytest.mark.parametrize("fused", [True, False])
+def test_conv2_modes_agree():
+    """dense / pooled / legacy conv2 paths give the same loss and the same gradients."""
+    from tadnn.models.cifar_cnn import CifarCNN
+    res = {}
+    for mode in ("legacy", "dense", "pooled"):
+        torch.manual_seed(0)
+        m = CifarCNN(conv2_mode=mode).cuda().eval()
+        x = torch.randn(37, 3, 32, 32, device="cuda", generator=torch.Generator(device="cuda").manual_seed(5)).bfloat16()
+        t = torch.arange(37, device="cuda") % 10
+        loss = m.loss(x, t)
+        loss.backward()
+        res[mode] = (loss.item(), {n: p.grad.clone() for n, p in m.named_parameters()})
+    for mode in ("dense", "pooled"):
+        assert abs(res[mode][0] - res["legacy"][0]) < 1e-6
+        for n, g in res[mode][1].items():
+            ref = res["legacy"][1][n]
+            assert ((g - ref).norm() / (ref.norm() + 1e-12)).item() < 1.5e-2, (mode, n)
+    for n, g in res["pooled"][1].items():
+        assert torch.equal(g, res["dense"][1][n]) or ((g - res["dense"][1][n]).norm() / (g.norm() + 1e-12)).item() < 1e-3
+
+
+@pytest.mark.parametrize("fused,mode", [(True, "dense"), (True, "pooled"), (False, "legacy")])
 @pytest.mark.parametrize("B", [1, 7, 64, 300])
-def test_cifar_cnn_loss_and_grads_match_pytorch(B, fused):
+def test_cifar_cnn_loss_and_grads_match_pytorch(B, fused, mode):
     from tadnn.models.cifar_cnn import CifarCNN
     torch.manual_seed(0)
-    m = CifarCNN(fused_conv1=fused).cuda().eval()  # eval: dropout off, exact comparison
+    m = CifarCNN(fused_conv1=fused, conv2_mode=mode).cuda().eval()  # eval: dropout off, exact comparison
     with torch.no_grad():  # widen the init a little so ReLUs/pools are well exercised
         for p in m.parameters():
             p.mul_(2.0)

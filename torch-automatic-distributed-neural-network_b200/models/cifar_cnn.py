@@ -28,7 +28,7 @@ K1PAD = 80  # 75 -> multiple of 8 (TMA pitch)
 
 class _CnnLoss(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fused_conv1):
+    def forward(ctx, x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fused_conv1, conv2_mode):
         from ..ops import cnn as K
         B = x.shape[0]
         dev = x.device
@@ -44,9 +44,16 @@ class _CnnLoss(torch.autograd.Function):
             col1 = K.im2col(xb, 5, 5, K1PAD, nchw=True)                       # [B*784, 80]
             a1 = K.gemm_bf16(col1, w1p, bias=b1, act="relu", tile_n=64)       # [B*784, 64] == NHWC [B,28,28,64]
             p1, idx1 = K.maxpool_fwd(a1.view(B, 28, 28, 64), 3)               # [B,9,9,64]
-        col2 = K.im2col(p1, 5, 5, 1600, nchw=False)                       # [B*25, 1600]
-        a2 = K.gemm_bf16(col2, w2p, bias=b2, act="relu", tile_n=64)       # [B*25, 64] == [B,5,5,64]
-        p2, idx2 = K.maxpool_fwd(a2.view(B, 5, 5, 64), 3)                 # [B,1,1,64]
+        if conv2_mode == "legacy":
+            col2 = K.im2col(p1, 5, 5, 1600, nchw=False)                       # [B*25, 1600]
+            a2 = K.gemm_bf16(col2, w2p, bias=b2, act="relu", tile_n=64)       # [B*25, 64] == [B,5,5,64]
+            p2, idx2 = K.maxpool_fwd(a2.view(B, 5, 5, 64), 3)                 # [B,1,1,64]
+        else:
+            # rows ordered with the 3x3 pixels that pool2 reads first; "dense" still evaluates the
+            # convolution at all 25 pixels (as the reference does), "pooled" only at those 9
+            col2 = K.im2col_winfirst(p1, 5, 5, 3, only_window=(conv2_mode == "pooled"))
+            a2 = K.gemm_bf16(col2, w2p, bias=b2, act="relu", tile_n=64)
+            p2, idx2 = K.maxpool_fwd(a2[:B * 9].view(B, 3, 3, 64), 3)         # [B,1,1,64]
         hidden = torch.empty((B, 100), device=dev, dtype=torch.float32)
         logp = torch.empty((B, 10), device=dev, dtype=torch.float32)
         loss = torch.empty((), device=dev, dtype=torch.float32)
@@ -63,6 +70,7 @@ class _CnnLoss(torch.autograd.Function):
         ctx.save_for_backward(col1, a1, p1, idx1, col2, a2, p2, idx2, hidden, logp, tgt, w2p, fw1, fb1, fw2, fb2)
         ctx.p_drop, ctx.seed, ctx.B = float(p_drop), int(seed) & 0xFFFFFFFF, B
         ctx.fused_conv1 = bool(fused_conv1)
+        ctx.conv2_mode = conv2_mode
         ctx.mark_non_differentiable(logp)
         return loss, logp
 
@@ -89,14 +97,26 @@ class _CnnLoss(torch.autograd.Function):
         gl = gloss.to(device=dev, dtype=torch.float32).contiguous()
         h.grad_scale_dev = gl.data_ptr()  # upstream dLoss stays on the device: no host sync
         _native.check(_native.lib().tadnn_head_backward(C.byref(h), C.c_void_p(_native.stream_ptr())), "tadnn_head_backward")
-        # conv2: pool/relu backward into a2's storage, bias grad, wgrad (split-K), dgrad into col2's storage
-        da2 = K.maxpool_relu_bwd(dp2, p2, idx2, 5, 5, 3, out=a2.view(B, 5, 5, 64)).view(B * 25, 64)
         K.colsum_relu_mask(dp2, p2, gb2)
-        dw2p = K.gemm_bf16(da2, col2, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
-                           split_k=K.auto_split_k(64, 1600, B * 25))
-        K.conv_wgrad_unpack(dw2p, gw2, 64, 5, 5)
-        dcol2 = K.gemm_bf16(da2, w2p, b_mn_major=True, out=col2)
-        dp1 = K.col2im(dcol2, B, 64, 9, 9, 5, 5)
+        if ctx.conv2_mode == "legacy":
+            # pool/relu backward into a2's storage, wgrad (split-K), dgrad into col2's storage, col2im
+            da2 = K.maxpool_relu_bwd(dp2, p2, idx2, 5, 5, 3, out=a2.view(B, 5, 5, 64)).view(B * 25, 64)
+            dw2p = K.gemm_bf16(da2, col2, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
+                               split_k=K.auto_split_k(64, 1600, B * 25))
+            K.conv_wgrad_unpack(dw2p, gw2, 64, 5, 5)
+            dcol2 = K.gemm_bf16(da2, w2p, b_mn_major=True, out=col2)
+            dp1 = K.col2im(dcol2, B, 64, 9, 9, 5, 5)
+        else:
+            # d(conv2 out) is exactly zero outside the 3x3 pooled window: wgrad over those 9 pixels'
+            # patches, and the transposed convolution as ONE dense GEMM against the Toeplitz-expanded
+            # weights ([B, 9*64] x [9*64, 7*7*64]) instead of a 25-tap dgrad GEMM + col2im
+            da2w = K.maxpool_relu_bwd(dp2, p2, idx2, 3, 3, 3).view(B * 9, 64)
+            dw2p = K.gemm_bf16(da2w, col2[:B * 9], a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
+                               split_k=K.auto_split_k(64, 1600, B * 9))
+            K.conv_wgrad_unpack(dw2p, gw2, 64, 5, 5)
+            T = K.conv_toeplitz_pack(w2p, 64, 64, 5, 5, 3)                    # [7*7*64, 9*64]
+            dp1c = K.gemm_bf16(da2w.view(B, 576), T)                          # [B, 7*7*64]
+            dp1 = K.expand_corner(dp1c.view(B, 7, 7, 64), 9, 9)
         # conv1 (no dgrad: the image needs no gradient)
         K.colsum_relu_mask(dp1, p1, gb1)
         if ctx.fused_conv1:
@@ -107,14 +127,19 @@ class _CnnLoss(torch.autograd.Function):
                                split_k=K.auto_split_k(64, K1PAD, B * 784, 128), tile_n=128)
             K.conv_wgrad_unpack(dw1p, gw1, 3, 5, 5)
         grads = [gw1, gb1, gw2, gb2, gfw1, gfb1, gfw2, gfb2]
-        return (None, None, *grads, None, None, None)
+        return (None, None, *grads, None, None, None, None)
 
 
 class CifarCNN(torch.nn.Module, T7Protocol):
-    def __init__(self, dropout: float = 0.5, seed: int = 1, fused_conv1: bool = True):
+    def __init__(self, dropout: float = 0.5, seed: int = 1, fused_conv1: bool = True, conv2_mode: str = "dense"):
         super().__init__()
+        assert conv2_mode in ("dense", "pooled", "legacy")
         self.dropout = dropout
         self.fused_conv1 = fused_conv1  # False: im2col + GEMM + separate pooling kernels (generic path)
+        # conv2 forward: "dense" evaluates all 5x5 output pixels like the reference; "pooled" only the
+        # 3x3 that pool2 reads (identical loss and gradients); both use the sparse-gradient backward.
+        # "legacy": raster-order im2col, 25-tap dgrad GEMM + col2im (first implementation, kept as oracle).
+        self.conv2_mode = conv2_mode
         self._step = 0
         self._seed = seed
         P = torch.nn.Parameter
@@ -167,7 +192,7 @@ class CifarCNN(torch.nn.Module, T7Protocol):
             seed = (self._seed * 2654435761 + self._step * 40503) & 0xFFFFFFFF
             return _CnnLoss.apply(x, target.to(x.device), self.conv1_weight, self.conv1_bias, self.conv2_weight,
                                   self.conv2_bias, self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias, p, seed,
-                                  self.fused_conv1)
+                                  self.fused_conv1, self.conv2_mode)
         logp = self.reference_logp(x)
         return F.nll_loss(logp, target.long().to(logp.device)), logp.detach()
 

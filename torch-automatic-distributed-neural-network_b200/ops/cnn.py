@@ -41,6 +41,31 @@ def im2col(x: torch.Tensor, KH: int, KW: int, Kpad: int, nchw: bool, out=None) -
     return out
 
 
+def im2col_winfirst(x: torch.Tensor, KH: int, KW: int, win: int, only_window: bool) -> torch.Tensor:
+    """NHWC im2col with the pooled window's pixels first: rows [0, B*win*win) are (b, oy<win, ox<win)."""
+    B, H, W, Cc = x.shape
+    OH, OW = H - KH + 1, W - KW + 1
+    rows = B * (win * win if only_window else OH * OW)
+    out = torch.empty((rows, Cc * KH * KW), device=x.device, dtype=torch.bfloat16)
+    _native.check(_native.lib().tadnn_im2col_winfirst(_p(x), _p(out), B, Cc, H, W, KH, KW, win, int(only_window), _s()),
+                  "tadnn_im2col_winfirst")
+    return out
+
+
+def conv_toeplitz_pack(wp: torch.Tensor, O: int, Cc: int, KH: int, KW: int, win: int) -> torch.Tensor:
+    FH, FW = win + KH - 1, win + KW - 1
+    T = torch.empty((FH * FW * Cc, win * win * O), device=wp.device, dtype=torch.bfloat16)
+    _native.check(_native.lib().tadnn_conv_toeplitz_pack(_p(wp), _p(T), O, Cc, KH, KW, win, _s()), "tadnn_conv_toeplitz_pack")
+    return T
+
+
+def expand_corner(src: torch.Tensor, H: int, W: int) -> torch.Tensor:
+    B, FH, FW, Cc = src.shape
+    dst = torch.empty((B, H, W, Cc), device=src.device, dtype=torch.bfloat16)
+    _native.check(_native.lib().tadnn_expand_corner(_p(src), _p(dst), B, H, W, FH, FW, Cc, _s()), "tadnn_expand_corner")
+    return dst
+
+
 def col2im(dcol: torch.Tensor, B: int, Cc: int, H: int, W: int, KH: int, KW: int) -> torch.Tensor:
     dx = torch.empty((B, H, W, Cc), device=dcol.device, dtype=torch.bfloat16)
     _native.check(_native.lib().tadnn_col2im(_p(dcol), _p(dx), B, Cc, H, W, KH, KW, _s()), "tadnn_col2im")
@@ -141,5 +166,5 @@ def auto_split_k(M: int, N: int, K: int, tile_n: int = 256) -> int:
     return max(1, min(kb, 148 // max(1, tiles)))
 
 
-__all__ = ["conv1_weight_pack", "conv1_pool_forward", "conv1_pool_backward", "im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "conv_weight_pack",
+__all__ = ["im2col_winfirst", "conv_toeplitz_pack", "expand_corner", "conv1_weight_pack", "conv1_pool_forward", "conv1_pool_backward", "im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "conv_weight_pack",
            "conv_wgrad_unpack", "head_workspace", "sgd_step", "auto_split_k", "HeadArgs", "gemm_bf16"]

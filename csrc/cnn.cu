@@ -352,6 +352,44 @@ __global__ void colsum_relu_mask_kernel(const __nv_bfloat16* __restrict__ dy, co
   }
 }
 
+// Vectorised, corner-restricted variant: dy is [B, FH, FW, C] (compact), y is [B, H, W, C].
+// blockDim = (8, 32): x = 8-channel vector of a 64-channel chunk, y = row lane; grid.x = C/64 chunks.
+__global__ void __launch_bounds__(256) colsum_relu_mask_corner_kernel(const __nv_bfloat16* __restrict__ dy,
+                                                                       const __nv_bfloat16* __restrict__ y, float* __restrict__ out,
+                                                                       int B, int H, int W, int FH, int FW, int C) {
+  __shared__ float part[32][65];
+  const int c = blockIdx.x * 64 + threadIdx.x * 8;
+  float acc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  const long long R = static_cast<long long>(B) * FH * FW;
+  if (c < C) {
+    const long long rows_per = (R + gridDim.y - 1) / gridDim.y;
+    const long long r0 = blockIdx.y * rows_per, r1 = min(R, r0 + rows_per);
+    for (long long r = r0 + threadIdx.y; r < r1; r += 32) {
+      const int fx = static_cast<int>(r % FW), fy = static_cast<int>((r / FW) % FH);
+      const long long b = r / (static_cast<long long>(FW) * FH);
+      const uint4 dv = *reinterpret_cast<const uint4*>(dy + r * C + c);
+      const uint4 yv = *reinterpret_cast<const uint4*>(y + ((b * H + fy) * W + fx) * C + c);
+      const uint32_t dw[4] = {dv.x, dv.y, dv.z, dv.w}, yw[4] = {yv.x, yv.y, yv.z, yv.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 d2 = unpack_bf16x2(dw[e]);
+        if (yw[e] & 0xffffu) acc[2 * e] += d2.x;          // y is a ReLU output: > 0  <=>  bits != 0
+        if (yw[e] & 0xffff0000u) acc[2 * e + 1] += d2.y;
+      }
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) part[threadIdx.y][threadIdx.x * 8 + e] = acc[e];
+  __syncthreads();
+  const int t = threadIdx.y * 8 + threadIdx.x;
+  if (t < 64 && blockIdx.x * 64 + t < C) {
+    float sum = 0.f;
+#pragma unroll 8
+    for (int yy = 0; yy < 32; ++yy) sum += part[yy][t];
+    atomicAdd(out + blockIdx.x * 64 + t, sum);
+  }
+}
+
 // ---- conv weight layout/dtype conversion -----------------------------------------------------
 // Torch7 SpatialConvolutionMM keeps weight [O, C*KH*KW] with k = (c*KH + kh)*KW + kw.  The GEMMs
 // want bf16 [O, Kpad] with k' = (kh*KW + kw)*C + c (matches the NHWC im2col), zero padded.
@@ -703,6 +741,20 @@ extern "C" int tadnn_colsum_relu_mask(const void* dy, const void* y, float* out,
   if (blocks > sm_count() * 4) blocks = sm_count() * 4;
   colsum_relu_mask_kernel<<<static_cast<int>(blocks), dim3(64, 4), 0, static_cast<cudaStream_t>(stream_)>>>(static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(y), out, R, C);
   TADNN_LAUNCH_CHECK("colsum_relu_mask");
+  return 0;
+}
+
+extern "C" int tadnn_colsum_relu_mask_corner(const void* dy, const void* y, float* out, int B, int H, int W, int FH, int FW, int C,
+                                             tadnn_stream_t stream_) {
+  TADNN_REQUIRE(B > 0 && C % 8 == 0 && FH >= 1 && FW >= 1 && FH <= H && FW <= W, "colsum_relu_mask_corner: bad shape");
+  const int cx = (C + 63) / 64;
+  const long long R = static_cast<long long>(B) * FH * FW;
+  long long ry = (4ll * sm_count() + cx - 1) / cx;
+  if (ry > (R + 255) / 256) ry = (R + 255) / 256;
+  if (ry < 1) ry = 1;
+  colsum_relu_mask_corner_kernel<<<dim3(cx, static_cast<unsigned>(ry)), dim3(8, 32), 0, static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const __nv_bfloat16*>(dy), static_cast<const __nv_bfloat16*>(y), out, B, H, W, FH, FW, C);
+  TADNN_LAUNCH_CHECK("colsum_relu_mask_corner");
   return 0;
 }
 

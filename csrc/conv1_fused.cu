@@ -43,6 +43,7 @@ struct Conv1Args {
   const __nv_bfloat16* dp1;   // backward: [B, 9, 9, 64]
   float* gw;                  // backward: [64, 75] Torch7 layout (c,kh,kw), accumulated with red.add
   int B;
+  int dph, dpw;               // backward: dp1 is stored compactly as [B, dph, dpw, 64] (zero outside), dph,dpw <= 9
 };
 
 // byte offset of 16-byte chunk j of row r inside a SWIZZLE_128B [rows x 128 B] block
@@ -386,7 +387,12 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args 
       const long long win = t * kWinPerTile + wl;
       ok = (wl < kWinPerTile) && (t < num_tiles) && (win < total_win);
       if (ok) {
-        dv = __ldg(reinterpret_cast<const uint4*>(a.dp1 + win * kO + j * 8));
+        const int b = static_cast<int>(win / kWinPerImg), wi = static_cast<int>(win % kWinPerImg);
+        const int py = wi / kPW, px = wi % kPW;
+        ok = (py < a.dph) && (px < a.dpw);  // the pooled gradient is zero outside its stored corner
+        if (ok) dv = __ldg(reinterpret_cast<const uint4*>(a.dp1 + ((static_cast<long long>(b) * a.dph + py) * a.dpw + px) * kO + j * 8));
+      }
+      if (ok) {
         pv = __ldg(reinterpret_cast<const uint4*>(a.p1 + win * kO + j * 8));
         iv = __ldg(reinterpret_cast<const uint2*>(a.idx1 + win * kO + j * 8));
       }
@@ -498,9 +504,10 @@ extern "C" int tadnn_conv1_pool_forward(const void* x, const void* w_packed, con
   return 0;
 }
 
-extern "C" int tadnn_conv1_pool_backward(const void* x, const void* dp1, const void* p1, const void* idx1, float* grad_weight,
-                                         int B, tadnn_stream_t stream) {
+extern "C" int tadnn_conv1_pool_backward(const void* x, const void* dp1, int dp1_h, int dp1_w, const void* p1, const void* idx1,
+                                         float* grad_weight, int B, tadnn_stream_t stream) {
   TADNN_REQUIRE(B > 0, "conv1_pool_backward: empty batch");
+  TADNN_REQUIRE(dp1_h >= 1 && dp1_h <= kPH && dp1_w >= 1 && dp1_w <= kPW, "conv1_pool_backward: dp1 extent %dx%d out of range", dp1_h, dp1_w);
   TADNN_REQUIRE(((reinterpret_cast<uintptr_t>(dp1) | reinterpret_cast<uintptr_t>(p1) | reinterpret_cast<uintptr_t>(idx1)) & 15) == 0,
                 "conv1_pool_backward: operands must be 16-byte aligned");
   static bool attr = false;
@@ -510,7 +517,7 @@ extern "C" int tadnn_conv1_pool_backward(const void* x, const void* dp1, const v
   a.x = static_cast<const __nv_bfloat16*>(x); a.dp1 = static_cast<const __nv_bfloat16*>(dp1);
   a.p1 = const_cast<__nv_bfloat16*>(static_cast<const __nv_bfloat16*>(p1));
   a.idx1 = const_cast<unsigned char*>(static_cast<const unsigned char*>(idx1));
-  a.gw = grad_weight; a.B = B;
+  a.gw = grad_weight; a.B = B; a.dph = dp1_h; a.dpw = dp1_w;
   const long long tiles = (static_cast<long long>(B) * kWinPerImg + kWinPerTile - 1) / kWinPerTile;
   const int grid = tiles < sm_count() ? static_cast<int>(tiles) : sm_count();
   conv1_bwd_kernel<<<grid, kThreads, kBwdSmem, static_cast<cudaStream_t>(stream)>>>(a);

@@ -218,6 +218,9 @@ int tadnn_colsum_bf16(const void* x, float* out, long long R, int C, int ld, tad
  * pooled tensors (dy, y: bf16 [R, C] contiguous). */
 int tadnn_colsum_relu_mask(const void* dy, const void* y, float* out, long long R, int C,
                            tadnn_stream_t stream);
+/* Same, dy stored compactly as [B, FH, FW, C] (top-left corner of y's [B, H, W, C] grid). */
+int tadnn_colsum_relu_mask_corner(const void* dy, const void* y, float* out, int B, int H, int W, int FH,
+                                  int FW, int C, tadnn_stream_t stream);
 /* Torch7 conv weight [O, C*KH*KW] fp32 (k = (c*KH+kh)*KW+kw)  <->  GEMM operand [O, Kpad] bf16
  * (k' = (kh*KW+kw)*C+c); unpack accumulates: grad += scale * dwp. */
 int tadnn_conv_weight_pack(const float* w, void* wp, int O, int C, int KH, int KW, int Kpad,
@@ -235,8 +238,10 @@ int tadnn_conv_wgrad_unpack(const float* dwp, float* grad, int O, int C, int KH,
 int tadnn_conv1_weight_pack(const float* w, void* w_packed, tadnn_stream_t stream);
 int tadnn_conv1_pool_forward(const void* x, const void* w_packed, const float* bias, void* p1,
                              void* idx1, int B, tadnn_stream_t stream);
-int tadnn_conv1_pool_backward(const void* x, const void* dp1, const void* p1, const void* idx1,
-                              float* grad_weight, int B, tadnn_stream_t stream);
+/* dp1 may be stored compactly as [B, dp1_h, dp1_w, 64] (its non-zero top-left corner); pass 9, 9
+ * for the full tensor. */
+int tadnn_conv1_pool_backward(const void* x, const void* dp1, int dp1_h, int dp1_w, const void* p1,
+                              const void* idx1, float* grad_weight, int B, tadnn_stream_t stream);
 
 /* Fused classifier head: dropout -> Linear(D,H)+ReLU -> Linear(H,NC) -> log-softmax -> NLL.
  * Limits: D <= 64, H <= 128, NC <= 32.  fc weights in Torch7 nn.Linear layout, fp32. */

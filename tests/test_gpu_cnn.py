@@ -137,6 +137,22 @@ def test_cifar_cnn_loss_and_grads_match_pytorch(B, fused, mode):
         assert v < 4e-2, f"{n}: relative error {v}"
 
 
+def test_forward_backward_matches_autograd_path():
+    from tadnn.models.cifar_cnn import CifarCNN
+    torch.manual_seed(0)
+    a, b = CifarCNN().cuda().eval(), CifarCNN().cuda().eval()
+    b.load_state_dict(a.state_dict())
+    x = torch.randn(50, 3, 32, 32, device="cuda").bfloat16()
+    t = torch.randint(0, 10, (50,), device="cuda")
+    la = a.loss(x, t)
+    la.backward()
+    lb = b.forward_backward(x, t)
+    lb2 = b.forward_backward(x, t)  # accumulates
+    assert la.item() == lb.item() == lb2.item()
+    for (n, p), q in zip(a.named_parameters(), b.parameters()):
+        assert ((q.grad - 2 * p.grad).norm() / (p.grad.norm() + 1e-12)).item() < 2e-3, n
+
+
 def test_cifar_cnn_dropout_is_consistent_and_seeded():
     from tadnn.models.cifar_cnn import CifarCNN
     torch.manual_seed(0)

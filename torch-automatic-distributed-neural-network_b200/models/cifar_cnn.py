@@ -26,107 +26,132 @@ from ..nn.protocol import T7Protocol
 K1PAD = 80  # 75 -> multiple of 8 (TMA pitch)
 
 
+def _cnn_forward(x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fused_conv1, conv2_mode):
+    """Launch the forward kernels; returns (loss, logp, saved-for-backward dict)."""
+    from ..ops import cnn as K
+    B = x.shape[0]
+    dev = x.device
+    xb = x if x.dtype == torch.bfloat16 else x.to(torch.bfloat16)
+    xb = xb.contiguous()
+    w2p = K.conv_weight_pack(w2, 64, 5, 5, 1600)
+    col1 = a1 = None
+    if fused_conv1:
+        # implicit-GEMM conv + bias + ReLU + max-pool in one tcgen05 kernel: no col1 / a1 in HBM
+        p1, idx1 = K.conv1_pool_forward(xb, K.conv1_weight_pack(w1), b1)
+    else:
+        w1p = K.conv_weight_pack(w1, 3, 5, 5, K1PAD)
+        col1 = K.im2col(xb, 5, 5, K1PAD, nchw=True)                       # [B*784, 80]
+        a1 = K.gemm_bf16(col1, w1p, bias=b1, act="relu", tile_n=64)       # [B*784, 64] == NHWC [B,28,28,64]
+        p1, idx1 = K.maxpool_fwd(a1.view(B, 28, 28, 64), 3)               # [B,9,9,64]
+    if conv2_mode == "legacy":
+        col2 = K.im2col(p1, 5, 5, 1600, nchw=False)                       # [B*25, 1600]
+        a2 = K.gemm_bf16(col2, w2p, bias=b2, act="relu", tile_n=64)       # [B*25, 64] == [B,5,5,64]
+        p2, idx2 = K.maxpool_fwd(a2.view(B, 5, 5, 64), 3)                 # [B,1,1,64]
+    else:
+        # rows ordered with the 3x3 pixels that pool2 reads first; "dense" still evaluates the
+        # convolution at all 25 pixels (as the reference does), "pooled" only at those 9
+        col2 = K.im2col_winfirst(p1, 5, 5, 3, only_window=(conv2_mode == "pooled"))
+        a2 = K.gemm_bf16(col2, w2p, bias=b2, act="relu", tile_n=64)
+        p2, idx2 = K.maxpool_fwd(a2[:B * 9].view(B, 3, 3, 64), 3)         # [B,1,1,64]
+    hidden = torch.empty((B, 100), device=dev, dtype=torch.float32)
+    logp = torch.empty((B, 10), device=dev, dtype=torch.float32)
+    loss = torch.empty((), device=dev, dtype=torch.float32)
+    tgt = target.to(device=dev, dtype=torch.int64).contiguous()
+    seed = int(seed) & 0xFFFFFFFF
+    h = K.HeadArgs()
+    h.p2, h.w1, h.b1, h.w2, h.b2 = p2.data_ptr(), fw1.data_ptr(), fb1.data_ptr(), fw2.data_ptr(), fb2.data_ptr()
+    h.target = tgt.data_ptr()
+    h.B, h.D, h.H, h.NC = B, 64, 100, 10
+    h.dropout_p, h.seed = float(p_drop), seed
+    h.hidden, h.logp, h.loss = hidden.data_ptr(), logp.data_ptr(), loss.data_ptr()
+    ws = K.head_workspace(dev)
+    _native.check(_native.lib().tadnn_head_forward(C.byref(h), C.c_void_p(ws.data_ptr()),
+                                                   C.c_void_p(_native.stream_ptr())), "tadnn_head_forward")
+    saved = dict(xb=xb, col1=col1, a1=a1, p1=p1, idx1=idx1, col2=col2, a2=a2, p2=p2, idx2=idx2, hidden=hidden,
+                 logp=logp, tgt=tgt, w2p=w2p, fw1=fw1, fb1=fb1, fw2=fw2, fb2=fb2, p_drop=float(p_drop), seed=seed,
+                 B=B, fused_conv1=bool(fused_conv1), conv2_mode=conv2_mode)
+    return loss, logp, saved
+
+
+def _cnn_backward(sv, gw1, gb1, gw2, gb2, gfw1, gfb1, gfw2, gfb2, gloss=None):
+    """Launch the backward kernels; every gradient is ACCUMULATED (+=) into the given fp32 buffers
+    (Torch7 layouts).  ``gloss``: optional device scalar dLoss."""
+    from ..ops import cnn as K
+    B, dev = sv["B"], sv["p2"].device
+    p1, idx1, p2, idx2, col2, a2, w2p = sv["p1"], sv["idx1"], sv["p2"], sv["idx2"], sv["col2"], sv["a2"], sv["w2p"]
+    dp2 = torch.empty((B, 1, 1, 64), device=dev, dtype=torch.bfloat16)
+    h = K.HeadArgs()
+    h.p2, h.w1, h.b1, h.w2, h.b2 = p2.data_ptr(), sv["fw1"].data_ptr(), sv["fb1"].data_ptr(), sv["fw2"].data_ptr(), sv["fb2"].data_ptr()
+    h.target = sv["tgt"].data_ptr()
+    h.B, h.D, h.H, h.NC = B, 64, 100, 10
+    h.dropout_p, h.seed = sv["p_drop"], sv["seed"]
+    h.hidden, h.logp = sv["hidden"].data_ptr(), sv["logp"].data_ptr()
+    h.gw1, h.gb1, h.gw2, h.gb2 = gfw1.data_ptr(), gfb1.data_ptr(), gfw2.data_ptr(), gfb2.data_ptr()
+    h.dp2 = dp2.data_ptr()
+    h.grad_scale = 1.0
+    if gloss is not None:
+        gl = gloss.to(device=dev, dtype=torch.float32).contiguous()
+        h.grad_scale_dev = gl.data_ptr()  # upstream dLoss stays on the device: no host sync
+    _native.check(_native.lib().tadnn_head_backward(C.byref(h), C.c_void_p(_native.stream_ptr())), "tadnn_head_backward")
+    K.colsum_relu_mask(dp2, p2, gb2)
+    if sv["conv2_mode"] == "legacy":
+        # pool/relu backward into a2's storage, wgrad (split-K), dgrad into col2's storage, col2im
+        da2 = K.maxpool_relu_bwd(dp2, p2, idx2, 5, 5, 3, out=a2.view(B, 5, 5, 64)).view(B * 25, 64)
+        dw2p = K.gemm_bf16(da2, col2, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
+                           split_k=K.auto_split_k(64, 1600, B * 25))
+        K.conv_wgrad_unpack(dw2p, gw2, 64, 5, 5)
+        dcol2 = K.gemm_bf16(da2, w2p, b_mn_major=True, out=col2)
+        dp1 = K.col2im(dcol2, B, 64, 9, 9, 5, 5)
+        K.colsum_relu_mask(dp1, p1, gb1)
+    else:
+        # d(conv2 out) is exactly zero outside the 3x3 pooled window: wgrad over those 9 pixels'
+        # patches, and the transposed convolution as ONE dense GEMM against the Toeplitz-expanded
+        # weights ([B, 9*64] x [9*64, 7*7*64]) instead of a 25-tap dgrad GEMM + col2im.  The result
+        # is the 7x7 top-left corner of dp1 (the rest is zero) and is consumed in that compact form.
+        da2w = K.maxpool_relu_bwd(dp2, p2, idx2, 3, 3, 3).view(B * 9, 64)
+        dw2p = K.gemm_bf16(da2w, col2[:B * 9], a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
+                           split_k=K.auto_split_k(64, 1600, B * 9))
+        K.conv_wgrad_unpack(dw2p, gw2, 64, 5, 5)
+        T = K.conv_toeplitz_pack(w2p, 64, 64, 5, 5, 3)                    # [7*7*64, 9*64]
+        dp1 = K.gemm_bf16(da2w.view(B, 576), T).view(B, 7, 7, 64)        # compact corner of [B,9,9,64]
+        K.colsum_relu_mask_corner(dp1, p1, gb1)
+        if not sv["fused_conv1"]:
+            dp1 = K.expand_corner(dp1, 9, 9)
+    # conv1 (no dgrad: the image needs no gradient)
+    if sv["fused_conv1"]:
+        K.conv1_pool_backward(sv["xb"], dp1, p1, idx1, gw1)
+    else:
+        a1, col1 = sv["a1"], sv["col1"]
+        da1 = K.maxpool_relu_bwd(dp1, p1, idx1, 28, 28, 3, out=a1.view(B, 28, 28, 64)).view(B * 784, 64)
+        dw1p = K.gemm_bf16(da1, col1, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
+                           split_k=K.auto_split_k(64, K1PAD, B * 784, 128), tile_n=128)
+        K.conv_wgrad_unpack(dw1p, gw1, 3, 5, 5)
+
+
 class _CnnLoss(torch.autograd.Function):
+    """Autograd wrapper (``loss.backward()`` idiom).  ``CifarCNN.forward_backward`` is the same pair
+    of launch sequences without autograd, accumulating straight into ``param.grad``."""
+
     @staticmethod
     def forward(ctx, x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fused_conv1, conv2_mode):
-        from ..ops import cnn as K
-        B = x.shape[0]
-        dev = x.device
-        xb = x if x.dtype == torch.bfloat16 else x.to(torch.bfloat16)
-        xb = xb.contiguous()
-        w2p = K.conv_weight_pack(w2, 64, 5, 5, 1600)
-        if fused_conv1:
-            # implicit-GEMM conv + bias + ReLU + max-pool in one tcgen05 kernel: no col1 / a1 in HBM
-            p1, idx1 = K.conv1_pool_forward(xb, K.conv1_weight_pack(w1), b1)
-            col1 = a1 = xb  # placeholders (the backward regenerates its operands from xb)
-        else:
-            w1p = K.conv_weight_pack(w1, 3, 5, 5, K1PAD)
-            col1 = K.im2col(xb, 5, 5, K1PAD, nchw=True)                       # [B*784, 80]
-            a1 = K.gemm_bf16(col1, w1p, bias=b1, act="relu", tile_n=64)       # [B*784, 64] == NHWC [B,28,28,64]
-            p1, idx1 = K.maxpool_fwd(a1.view(B, 28, 28, 64), 3)               # [B,9,9,64]
-        if conv2_mode == "legacy":
-            col2 = K.im2col(p1, 5, 5, 1600, nchw=False)                       # [B*25, 1600]
-            a2 = K.gemm_bf16(col2, w2p, bias=b2, act="relu", tile_n=64)       # [B*25, 64] == [B,5,5,64]
-            p2, idx2 = K.maxpool_fwd(a2.view(B, 5, 5, 64), 3)                 # [B,1,1,64]
-        else:
-            # rows ordered with the 3x3 pixels that pool2 reads first; "dense" still evaluates the
-            # convolution at all 25 pixels (as the reference does), "pooled" only at those 9
-            col2 = K.im2col_winfirst(p1, 5, 5, 3, only_window=(conv2_mode == "pooled"))
-            a2 = K.gemm_bf16(col2, w2p, bias=b2, act="relu", tile_n=64)
-            p2, idx2 = K.maxpool_fwd(a2[:B * 9].view(B, 3, 3, 64), 3)         # [B,1,1,64]
-        hidden = torch.empty((B, 100), device=dev, dtype=torch.float32)
-        logp = torch.empty((B, 10), device=dev, dtype=torch.float32)
-        loss = torch.empty((), device=dev, dtype=torch.float32)
-        h = K.HeadArgs()
-        h.p2, h.w1, h.b1, h.w2, h.b2 = p2.data_ptr(), fw1.data_ptr(), fb1.data_ptr(), fw2.data_ptr(), fb2.data_ptr()
-        tgt = target.to(torch.int64).contiguous()
-        h.target = tgt.data_ptr()
-        h.B, h.D, h.H, h.NC = B, 64, 100, 10
-        h.dropout_p, h.seed = float(p_drop), int(seed) & 0xFFFFFFFF
-        h.hidden, h.logp, h.loss = hidden.data_ptr(), logp.data_ptr(), loss.data_ptr()
-        ws = K.head_workspace(dev)
-        _native.check(_native.lib().tadnn_head_forward(C.byref(h), C.c_void_p(ws.data_ptr()),
-                                                       C.c_void_p(_native.stream_ptr())), "tadnn_head_forward")
-        ctx.save_for_backward(col1, a1, p1, idx1, col2, a2, p2, idx2, hidden, logp, tgt, w2p, fw1, fb1, fw2, fb2)
-        ctx.p_drop, ctx.seed, ctx.B = float(p_drop), int(seed) & 0xFFFFFFFF, B
-        ctx.fused_conv1 = bool(fused_conv1)
-        ctx.conv2_mode = conv2_mode
+        loss, logp, sv = _cnn_forward(x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fused_conv1, conv2_mode)
+        ctx.sv = sv
         ctx.mark_non_differentiable(logp)
         return loss, logp
 
     @staticmethod
     def backward(ctx, gloss, _glogp):
-        from ..ops import cnn as K
-        col1, a1, p1, idx1, col2, a2, p2, idx2, hidden, logp, tgt, w2p, fw1, fb1, fw2, fb2 = ctx.saved_tensors
-        B, dev = ctx.B, p2.device
-        f32 = dict(device=dev, dtype=torch.float32)
-        gfw1, gfb1 = torch.zeros((100, 64), **f32), torch.zeros(100, **f32)
-        gfw2, gfb2 = torch.zeros((10, 100), **f32), torch.zeros(10, **f32)
-        gw1, gb1 = torch.zeros((64, 75), **f32), torch.zeros(64, **f32)
-        gw2, gb2 = torch.zeros((64, 1600), **f32), torch.zeros(64, **f32)
-        dp2 = torch.empty((B, 1, 1, 64), device=dev, dtype=torch.bfloat16)
-        h = K.HeadArgs()
-        h.p2, h.w1, h.b1, h.w2, h.b2 = p2.data_ptr(), fw1.data_ptr(), fb1.data_ptr(), fw2.data_ptr(), fb2.data_ptr()
-        h.target = tgt.data_ptr()
-        h.B, h.D, h.H, h.NC = B, 64, 100, 10
-        h.dropout_p, h.seed = ctx.p_drop, ctx.seed
-        h.hidden, h.logp = hidden.data_ptr(), logp.data_ptr()
-        h.gw1, h.gb1, h.gw2, h.gb2 = gfw1.data_ptr(), gfb1.data_ptr(), gfw2.data_ptr(), gfb2.data_ptr()
-        h.dp2 = dp2.data_ptr()
-        h.grad_scale = 1.0
-        gl = gloss.to(device=dev, dtype=torch.float32).contiguous()
-        h.grad_scale_dev = gl.data_ptr()  # upstream dLoss stays on the device: no host sync
-        _native.check(_native.lib().tadnn_head_backward(C.byref(h), C.c_void_p(_native.stream_ptr())), "tadnn_head_backward")
-        K.colsum_relu_mask(dp2, p2, gb2)
-        if ctx.conv2_mode == "legacy":
-            # pool/relu backward into a2's storage, wgrad (split-K), dgrad into col2's storage, col2im
-            da2 = K.maxpool_relu_bwd(dp2, p2, idx2, 5, 5, 3, out=a2.view(B, 5, 5, 64)).view(B * 25, 64)
-            dw2p = K.gemm_bf16(da2, col2, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
-                               split_k=K.auto_split_k(64, 1600, B * 25))
-            K.conv_wgrad_unpack(dw2p, gw2, 64, 5, 5)
-            dcol2 = K.gemm_bf16(da2, w2p, b_mn_major=True, out=col2)
-            dp1 = K.col2im(dcol2, B, 64, 9, 9, 5, 5)
-        else:
-            # d(conv2 out) is exactly zero outside the 3x3 pooled window: wgrad over those 9 pixels'
-            # patches, and the transposed convolution as ONE dense GEMM against the Toeplitz-expanded
-            # weights ([B, 9*64] x [9*64, 7*7*64]) instead of a 25-tap dgrad GEMM + col2im
-            da2w = K.maxpool_relu_bwd(dp2, p2, idx2, 3, 3, 3).view(B * 9, 64)
-            dw2p = K.gemm_bf16(da2w, col2[:B * 9], a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
-                               split_k=K.auto_split_k(64, 1600, B * 9))
-            K.conv_wgrad_unpack(dw2p, gw2, 64, 5, 5)
-            T = K.conv_toeplitz_pack(w2p, 64, 64, 5, 5, 3)                    # [7*7*64, 9*64]
-            dp1c = K.gemm_bf16(da2w.view(B, 576), T)                          # [B, 7*7*64]
-            dp1 = K.expand_corner(dp1c.view(B, 7, 7, 64), 9, 9)
-        # conv1 (no dgrad: the image needs no gradient)
-        K.colsum_relu_mask(dp1, p1, gb1)
-        if ctx.fused_conv1:
-            K.conv1_pool_backward(col1, dp1, p1, idx1, gw1)   # col1 is the bf16 input image here
-        else:
-            da1 = K.maxpool_relu_bwd(dp1, p1, idx1, 28, 28, 3, out=a1.view(B, 28, 28, 64)).view(B * 784, 64)
-            dw1p = K.gemm_bf16(da1, col1, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
-                               split_k=K.auto_split_k(64, K1PAD, B * 784, 128), tile_n=128)
-            K.conv_wgrad_unpack(dw1p, gw1, 3, 5, 5)
-        grads = [gw1, gb1, gw2, gb2, gfw1, gfb1, gfw2, gfb2]
+        sv = ctx.sv
+        dev = sv["p2"].device
+        sizes = [(64, 75), (64,), (64, 1600), (64,), (100, 64), (100,), (10, 100), (10,)]
+        flat = torch.zeros(sum(math.prod(s) for s in sizes), device=dev, dtype=torch.float32)  # one fill
+        grads, off = [], 0
+        for sz in sizes:
+            n = math.prod(sz)
+            grads.append(flat[off:off + n].view(sz))
+            off += n
+        _cnn_backward(sv, *grads, gloss=gloss)
+        ctx.sv = None
         return (None, None, *grads, None, None, None, None)
 
 
@@ -198,6 +223,32 @@ class CifarCNN(torch.nn.Module, T7Protocol):
 
     def loss(self, x, target):
         return self.loss_and_logp(x, target)[0]
+
+    def _plist(self):
+        return [self.conv1_weight, self.conv1_bias, self.conv2_weight, self.conv2_bias,
+                self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias]
+
+    def forward_backward(self, x: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        """Torch7-style explicit step (``model:forward`` + ``model:backward``): runs the fused
+        forward and backward kernels without autograd and ACCUMULATES the gradients into
+        ``param.grad`` (= gradWeight/gradBias).  Returns the loss tensor (device).  The caller runs
+        the synchronisation hook (``model._tadnn_sync.after_backward(model)``), as the hooked
+        ``Sequential:backward`` does (datamodule.lua:96-110)."""
+        if not self._native_ok(x):
+            loss = self.loss(x, target)
+            loss.backward()
+            return loss.detach()
+        ps = self._plist()
+        for p in ps:
+            if p.grad is None:
+                p.grad = torch.zeros_like(p)
+        self._step += 1
+        pd = self.dropout if self.training else 0.0
+        seed = (self._seed * 2654435761 + self._step * 40503) & 0xFFFFFFFF
+        with torch.no_grad():
+            loss, _logp, sv = _cnn_forward(x, target, *[p.data for p in ps], pd, seed, self.fused_conv1, self.conv2_mode)
+            _cnn_backward(sv, *[p.grad for p in ps])
+        return loss
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         """Log-probabilities ``[B, 10]`` (what the reference model outputs after LogSoftMax)."""

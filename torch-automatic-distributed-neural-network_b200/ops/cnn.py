@@ -135,9 +135,20 @@ def conv1_pool_forward(x: torch.Tensor, wp: torch.Tensor, bias: torch.Tensor):
 
 
 def conv1_pool_backward(x, dp1, p1, idx1, grad_weight):
-    _native.check(_native.lib().tadnn_conv1_pool_backward(_p(x), _p(dp1), _p(p1), _p(idx1), _p(grad_weight),
-                                                          x.shape[0], _s()), "tadnn_conv1_pool_backward")
+    """dp1: [B, h, w, 64] with h, w <= 9 — the (possibly compact, top-left) pooled gradient."""
+    _native.check(_native.lib().tadnn_conv1_pool_backward(_p(x), _p(dp1), int(dp1.shape[1]), int(dp1.shape[2]), _p(p1),
+                                                          _p(idx1), _p(grad_weight), x.shape[0], _s()),
+                  "tadnn_conv1_pool_backward")
     return grad_weight
+
+
+def colsum_relu_mask_corner(dy: torch.Tensor, y: torch.Tensor, out: torch.Tensor):
+    """out[c] += sum dy * (y > 0) where dy is [B, FH, FW, C], the top-left corner of y [B, H, W, C]."""
+    B, FH, FW, Cc = dy.shape
+    assert dy.is_contiguous() and y.is_contiguous() and y.shape[0] == B and y.shape[3] == Cc
+    _native.check(_native.lib().tadnn_colsum_relu_mask_corner(_p(dy), _p(y), _p(out), B, int(y.shape[1]), int(y.shape[2]),
+                                                              FH, FW, Cc, _s()), "tadnn_colsum_relu_mask_corner")
+    return out
 
 
 _head_ws = {}
@@ -166,5 +177,5 @@ def auto_split_k(M: int, N: int, K: int, tile_n: int = 256) -> int:
     return max(1, min(kb, 148 // max(1, tiles)))
 
 
-__all__ = ["im2col_winfirst", "conv_toeplitz_pack", "expand_corner", "conv1_weight_pack", "conv1_pool_forward", "conv1_pool_backward", "im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "conv_weight_pack",
+__all__ = ["im2col_winfirst", "conv_toeplitz_pack", "expand_corner", "conv1_weight_pack", "conv1_pool_forward", "conv1_pool_backward", "im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "colsum_relu_mask_corner", "conv_weight_pack",
            "conv_wgrad_unpack", "head_workspace", "sgd_step", "auto_split_k", "HeadArgs", "gemm_bf16"]

@@ -57,8 +57,15 @@ class BatchTrainer:
 
     def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         """Returns the (device) loss tensor of this step; does not synchronise."""
-        loss = self._loss(x, y)
-        loss.backward()  # parallelize()'s hook synchronises the model in here
+        if self.criterion is None and self._cuda and hasattr(self.model, "forward_backward"):
+            # explicit forward+backward (no autograd), then the hooked-backward bookkeeping
+            loss = self.model.forward_backward(x, y)
+            st = getattr(self.model, "_tadnn_sync", None)
+            if st is not None:
+                st.after_backward(self.model)
+        else:
+            loss = self._loss(x, y)
+            loss.backward()  # parallelize()'s hook synchronises the model in here
         self._sgd()
         self.steps += 1
         return loss.detach()

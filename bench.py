@@ -32,8 +32,8 @@ MODEL = "cifar_example CNN (conv5x5x64-relu-pool3, conv5x5x64-relu-pool3, fc64x1
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=100)
-    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=500)
+    ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="tadnn", choices=["tadnn", "reference", "baseline"])
     ap.add_argument("--batch-per-gpu", type=int, default=4096)
     ap.add_argument("--pool-batches", type=int, default=8,

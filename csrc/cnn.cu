@@ -136,6 +136,37 @@ __global__ void im2col_nhwc_winfirst_kernel(const uint4* __restrict__ x, uint4* 
   }
 }
 
+// Compile-time specialisation for the example's second conv (9x9x64 -> 5x5, 5x5 taps, window 3):
+// every div/mod folds to a multiply-shift.
+template <int H, int W, int C8, int KH, int KW, int WIN>
+__global__ void __launch_bounds__(256) im2col_nhwc_winfirst_fixed_kernel(const uint4* __restrict__ x, uint4* __restrict__ col, int B,
+                                                                          int only_window) {
+  constexpr int OH = H - KH + 1, OW = W - KW + 1, NWIN = WIN * WIN, NREST = OH * OW - NWIN, TOP = OW - WIN;
+  constexpr int KP8 = KH * KW * C8;
+  const int npix = only_window ? NWIN : OH * OW;
+  const long long total = static_cast<long long>(B) * npix * KP8;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int k8 = static_cast<int>(i % KP8);           // (tap, c8)
+    const long long t = i / KP8;
+    const int pix = static_cast<int>(t % npix);
+    const int b = static_cast<int>(t / npix);
+    const int c8 = k8 % C8, tap = k8 / C8, kw = tap % KW, kh = tap / KW;
+    int oy, ox;
+    long long row;
+    if (pix < NWIN) {
+      oy = pix / WIN; ox = pix % WIN;
+      row = static_cast<long long>(b) * NWIN + pix;
+    } else {
+      int r = pix - NWIN;
+      if (r < WIN * TOP) { oy = r / TOP; ox = WIN + r % TOP; }
+      else { r -= WIN * TOP; oy = WIN + r / OW; ox = r % OW; }
+      row = static_cast<long long>(B) * NWIN + static_cast<long long>(b) * NREST + (pix - NWIN);
+    }
+    col[row * KP8 + k8] = x[((static_cast<long long>(b) * H + oy + kh) * W + ox + kw) * C8 + c8];
+  }
+}
+
 // ---- Toeplitz expansion of the packed conv weights for the transposed convolution ----------------
 // The gradient of the conv output is non-zero only inside the win x win pooled window, so
 //   dX[b, y, x, c] = sum_{(oy,ox) in window} sum_co dY[b,oy,ox,co] * Wp[co, ((y-oy)*KW + (x-ox))*C + c]
@@ -667,6 +698,12 @@ extern "C" int tadnn_im2col_winfirst(const void* x, void* col, int B, int C, int
   TADNN_REQUIRE(B > 0 && OH > 0 && OW > 0 && C % 8 == 0, "im2col_winfirst: bad shape (C must be a multiple of 8)");
   TADNN_REQUIRE(win >= 1 && win <= OH && win <= OW, "im2col_winfirst: window %d does not fit %dx%d", win, OH, OW);
   const long long total = static_cast<long long>(B) * (only_window ? win * win : OH * OW) * KH * KW * (C / 8);
+  if (C == 64 && H == 9 && W == 9 && KH == 5 && KW == 5 && win == 3) {
+    im2col_nhwc_winfirst_fixed_kernel<9, 9, 8, 5, 5, 3><<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+        static_cast<const uint4*>(x), static_cast<uint4*>(col), B, only_window);
+    TADNN_LAUNCH_CHECK("im2col_nhwc_winfirst");
+    return 0;
+  }
   im2col_nhwc_winfirst_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(
       static_cast<const uint4*>(x), static_cast<uint4*>(col), B, H, W, C / 8, KH, KW, OH, OW, C * KH * KW / 8, win, only_window);
   TADNN_LAUNCH_CHECK("im2col_nhwc_winfirst");

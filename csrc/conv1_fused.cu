@@ -66,15 +66,15 @@ __device__ __forceinline__ void stage_images_async(const __nv_bfloat16* __restri
 // k 64..79 in its chunks 0..1.  Each (kh, c) run of 5 contiguous input pixels is fetched as three
 // aligned 32-bit words and funnel-shifted by the pixel's column parity; the 2-byte shuffles into
 // patch order are compile-time byte permutes.
-__device__ __forceinline__ void build_patch_row(const uint32_t* __restrict__ img_words, long long total_win, int tile, int b0,
+__device__ __forceinline__ void build_patch_row(const uint32_t* __restrict__ img_words, int total_win, int tile, int b0,
                                                 int r, uint8_t* blk0, uint8_t* blk1) {
-  const long long win = static_cast<long long>(tile) * kWinPerTile + r / 9;
+  const int win = tile * kWinPerTile + r / 9;
   const bool valid = (r < kWinPerTile * 9) && (win < total_win);
   uint32_t out[kKpad / 2];
   if (valid) {
     const int pos = r % 9;
-    const int b = static_cast<int>(win / kWinPerImg);
-    const int wi = static_cast<int>(win % kWinPerImg);
+    const int b = win / kWinPerImg;
+    const int wi = win - b * kWinPerImg;
     const int oy = (wi / kPW) * kPool + pos / 3;
     const int ox = (wi % kPW) * kPool + pos % 3;
     const uint32_t* base = img_words + (b - b0) * (kC * kH * kW / 2) + oy * (kW / 2) + (ox >> 1);
@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1_fwd_kernel(const Conv1Ar
                            &img_full[grp][buf ^ 1]);
       mbar_wait(&img_full[grp][buf], (n >> 1) & 1);
       mbar_wait(&a_empty[grp], (n & 1) ^ 1);
-      build_patch_row(reinterpret_cast<const uint32_t*>(img + buf * 2 * kImgBytes), total_win, static_cast<int>(t), b0, r, b0p,
+      build_patch_row(reinterpret_cast<const uint32_t*>(img + buf * 2 * kImgBytes), static_cast<int>(total_win), static_cast<int>(t), b0, r, b0p,
                       b0p + kBlockBytes);
       fence_proxy_async_smem();
       mbar_arrive(&a_full[grp]);
@@ -296,6 +296,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1_fwd_kernel(const Conv1Ar
 // smem: A[2] x (block0 + block1) | G[2] x 16 KB
 constexpr int kBwdSmem = 2 * 2 * kBlockBytes + 2 * kBlockBytes + 2 * kImgStageBytes + 1024;
 
+template <bool COMPACT>
 __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
@@ -371,7 +372,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args 
                            &img_full[grp][buf ^ 1]);
       mbar_wait(&img_full[grp][buf], (n >> 1) & 1);
       mbar_wait(&ab_empty[grp], (n & 1) ^ 1);
-      build_patch_row(reinterpret_cast<const uint32_t*>(img + buf * 2 * kImgBytes), total_win, static_cast<int>(t), b0, r, b0p,
+      build_patch_row(reinterpret_cast<const uint32_t*>(img + buf * 2 * kImgBytes), static_cast<int>(total_win), static_cast<int>(t), b0, r, b0p,
                       b0p + kBlockBytes);
       fence_proxy_async_smem();
       mbar_arrive(&ab_full[grp]);
@@ -387,12 +388,17 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args 
       const long long win = t * kWinPerTile + wl;
       ok = (wl < kWinPerTile) && (t < num_tiles) && (win < total_win);
       if (ok) {
-        const int b = static_cast<int>(win / kWinPerImg), wi = static_cast<int>(win % kWinPerImg);
-        const int py = wi / kPW, px = wi % kPW;
-        ok = (py < a.dph) && (px < a.dpw);  // the pooled gradient is zero outside its stored corner
-        if (ok) dv = __ldg(reinterpret_cast<const uint4*>(a.dp1 + ((static_cast<long long>(b) * a.dph + py) * a.dpw + px) * kO + j * 8));
-      }
-      if (ok) {
+        if (!COMPACT) {
+          dv = __ldg(reinterpret_cast<const uint4*>(a.dp1 + win * kO + j * 8));
+        } else {
+          // compact corner [B, dph, dpw, 64]: zero outside
+          const int w32 = static_cast<int>(win);  // B*81 < 2^31 is checked on the host; 32-bit division is cheap
+          const int b = w32 / kWinPerImg, wi = w32 - b * kWinPerImg;
+          const int py = wi / kPW, px = wi - py * kPW;
+          dv = make_uint4(0, 0, 0, 0);
+          if (py < a.dph && px < a.dpw)
+            dv = __ldg(reinterpret_cast<const uint4*>(a.dp1 + ((static_cast<long long>(b) * a.dph + py) * a.dpw + px) * kO + j * 8));
+        }
         pv = __ldg(reinterpret_cast<const uint4*>(a.p1 + win * kO + j * 8));
         iv = __ldg(reinterpret_cast<const uint2*>(a.idx1 + win * kO + j * 8));
       }
@@ -489,7 +495,7 @@ extern "C" int tadnn_conv1_weight_pack(const float* w, void* wp, tadnn_stream_t 
 
 extern "C" int tadnn_conv1_pool_forward(const void* x, const void* w_packed, const float* bias, void* p1, void* idx1, int B,
                                         tadnn_stream_t stream) {
-  TADNN_REQUIRE(B > 0, "conv1_pool_forward: empty batch");
+  TADNN_REQUIRE(B > 0 && B <= 20000000, "conv1_pool_forward: batch %d out of range", B);
   TADNN_REQUIRE(((reinterpret_cast<uintptr_t>(w_packed) | reinterpret_cast<uintptr_t>(p1)) & 15) == 0, "conv1_pool_forward: operands must be 16-byte aligned");
   static bool attr = false;
   if (!attr) { TADNN_CHECK_CUDA(cudaFuncSetAttribute(conv1_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem)); attr = true; }
@@ -506,12 +512,16 @@ extern "C" int tadnn_conv1_pool_forward(const void* x, const void* w_packed, con
 
 extern "C" int tadnn_conv1_pool_backward(const void* x, const void* dp1, int dp1_h, int dp1_w, const void* p1, const void* idx1,
                                          float* grad_weight, int B, tadnn_stream_t stream) {
-  TADNN_REQUIRE(B > 0, "conv1_pool_backward: empty batch");
+  TADNN_REQUIRE(B > 0 && B <= 20000000, "conv1_pool_backward: batch %d out of range", B);
   TADNN_REQUIRE(dp1_h >= 1 && dp1_h <= kPH && dp1_w >= 1 && dp1_w <= kPW, "conv1_pool_backward: dp1 extent %dx%d out of range", dp1_h, dp1_w);
   TADNN_REQUIRE(((reinterpret_cast<uintptr_t>(dp1) | reinterpret_cast<uintptr_t>(p1) | reinterpret_cast<uintptr_t>(idx1)) & 15) == 0,
                 "conv1_pool_backward: operands must be 16-byte aligned");
   static bool attr = false;
-  if (!attr) { TADNN_CHECK_CUDA(cudaFuncSetAttribute(conv1_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem)); attr = true; }
+  if (!attr) {
+    TADNN_CHECK_CUDA(cudaFuncSetAttribute(conv1_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
+    TADNN_CHECK_CUDA(cudaFuncSetAttribute(conv1_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
+    attr = true;
+  }
   Conv1Args a;
   memset(&a, 0, sizeof(a));
   a.x = static_cast<const __nv_bfloat16*>(x); a.dp1 = static_cast<const __nv_bfloat16*>(dp1);
@@ -520,7 +530,8 @@ extern "C" int tadnn_conv1_pool_backward(const void* x, const void* dp1, int dp1
   a.gw = grad_weight; a.B = B; a.dph = dp1_h; a.dpw = dp1_w;
   const long long tiles = (static_cast<long long>(B) * kWinPerImg + kWinPerTile - 1) / kWinPerTile;
   const int grid = tiles < sm_count() ? static_cast<int>(tiles) : sm_count();
-  conv1_bwd_kernel<<<grid, kThreads, kBwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
+  if (dp1_h == kPH && dp1_w == kPW) conv1_bwd_kernel<false><<<grid, kThreads, kBwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
+  else conv1_bwd_kernel<true><<<grid, kThreads, kBwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
   TADNN_LAUNCH_CHECK("conv1_pool_bwd_tcgen05");
   return 0;
 }

@@ -115,8 +115,7 @@ def _cnn_backward(sv, gw1, gb1, gw2, gb2, gfw1, gfb1, gfw2, gfb2, gloss=None):
         T = K.conv_toeplitz_pack(w2p, 64, 64, 5, 5, 3)                    # [7*7*64, 9*64]
         dp1 = K.gemm_bf16(da2w.view(B, 576), T).view(B, 7, 7, 64)        # compact corner of [B,9,9,64]
         K.colsum_relu_mask_corner(dp1, p1, gb1)
-        if not sv["fused_conv1"]:
-            dp1 = K.expand_corner(dp1, 9, 9)
+        dp1 = K.expand_corner(dp1, 9, 9)  # (the fused conv1 backward also accepts the compact corner; full is faster)
     # conv1 (no dgrad: the image needs no gradient)
     if sv["fused_conv1"]:
         K.conv1_pool_backward(sv["xb"], dp1, p1, idx1, gw1)

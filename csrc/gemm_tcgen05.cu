@@ -63,6 +63,7 @@ struct DevArgs {
   int rs_width;   // >0: reduce-scatter push: column block q = col/rs_width goes ONLY to push map q
   const __nv_bfloat16* aux;  // optional [M, ld_aux] bf16; epilogue multiplies by (1 - aux^2) (tanh backward)
   int ld_aux;
+  int group_m;   // m-blocks per rasterisation group
   int n_rotate;  // tile column order starts at this n-block (reduce-scatter push: de-synchronises the ranks' targets)
 };
 
@@ -128,6 +129,19 @@ __device__ __forceinline__ void store_row32(void* base, int ld, int c_fp32, int 
   }
 }
 
+// Tile rasterisation: m-blocks are walked in groups of `group_m` (m fastest inside a group, then n),
+// so that the ~148 tiles in flight form a roughly square patch of the output and re-use each
+// other's A and B panels out of L2 (a plain m-fastest sweep streams all of A once per ~2 n-blocks).
+__device__ __forceinline__ void decode_tile(int tile, int num_m, int num_n, int group_m, int n_rotate, int& m_blk, int& n_blk) {
+  const int per_group = group_m * num_n;
+  const int g = tile / per_group;
+  const int first_m = g * group_m;
+  const int gsz = min(num_m - first_m, group_m);
+  const int in_g = tile - g * per_group;
+  m_blk = first_m + in_g % gsz;
+  n_blk = (in_g / gsz + n_rotate) % num_n;
+}
+
 template <bool A_MN, bool B_MN, int BN, bool AUX>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
@@ -185,8 +199,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
       for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
         const int split = w % splits;
         const int tile = w / splits;
-        const int m_blk = tile % num_m;
-        const int n_blk = (tile / num_m + p.n_rotate) % num_n;
+        int m_blk, n_blk;
+        decode_tile(tile, num_m, num_n, p.group_m, p.n_rotate, m_blk, n_blk);
         const int kb0 = split * kb_per_split;
         const int kb1 = min(num_kb, kb0 + kb_per_split);
         for (int kb = kb0; kb < kb1; ++kb) {
@@ -274,8 +288,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
       int buf = 0;
       for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
         const int tile = w / splits;
-        const int m_blk = tile % num_m;
-        const int n_blk = (tile / num_m + p.n_rotate) % num_n;
+        int m_blk, n_blk;
+        decode_tile(tile, num_m, num_n, p.group_m, p.n_rotate, m_blk, n_blk);
         mbar_wait(&tmem_full_bar[acc], acc_phase);
         tc_fence_after_sync();
         const int row0 = m_blk * BM + wg * 32;
@@ -361,8 +375,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     } else {
     for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
       const int tile = w / splits;
-      const int m_blk = tile % num_m;
-      const int n_blk = (tile / num_m + p.n_rotate) % num_n;
+      int m_blk, n_blk;
+      decode_tile(tile, num_m, num_n, p.group_m, p.n_rotate, m_blk, n_blk);
       mbar_wait(&tmem_full_bar[acc], acc_phase);
       tc_fence_after_sync();
       const int row = m_blk * BM + wg * 32 + lane;
@@ -536,6 +550,12 @@ extern "C" int tadnn_gemm_bf16(const tadnn_gemm_args* a, tadnn_stream_t stream_)
   d.push_ldc = a->push_ldc; d.push_col_offset = a->push_col_offset;
   d.rs_width = a->rs_width;
   d.n_rotate = a->n_rotate > 0 ? a->n_rotate : 0;
+  {
+    // group height so that group_m x (148 / group_m) tiles in flight are about square in bytes
+    // (an n-block is BN=256 wide, an m-block 128 tall): 16 x 9 for big problems
+    const int num_m = ceil_div(a->M, BM);
+    d.group_m = a->rs_width > 0 ? num_m : (num_m < 16 ? num_m : 16);
+  }
   d.aux = static_cast<const __nv_bfloat16*>(a->aux_tanh_out);
   d.ld_aux = a->ld_aux;
   if (a->rs_width > 0) {

@@ -329,6 +329,52 @@ __global__ void __launch_bounds__(512) reduce_slots_kernel(CommDev c, size_t slo
   block_barrier(c, channel);  // slots may be overwritten / pushed results are visible
 }
 
+// Slab-major staging (GEMM rs_slab_major): slot q holds ceil(rows/32) x (width/64) slabs of 4 KB, each a
+// 32-row x 64-column tile in the SWIZZLE_128B order of the GEMM's staging buffer (16-byte chunk j of
+// slab row rr sits at chunk position j ^ (rr & 7)).  Threads walk the slots linearly (fully
+// coalesced) and undo the swizzle when they write the row-major result.
+__global__ void __launch_bounds__(512) reduce_slots_slab_kernel(CommDev c, size_t slots_off, int rows, int width8, float scale,
+                                                                const float* bias, int act, __nv_bfloat16* out_local,
+                                                                size_t out_pitch, size_t push_off, int do_push, int channel) {
+  const int rank = my_rank(c);
+  const int slabs_per_rowblk = width8 >> 3;                       // width / 64
+  const size_t rowblks = (static_cast<size_t>(rows) + 31) >> 5;
+  const size_t total = rowblks * slabs_per_rowblk * 256;           // uint4 units per slot
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const uint4* slots = reinterpret_cast<const uint4*>(c.heap[rank] + slots_off);
+  block_barrier(c, channel);
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const size_t slab = i >> 8;
+    const int within = static_cast<int>(i & 255), rr = within >> 3, pos = within & 7;
+    const int j = pos ^ (rr & 7);
+    const size_t row = (slab / slabs_per_rowblk) * 32 + rr;
+    const size_t c8 = (slab % slabs_per_rowblk) * 8 + j;
+    if (row >= static_cast<size_t>(rows)) continue;
+    float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int q = 0; q < kMaxRanks; ++q)
+      if (q < c.world) Vec<1>::add(a, slots[q * total + i]);
+    float v[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      float x = a[e] * scale;
+      if (bias != nullptr) x += bias[(static_cast<size_t>(rank) * width8 + c8) * 8 + e];
+      if (act == 1) x = tanh_f32(x);
+      else if (act == 2) x = fmaxf(x, 0.f);
+      v[e] = x;
+    }
+    const uint4 o = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+    if (out_local != nullptr) *reinterpret_cast<uint4*>(out_local + row * out_pitch + c8 * 8) = o;
+    if (do_push) {
+      const size_t off = push_off + (row * (static_cast<size_t>(width8) * c.world) + static_cast<size_t>(rank) * width8 + c8) * 16;
+#pragma unroll
+      for (int q = 0; q < kMaxRanks; ++q)
+        if (q < c.world) st_peer16(c.heap[q] + off, o);
+    }
+  }
+  block_barrier(c, channel);
+}
+
 int pick_blocks(size_t work_items_per_thread_1, int max_blocks, int cap_default) {
   int cap = max_blocks > 0 ? max_blocks : cap_default;
   if (cap > kMaxBlocks) cap = kMaxBlocks;
@@ -587,18 +633,25 @@ extern "C" int tadnn_reduce_scatter_cols(tadnn_comm* c, unsigned long long off_b
 
 extern "C" int tadnn_reduce_slots(tadnn_comm* c, unsigned long long slots_off, int rows, int width, float scale,
                                   const float* bias, int act, void* out_local, unsigned long long out_pitch,
-                                  unsigned long long push_off, int do_push, int max_blocks, int channel,
+                                  unsigned long long push_off, int do_push, int slab_major, int max_blocks, int channel,
                                   tadnn_stream_t stream) {
   if (int rc = validate(c, channel, "reduce_slots")) return rc;
   TADNN_REQUIRE(rows > 0 && width > 0 && width % 8 == 0, "reduce_slots: width must be a positive multiple of 8");
   TADNN_REQUIRE(slots_off % 16 == 0 && (!do_push || push_off % 16 == 0), "reduce_slots: offsets must be 16-byte aligned");
-  TADNN_REQUIRE(slots_off + 2ull * rows * width * c->world <= c->heap_bytes, "reduce_slots: slots exceed the heap");
+  const unsigned long long rows_pad = slab_major ? ((static_cast<unsigned long long>(rows) + 31) / 32) * 32 : rows;
+  TADNN_REQUIRE(!slab_major || width % 64 == 0, "reduce_slots: slab-major staging needs width %% 64 == 0");
+  TADNN_REQUIRE(slots_off + 2ull * rows_pad * width * c->world <= c->heap_bytes, "reduce_slots: slots exceed the heap");
   TADNN_REQUIRE(out_local == nullptr || ((reinterpret_cast<uintptr_t>(out_local) & 15) == 0 && out_pitch % 8 == 0),
                 "reduce_slots: out_local must be 16-byte aligned with a pitch multiple of 8");
   const int blocks = pick_blocks(static_cast<size_t>(rows) * (width / 8), max_blocks, 148);
-  reduce_slots_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(
-      c->dev, slots_off, rows, width / 8, scale, bias, act, static_cast<__nv_bfloat16*>(out_local), out_pitch, push_off,
-      do_push, channel);
+  if (slab_major)
+    reduce_slots_slab_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(
+        c->dev, slots_off, rows, width / 8, scale, bias, act, static_cast<__nv_bfloat16*>(out_local), out_pitch, push_off,
+        do_push, channel);
+  else
+    reduce_slots_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(
+        c->dev, slots_off, rows, width / 8, scale, bias, act, static_cast<__nv_bfloat16*>(out_local), out_pitch, push_off,
+        do_push, channel);
   TADNN_LAUNCH_CHECK("reduce_slots");
   return 0;
 }

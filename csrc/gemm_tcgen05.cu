@@ -61,6 +61,7 @@ struct DevArgs {
   int push_col_offset;
   int tma_store;  // bf16 output through shared memory + cp.async.bulk.tensor stores
   int rs_width;   // >0: reduce-scatter push: column block q = col/rs_width goes ONLY to push map q
+  int rs_slab;    // rs push writes 4 KB slabs (32 rows x 64 cols, swizzled as staged) contiguously: slab-major staging
   const __nv_bfloat16* aux;  // optional [M, ld_aux] bf16; epilogue multiplies by (1 - aux^2) (tanh backward)
   int ld_aux;
   int group_m;   // m-blocks per rasterisation group
@@ -311,6 +312,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           __syncwarp();
           uint8_t* dst = stg + buf * 4096 + lane * 128;
           const int row = row0 + lane;
+
           const bool aux_ok = AUX && row < p.M;
           const __nv_bfloat16* aux_row = p.aux + static_cast<size_t>(row < p.M ? row : 0) * p.ld_aux + col0;
 #pragma unroll
@@ -349,7 +351,15 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           fence_proxy_async_smem();
           __syncwarp();
           if (lane == 0 && row0 < p.M) {
-            if (p.rs_width > 0) {
+            if (p.rs_width > 0 && p.rs_slab) {
+              // slab-major reduce-scatter push: the staged 32x64 slab (4 KB, still swizzled) goes as ONE
+              // contiguous bulk copy into our slot of the owner's staging buffer: 4 KB NVLink writes
+              // instead of 32 separate 128-byte rows.  reduce_slots undoes the swizzle.
+              const int q = col0 / p.rs_width;
+              const size_t slab = static_cast<size_t>(row0 >> 5) * (p.rs_width >> 6) + ((col0 - q * p.rs_width) >> 6);
+              uint8_t* dst = static_cast<uint8_t*>(p.push[q]) + slab * 4096;
+              asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], 4096;" ::"l"(dst), "r"(smem_u32(stg + buf * 4096)) : "memory");
+            } else if (p.rs_width > 0) {
               // reduce-scatter push: this 64-column slab belongs to rank q; store it into OUR slot
               // of q's staging buffer (peer memory over NVLink), nowhere else.
               const int q = col0 / p.rs_width;
@@ -549,6 +559,7 @@ extern "C" int tadnn_gemm_bf16(const tadnn_gemm_args* a, tadnn_stream_t stream_)
   for (int i = 0; i < a->n_push; ++i) d.push[i] = a->push[i];
   d.push_ldc = a->push_ldc; d.push_col_offset = a->push_col_offset;
   d.rs_width = a->rs_width;
+  d.rs_slab = a->rs_slab_major ? 1 : 0;
   d.n_rotate = a->n_rotate > 0 ? a->n_rotate : 0;
   {
     // group height so that group_m x (148 / group_m) tiles in flight are about square in bytes

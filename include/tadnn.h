@@ -76,6 +76,10 @@ typedef struct tadnn_gemm_args {
   /* Start the tile sweep at this n-block (wraps around).  With rs_width each rank passes a
    * different value so that the ranks never all push to the same owner at the same time. */
   int n_rotate;
+  /* With rs_width: store each 32-row x 64-column slab as one contiguous 4 KB block (slab-major
+   * staging, rows padded to a multiple of 32; slab s = (row/32)*(rs_width/64) + col/64, contents in
+   * the SWIZZLE_128B order of the staging tile) -- tadnn_reduce_slots(slab_major=1) reads it. */
+  int rs_slab_major;
 } tadnn_gemm_args;
 
 int tadnn_gemm_bf16(const tadnn_gemm_args* args, tadnn_stream_t stream);
@@ -170,8 +174,8 @@ int tadnn_reduce_scatter_cols(tadnn_comm* c, unsigned long long off_bytes, void*
  * following Tanh (nodemodule.lua:134). */
 int tadnn_reduce_slots(tadnn_comm* c, unsigned long long slots_off, int rows, int width, float scale,
                        const float* bias, int act, void* out_local, unsigned long long out_pitch,
-                       unsigned long long push_off, int do_push, int max_blocks, int channel,
-                       tadnn_stream_t stream);
+                       unsigned long long push_off, int do_push, int slab_major, int max_blocks,
+                       int channel, tadnn_stream_t stream);
 
 /* Emulated (single launch, no cross-launch waiting) variants for 1-GPU numerics tests on a
  * tadnn_comm_create_local() set: performs rank `as_rank`'s share of the math with all

@@ -31,7 +31,7 @@ class GemmArgs(C.Structure):
         ("accumulate", C.c_int), ("split_k", C.c_int),
         ("n_push", C.c_int), ("push", C.c_void_p * 8),
         ("push_ldc", C.c_int), ("push_col_offset", C.c_int),
-        ("tile_n", C.c_int), ("rs_width", C.c_int), ("aux_tanh_out", C.c_void_p), ("ld_aux", C.c_int), ("n_rotate", C.c_int),
+        ("tile_n", C.c_int), ("rs_width", C.c_int), ("aux_tanh_out", C.c_void_p), ("ld_aux", C.c_int), ("n_rotate", C.c_int), ("rs_slab_major", C.c_int),
     ]
 
 

@@ -21,7 +21,7 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False,
               act: str | None = None, alpha: float = 1.0, accumulate: bool = False,
               split_k: int = 0, push=None, push_col_offset: int = 0, push_ldc: int = 0,
               tile_n: int = 0, rs_width: int = 0, aux_tanh_out: torch.Tensor | None = None,
-              n_rotate: int = 0, stream=None) -> torch.Tensor:
+              n_rotate: int = 0, rs_slab_major: bool = False, stream=None) -> torch.Tensor:
     """out[M,N] = act(alpha * A·Bᵀ + bias).
 
     a: [M,K] (or [K,M] if a_mn_major), b: [N,K] (or [K,N] if b_mn_major); bf16, last dim
@@ -65,6 +65,7 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False,
     args.tile_n = int(tile_n)
     args.rs_width = int(rs_width)
     args.n_rotate = int(n_rotate)
+    args.rs_slab_major = int(rs_slab_major)
     if aux_tanh_out is not None:
         assert aux_tanh_out.dtype == torch.bfloat16 and aux_tanh_out.stride(1) == 1 and aux_tanh_out.shape == (M, N)
         args.aux_tanh_out, args.ld_aux = aux_tanh_out.data_ptr(), aux_tanh_out.stride(0)

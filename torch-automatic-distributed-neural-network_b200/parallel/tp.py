@@ -54,8 +54,11 @@ class _Plan:
         maxo = max(big) if big else 0
         allo = max(sizes[1:])
         allo_pad = (allo + 7) // 8 * 8
-        self.slots_off = ctx.alloc(2 * B * maxo) if maxo else 0      # [P][B][o/P] bf16 == B*o elements
+        self.Bpad = (B + 31) // 32 * 32
+        self.slots_off = ctx.alloc(2 * self.Bpad * maxo) if maxo else 0  # [P] slots of Bpad x o/P bf16 (slab-major)
         self.gfull_off = ctx.alloc(2 * B * allo_pad)                  # [B, o] bf16 (gathered grads / outputs)
+        self.gfull2_off = ctx.alloc(2 * B * allo_pad)                 # second buffer: the all-gather of layer l-1's
+        #                                                               gradient lands here while layer l's wgrad still reads the first
         self.small = ctx.empty((B * allo_pad,), torch.float32)        # small-layer partial sums (all-reduced in place)
 
 
@@ -84,7 +87,7 @@ class _Fn(torch.autograd.Function):
             wbs.append(wb)
             if o % (64 * P) == 0:
                 w = o // P
-                push = [sc.heap_ptrs[q] + plan.slots_off + r * B * w * 2 for q in range(P)]
+                push = [sc.heap_ptrs[q] + plan.slots_off + r * B * w * 2 for q in range(P)]  # slot r of rank q: [B, w]
                 # every rank starts its tile sweep at a different owner's column block: at any moment the
                 # P ranks push to P different destinations instead of all hammering rank 0's ingress
                 nblk = (o + 255) // 256
@@ -92,7 +95,7 @@ class _Fn(torch.autograd.Function):
                 nxt = torch.empty((B, w), device=x.device, dtype=torch.bfloat16)
                 _native.check(lib.tadnn_reduce_slots(
                     sc.handle, C.c_ulonglong(plan.slots_off), B, w, C.c_float(1.0), None, 0 if last else 1,
-                    C.c_void_p(nxt.data_ptr()), C.c_ulonglong(w), C.c_ulonglong(plan.gfull_off), int(last), 0,
+                    C.c_void_p(nxt.data_ptr()), C.c_ulonglong(w), C.c_ulonglong(plan.gfull_off), int(last), 0, 0,
                     _symm.CH_TP, st), "tadnn_reduce_slots")
                 if last:
                     out = sc.tensor(plan.gfull_off, (B, o), torch.bfloat16).float()
@@ -135,11 +138,29 @@ class _Fn(torch.autograd.Function):
             g_full.zero_()
         g_full[:, :oL].copy_(gy)
         gx = None
+        offs = [plan.gfull_off, plan.gfull2_off]
+        cur = 0
+        side = mod._side_stream()
+        main = torch.cuda.current_stream()
         for l in range(L - 1, -1, -1):
             o, i_sh = mod.sizes[l + 1], mod.sizes[l] // P
             pitch = (o + 7) // 8 * 8
             gv = torch.as_strided(g_full, (B, o), (pitch, 1))  # [B, o] with row pitch `pitch`
             a = acts[l]
+            need_dx = l > 0 or ctx.needs_input_grad[1]
+            gathered = None
+            if need_dx:
+                # g'_r [B, i/P] = (g · W_r) (⊙ tanh' of the layer input if that input is a tanh output)
+                tn = 256 if i_sh >= 256 else 0  # measured: 256-wide tiles beat 128-wide ones even at 1.7 waves
+                gr = gemm_bf16(gv, wbs[l], b_mn_major=True, aux_tanh_out=a if l > 0 else None, tile_n=tn)
+                if P > 1:
+                    # all-gather of the slice gradients on a side stream, into the OTHER buffer, so that it
+                    # overlaps this layer's wgrad GEMM (the gather kernel needs few registers and co-resides)
+                    side.wait_event(main.record_event())
+                    gr.record_stream(side)
+                    with torch.cuda.stream(side):
+                        sc.allgather_cols_offset(gr, offs[cur ^ 1], _symm.CH_TP, side)
+                        gathered = side.record_event()
             # dW_r [o, i/P] = gᵀ · a_r   (A: g stored [K=B, M=o];  B: a_r stored [K=B, N=i/P])
             tile_n = 256 if i_sh > 128 else (128 if i_sh > 64 else 64)
             dW = gemm_bf16(gv, a, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
@@ -147,21 +168,16 @@ class _Fn(torch.autograd.Function):
             db = torch.zeros(o, device=dev, dtype=torch.float32)
             colsum_bf16(gv, db)
             grads[2 * l], grads[2 * l + 1] = dW, db
-            need_dx = l > 0 or ctx.needs_input_grad[1]
             if not need_dx:
                 break
-            # g'_r [B, i/P] = (g · W_r) (⊙ tanh' of the layer input if that input is a tanh output)
-            tn = 256 if ((B + 127) // 128) * ((i_sh + 255) // 256) >= 2 * 148 else 128  # fill the 148 SMs
-            gr = gemm_bf16(gv, wbs[l], b_mn_major=True, aux_tanh_out=a if l > 0 else None, tile_n=tn)
-            if l > 0 or P > 1:
-                w_prev = i_sh
-                if P > 1:
-                    sc.allgather_cols_offset(gr, plan.gfull_off, _symm.CH_TP)
-                    g_full = sc.tensor(plan.gfull_off, (B, w_prev * P), torch.bfloat16)
-                else:
-                    g_full = gr
+            if P > 1:
+                main.wait_event(gathered)
+                cur ^= 1
+                g_full = sc.tensor(offs[cur], (B, i_sh * P), torch.bfloat16)
+            else:
+                g_full = gr
             if l == 0:
-                gx = (g_full if P > 1 else gr).to(gy.dtype).clone()
+                gx = g_full.to(gy.dtype).clone()
         return (None, gx, *grads)
 
 
@@ -216,6 +232,12 @@ class FusedMPMLP(torch.nn.Module):
         if sc is None:
             raise _native.NativeError("FusedMPMLP needs the symmetric-memory context (mpi.start(True) on CUDA)")
         return sc
+
+    def _side_stream(self):
+        st = getattr(self, "_side", None)
+        if st is None:
+            st = self._side = torch.cuda.Stream()
+        return st
 
     def _plan(self, B: int) -> _Plan:
         p = self._plans.get(B)

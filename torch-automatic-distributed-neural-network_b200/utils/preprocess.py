@@ -1,0 +1,69 @@
+"""The example's dataset preprocessing (cifar_example/sgd-torchad_nn-cifar.lua:182-216): RGB -> YUV,
+local contrast normalisation of the Y channel with a 7-tap Gaussian neighbourhood
+(``nn.SpatialContrastiveNormalization(1, image.gaussian1D(7))``), global standardisation of U and V.
+
+Pure tensor arithmetic (runs on whatever device the data lives on); not on the training hot path.
+The reference divides U and V by the *negative* standard deviation (``-std_u``, ``-std_v``, lines
+195, 200, 213, 216 — SURVEY Q10); ``reference_sign=True`` reproduces that, the default uses +std.
+"""
+from __future__ import annotations
+
+import math
+
+import torch
+import torch.nn.functional as F
+
+
+def rgb2yuv(x: torch.Tensor) -> torch.Tensor:
+    """``image.rgb2yuv`` on ``[..., 3, H, W]``."""
+    r, g, b = x[..., 0, :, :], x[..., 1, :, :], x[..., 2, :, :]
+    y = 0.299 * r + 0.587 * g + 0.114 * b
+    u = -0.14713 * r - 0.28886 * g + 0.436 * b
+    v = 0.615 * r - 0.51499 * g - 0.10001 * b
+    return torch.stack([y, u, v], dim=-3)
+
+
+def gaussian1d(size: int = 7, sigma: float = 0.25, amplitude: float = 1.0) -> torch.Tensor:
+    """``image.gaussian1D(size)`` (sigma is relative to the size, Torch ``image`` convention)."""
+    center = size / 2.0 + 0.5
+    i = torch.arange(1, size + 1, dtype=torch.float64)
+    return (amplitude * torch.exp(-(((i - center) / (sigma * size)) ** 2) / 2)).float()
+
+
+def spatial_contrastive_normalization(y: torch.Tensor, kernel1d: torch.Tensor, threshold: float = 1e-4) -> torch.Tensor:
+    """``nn.SpatialContrastiveNormalization(1, kernel)`` on ``[N, 1, H, W]``: subtractive then divisive
+    normalisation with a separable, border-corrected neighbourhood average."""
+    k2 = torch.outer(kernel1d, kernel1d).to(y)
+    k2 = (k2 / k2.sum()).view(1, 1, *k2.shape)
+    pad = kernel1d.numel() // 2
+    ones = torch.ones_like(y[:1])
+    coef = F.conv2d(ones, k2, padding=pad)  # border correction
+    mean = F.conv2d(y, k2, padding=pad) / coef
+    centered = y - mean
+    std = torch.sqrt(F.conv2d(centered * centered, k2, padding=pad) / coef)
+    thr = torch.clamp(std.mean(dim=(1, 2, 3), keepdim=True), min=threshold)
+    return centered / torch.maximum(std, thr)
+
+
+def preprocess(train: torch.Tensor, test: torch.Tensor | None = None, reference_sign: bool = False):
+    """Returns preprocessed ``(train, test)`` (``test`` may be None).  U/V statistics come from the
+    training shard and are applied to the test set, as in the example."""
+    out = []
+    tr = rgb2yuv(train.float())
+    mean_u, std_u = tr[:, 1].mean(), tr[:, 1].std()
+    mean_v, std_v = tr[:, 2].mean(), tr[:, 2].std()
+    sign = -1.0 if reference_sign else 1.0
+    kernel = gaussian1d(7)
+    for x in (tr, rgb2yuv(test.float()) if test is not None else None):
+        if x is None:
+            out.append(None)
+            continue
+        y = spatial_contrastive_normalization(x[:, 0:1], kernel)
+        u = (x[:, 1:2] - mean_u) / (sign * std_u)
+        v = (x[:, 2:3] - mean_v) / (sign * std_v)
+        out.append(torch.cat([y, u, v], dim=1))
+    return out[0], out[1]
+
+
+__all__ = ["rgb2yuv", "gaussian1d", "spatial_contrastive_normalization", "preprocess"]
+assert math  # noqa: S101 (kept for readers comparing against the Lua formulas)

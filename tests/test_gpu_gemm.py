@@ -98,3 +98,50 @@ def test_gemm_perf_smoke():
     print(f"\n[gemm 8192^3] {ms:.3f} ms  {2 * M * N * K / ms / 1e9:.1f} TFLOP/s")
     ref = a[:256].float() @ b.float().t()
     assert (out[:256].float() - ref).abs().max().item() < 2.0
+
+
+def test_gemm_allgather_push_epilogue():
+    """n_push: every output tile is also stored to the push targets at a column offset (the fused
+    all-gather; on one GPU the "peers" are two local buffers)."""
+    from tadnn.ops.gemm import gemm_bf16
+    M, N, K, P, r = 300, 192, 256, 3, 1
+    a = torch.randn(M, K, device="cuda").bfloat16()
+    b = torch.randn(N, K, device="cuda").bfloat16()
+    bias = torch.randn(N, device="cuda")
+    peers = [torch.zeros(M, P * N, device="cuda", dtype=torch.bfloat16) for _ in range(2)]
+    out = gemm_bf16(a, b, bias=bias, act="tanh", alpha=0.05, push=[p.data_ptr() for p in peers], push_ldc=P * N,
+                    push_col_offset=r * N)
+    torch.cuda.synchronize()
+    ref = torch.tanh(0.05 * (a.float() @ b.float().t()) + bias)
+    assert (out.float() - ref).abs().max().item() < 2e-2
+    for p in peers:
+        assert torch.equal(p[:, r * N:(r + 1) * N], out)
+        assert float(p[:, :r * N].abs().sum()) == 0 and float(p[:, (r + 1) * N:].abs().sum()) == 0
+
+
+def test_gemm_reduce_scatter_push_epilogue():
+    """rs_width: column block q of the partial product goes only to push target q (row-major and
+    slab-major staging)."""
+    from tadnn.ops.gemm import gemm_bf16
+    M, N, K, P = 200, 512, 128, 4
+    w = N // P
+    a = torch.randn(M, K, device="cuda").bfloat16()
+    b = torch.randn(N, K, device="cuda").bfloat16()
+    ref = (a.float() @ b.float().t()).bfloat16()
+    slots = [torch.zeros(M, w, device="cuda", dtype=torch.bfloat16) for _ in range(P)]
+    gemm_bf16(a, b, push=[s.data_ptr() for s in slots], push_ldc=w, rs_width=w, n_rotate=1)
+    torch.cuda.synchronize()
+    for q, s in enumerate(slots):
+        assert (s.float() - ref[:, q * w:(q + 1) * w].float()).abs().max().item() <= 0.01 * ref.float().abs().max().item()
+    Mp = (M + 31) // 32 * 32
+    slabs = [torch.zeros(Mp * w, device="cuda", dtype=torch.bfloat16) for _ in range(P)]
+    gemm_bf16(a, b, push=[s.data_ptr() for s in slabs], push_ldc=w, rs_width=w, rs_slab_major=True)
+    torch.cuda.synchronize()
+    for q, s in enumerate(slabs):
+        t = s.view(Mp // 32, w // 64, 32, 8, 8)            # [rowblk, colslab, row, chunk position, 8 elems]
+        rows = torch.arange(32, device="cuda") & 7
+        pos = torch.arange(8, device="cuda")
+        idx = (pos.view(1, 8) ^ rows.view(32, 1))           # chunk j sits at position j ^ (row & 7)
+        un = torch.gather(t, 3, idx.view(1, 1, 32, 8, 1).expand(Mp // 32, w // 64, 32, 8, 8))
+        dense = un.permute(0, 2, 1, 3, 4).reshape(Mp, w)[:M]
+        assert torch.equal(dense, slots[q])

@@ -10,6 +10,7 @@ device never idles on the read.
 """
 from __future__ import annotations
 
+import os
 from typing import Callable, Iterator, Optional
 
 import torch
@@ -26,6 +27,7 @@ class BatchTrainer:
         self._params = [p for p in model.parameters() if p.requires_grad]
         self._cuda = any(p.is_cuda for p in self._params)
         self._copy_stream = torch.cuda.Stream() if self._cuda else None
+        self._nvtx = self._cuda and os.environ.get("TADNN_NVTX", "0") not in ("0", "false")
 
     # ------------------------------------------------------------------ one step
     def _loss(self, x, y):
@@ -56,7 +58,17 @@ class BatchTrainer:
                 p.grad.zero_()
 
     def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
-        """Returns the (device) loss tensor of this step; does not synchronise."""
+        """Returns the (device) loss tensor of this step; does not synchronise.  With
+        ``TADNN_NVTX=1`` the step is wrapped in NVTX ranges for Nsight timelines."""
+        if self._nvtx:
+            torch.cuda.nvtx.range_push(f"tadnn.step {self.steps}")
+            try:
+                return self._step(x, y)
+            finally:
+                torch.cuda.nvtx.range_pop()
+        return self._step(x, y)
+
+    def _step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         if self.criterion is None and self._cuda and hasattr(self.model, "forward_backward"):
             # explicit forward+backward (no autograd), then the hooked-backward bookkeeping
             loss = self.model.forward_backward(x, y)

@@ -532,6 +532,13 @@ extern "C" int tadnn_gemm_bf16(const tadnn_gemm_args* a, tadnn_stream_t stream_)
   TADNN_REQUIRE(a != nullptr, "tadnn_gemm_bf16: null args");
   TADNN_REQUIRE(a->M > 0 && a->N > 0 && a->K > 0, "tadnn_gemm_bf16: bad shape M=%d N=%d K=%d", a->M, a->N, a->K);
   TADNN_REQUIRE(a->n_push >= 0 && a->n_push <= 8, "tadnn_gemm_bf16: n_push=%d out of range", a->n_push);
+  // Large plain problems (K-major operands, bf16 output, no collective / split-K epilogue, tile width not
+  // forced) go to the 2-CTA kernel: cta_group::2 pairs, 256x256 tiles, 1/3 less L2->shared traffic.
+  if (!a->a_mn_major && !a->b_mn_major && !a->c_fp32 && !a->accumulate && a->split_k <= 1 && a->n_push == 0 &&
+      a->rs_width == 0 && a->aux_tanh_out == nullptr && a->tile_n == 0 && a->M >= 512 && a->N >= 256 && a->K >= 256 &&
+      a->lda % 8 == 0 && a->ldb % 8 == 0 && a->ldc % 8 == 0 &&
+      ((reinterpret_cast<uintptr_t>(a->A) | reinterpret_cast<uintptr_t>(a->B) | reinterpret_cast<uintptr_t>(a->C)) & 15) == 0)
+    return tadnn_gemm_bf16_2cta(a->A, a->lda, a->B, a->ldb, a->C, a->ldc, a->M, a->N, a->K, a->bias, a->act, a->alpha, stream_);
   const int num_kb = ceil_div(a->K, BK);
   int split = a->split_k > 1 ? a->split_k : 1;
   if (split > num_kb) split = num_kb;

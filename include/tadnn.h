@@ -84,6 +84,12 @@ typedef struct tadnn_gemm_args {
 
 int tadnn_gemm_bf16(const tadnn_gemm_args* args, tadnn_stream_t stream);
 
+/* 2-CTA variant (csrc/gemm_2cta.cu): thread-block clusters of two CTAs, tcgen05.mma.cta_group::2,
+ * 256x256 tiles, each CTA stages its 128 A rows and half of the B tile.  K-major bf16 operands,
+ * bf16 output, bias/act/alpha epilogue.  Same call sites as tadnn_gemm_bf16 (nodemodule.lua:47,95). */
+int tadnn_gemm_bf16_2cta(const void* A, int lda, const void* B, int ldb, void* C, int ldc, int M, int N,
+                         int K, const float* bias, int act, float alpha, tadnn_stream_t stream);
+
 /* ---- symmetric-memory communication context (csrc/comm.cu) -----------------
  * One process per GPU.  Every rank allocates the same-sized heap, exchanges a 64-byte
  * handle with its peers (any out-of-band channel; tadnn uses torch.distributed) and maps

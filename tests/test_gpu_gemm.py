@@ -145,3 +145,18 @@ def test_gemm_reduce_scatter_push_epilogue():
         un = torch.gather(t, 3, idx.view(1, 1, 32, 8, 1).expand(Mp // 32, w // 64, 32, 8, 8))
         dense = un.permute(0, 2, 1, 3, 4).reshape(Mp, w)[:M]
         assert torch.equal(dense, slots[q])
+
+
+@pytest.mark.parametrize("M,N,K", [(256, 256, 64), (512, 768, 1024), (1000, 520, 200), (300, 136, 72), (4096, 3136, 576)])
+def test_gemm_2cta_cluster_kernel(M, N, K):
+    """tcgen05.mma.cta_group::2 kernel (clusters of two CTAs) vs fp32 reference, incl. ragged edges."""
+    from tadnn.ops.gemm import gemm_bf16_2cta
+    g = torch.Generator(device="cuda").manual_seed(M + N + K)
+    a = torch.randn(M, K, device="cuda", generator=g).bfloat16()
+    b = torch.randn(N, K, device="cuda", generator=g).bfloat16()
+    bias = torch.randn(N, device="cuda", generator=g)
+    s = 1.0 / K ** 0.5
+    y = gemm_bf16_2cta(a, b, bias=bias, act="relu", alpha=s)
+    torch.cuda.synchronize()
+    ref = torch.relu(s * (a.float() @ b.float().t()) + bias)
+    assert (y.float() - ref).abs().max().item() < 2e-2 * max(1.0, ref.abs().max().item())

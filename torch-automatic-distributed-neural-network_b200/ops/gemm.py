@@ -72,3 +72,22 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False,
     rc = _native.lib().tadnn_gemm_bf16(C.byref(args), C.c_void_p(_native.stream_ptr(stream)))
     _native.check(rc, "tadnn_gemm_bf16")
     return out
+
+
+def gemm_bf16_2cta(a: torch.Tensor, b: torch.Tensor, *, out: torch.Tensor | None = None, bias: torch.Tensor | None = None,
+                   act: str | None = None, alpha: float = 1.0, stream=None) -> torch.Tensor:
+    """``out[M,N] = act(alpha * a[M,K] @ b[N,K]^T + bias)`` with the 2-CTA kernel (csrc/gemm_2cta.cu:
+    clusters of two CTAs, ``tcgen05.mma.cta_group::2``, 256x256 tiles).  K-major bf16 operands, bf16 out."""
+    assert a.is_cuda and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
+    assert a.dim() == 2 and b.dim() == 2 and a.stride(1) == 1 and b.stride(1) == 1 and a.shape[1] == b.shape[1]
+    M, K = a.shape
+    N = b.shape[0]
+    if out is None:
+        out = torch.empty((M, N), device=a.device, dtype=torch.bfloat16)
+    assert out.dtype == torch.bfloat16 and out.shape == (M, N) and out.stride(1) == 1
+    rc = _native.lib().tadnn_gemm_bf16_2cta(
+        C.c_void_p(a.data_ptr()), C.c_int(a.stride(0)), C.c_void_p(b.data_ptr()), C.c_int(b.stride(0)),
+        C.c_void_p(out.data_ptr()), C.c_int(out.stride(0)), C.c_int(M), C.c_int(N), C.c_int(K),
+        C.c_void_p(_native.ptr(bias)), C.c_int(_ACT[act]), C.c_float(alpha), C.c_void_p(_native.stream_ptr(stream)))
+    _native.check(rc, "tadnn_gemm_bf16_2cta")
+    return out

@@ -295,6 +295,33 @@ int tadnn_sgd_step(float* p, float* g, long long n, float lr, float weight_decay
                    tadnn_stream_t stream);
 int tadnn_cast_f32_bf16(const float* x, void* y, long long n, tadnn_stream_t stream);
 
+/* ---- linear layers with a tiny output width (csrc/smalln.cu) -----------------------------------
+ * The classifier layer of the README MLP is MPBaseLinear(i, 10) (nodemodule.lua:86-119): one 128-wide
+ * MMA tile would waste >90 % of the tensor core and leave most SMs without work, so N <= 16 gets
+ * bandwidth-shaped CUDA-core kernels.  x, W, g, dx are bf16 with row pitches in elements (K-wide
+ * operands: pitch % 8 == 0 and 16-byte aligned); out, dW, db are fp32.
+ *   fwd   : out[m, n] = sum_k x[m, k] W[n, k] (+ bias[n])
+ *   dgrad : dx[m, k]  = (sum_n g[m, n] W[n, k]) * (aux ? 1 - aux[m, k]^2 : 1)
+ *   wgrad : dW[n, k] (+)= sum_m g[m, n] x[m, k];   db[n] (+)= sum_m g[m, n]   (db may be NULL) */
+int tadnn_linear_smalln_fwd(const void* x, int ldx, const void* W, int ldw, const float* bias, float* out,
+                            int ldo, int M, int N, int K, tadnn_stream_t stream);
+int tadnn_linear_smalln_dgrad(const void* g, int ldg, const void* W, int ldw, const void* aux_tanh_out,
+                              int ld_aux, void* dx, int lddx, int M, int N, int K, tadnn_stream_t stream);
+int tadnn_linear_smalln_wgrad(const void* g, int ldg, const void* x, int ldx, float* dW, int lddw, float* db,
+                              int M, int N, int K, int accumulate, tadnn_stream_t stream);
+
+/* ---- dataset preprocessing (csrc/preprocess.cu) -------------------------------------------------
+ * cifar_example/sgd-torchad_nn-cifar.lua:182-216: rgb2yuv, U/V standardised with the training
+ * shard's mean/std, Y through SpatialContrastiveNormalization(1, gaussian1D(7)).  rgb is fp32
+ * [n, 3, H, W]; stats4 receives (sum u, sum u^2, sum v, sum v^2) in fp64 on the device; out is fp32 or
+ * bf16 [n, 3, H, W].  H*W <= 5120, odd tap count <= 15.  Pass a negative std for the reference's
+ * sign quirk (lines 195, 200, 213, 216). */
+int tadnn_preprocess_uv_stats(const float* rgb, double* stats4, long long n_img, int H, int W,
+                              tadnn_stream_t stream);
+int tadnn_preprocess_yuv_lcn(const float* rgb, void* out, int out_bf16, long long n_img, int H, int W,
+                             const float* taps1d, int n_taps, float mean_u, float std_u, float mean_v,
+                             float std_v, float threshold, tadnn_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

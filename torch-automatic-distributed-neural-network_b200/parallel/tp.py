@@ -20,7 +20,8 @@ Activations stay *sharded* between layers (``a'_r`` is exactly the slice the nex
 layer instead of the all-reduce's 2(P-1)/P·B·o, and the redundant full-width tanh of the
 reference disappears.  The backward is the exact gradient (the reference's ``syncTanh`` gather).
 Layers whose width is not a multiple of 64·P (e.g. the 10-way classifier) fall back to a plain
-GEMM + one-shot all-reduce of the small output.
+GEMM + one-shot all-reduce of the small output; a classifier-sized layer (o <= 16) runs on the
+GEMV-style kernels of csrc/smalln.cu instead of a mostly empty MMA tile.
 """
 from __future__ import annotations
 
@@ -34,6 +35,7 @@ import torch.nn.functional as F
 from .. import _native
 from .. import mpi as _mpi
 from . import symm as _symm
+from ..ops import smalln as _smalln
 
 
 def _cast_bf16(w: torch.Tensor) -> torch.Tensor:
@@ -42,6 +44,14 @@ def _cast_bf16(w: torch.Tensor) -> torch.Tensor:
                                                     C.c_longlong(w.numel()), C.c_void_p(_native.stream_ptr())),
                   "tadnn_cast_f32_bf16")
     return out
+
+
+def _smalln_ok(o: int, a: torch.Tensor, which: str) -> bool:
+    """The GEMV-style kernels (csrc/smalln.cu) take a classifier-sized layer when the activation rows are
+    16-byte aligned and the measured crossover (ops/smalln.py) says they beat the tcgen05 tile."""
+    prefer = getattr(_smalln, "prefer_" + which)
+    return (prefer(a.shape[0], o, a.shape[1]) and a.stride(1) == 1 and a.stride(0) % 8 == 0
+            and a.data_ptr() % 16 == 0)
 
 
 class _Plan:
@@ -102,7 +112,10 @@ class _Fn(torch.autograd.Function):
                 a = nxt
             else:
                 part = plan.small[:B * o].view(B, o)
-                gemm_bf16(a, wb, bias=b, out=part, out_dtype=torch.float32, tile_n=64)
+                if _smalln_ok(o, a, "fwd"):
+                    _smalln.linear_smalln_fwd(a, wb, bias=b, out=part)  # classifier-sized layer: GEMV-style kernel (K11)
+                else:
+                    gemm_bf16(a, wb, bias=b, out=part, out_dtype=torch.float32, tile_n=64)
                 if P > 1:
                     sc.allreduce_(part, 1.0, channel=_symm.CH_TP)
                 y = part.clone()
@@ -152,7 +165,10 @@ class _Fn(torch.autograd.Function):
             if need_dx:
                 # g'_r [B, i/P] = (g · W_r) (⊙ tanh' of the layer input if that input is a tanh output)
                 tn = 256 if i_sh >= 256 else 0  # measured: 256-wide tiles beat 128-wide ones even at 1.7 waves
-                gr = gemm_bf16(gv, wbs[l], b_mn_major=True, aux_tanh_out=a if l > 0 else None, tile_n=tn)
+                if _smalln_ok(o, a, "dgrad"):
+                    gr = _smalln.linear_smalln_dgrad(gv, wbs[l], aux_tanh_out=a if l > 0 else None)
+                else:
+                    gr = gemm_bf16(gv, wbs[l], b_mn_major=True, aux_tanh_out=a if l > 0 else None, tile_n=tn)
                 if P > 1:
                     # all-gather of the slice gradients on a side stream, into the OTHER buffer, so that it
                     # overlaps this layer's wgrad GEMM (the gather kernel needs few registers and co-resides)
@@ -162,11 +178,14 @@ class _Fn(torch.autograd.Function):
                         sc.allgather_cols_offset(gr, offs[cur ^ 1], _symm.CH_TP, side)
                         gathered = side.record_event()
             # dW_r [o, i/P] = gᵀ · a_r   (A: g stored [K=B, M=o];  B: a_r stored [K=B, N=i/P])
-            tile_n = 256 if i_sh > 128 else (128 if i_sh > 64 else 64)
-            dW = gemm_bf16(gv, a, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
-                           split_k=auto_split_k(o, i_sh, B, tile_n), tile_n=tile_n)
-            db = torch.zeros(o, device=dev, dtype=torch.float32)
-            colsum_bf16(gv, db)
+            if _smalln_ok(o, a, "wgrad"):
+                dW, db = _smalln.linear_smalln_wgrad(gv, a)  # weight and bias gradient in one pass over a_r
+            else:
+                tile_n = 256 if i_sh > 128 else (128 if i_sh > 64 else 64)
+                dW = gemm_bf16(gv, a, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
+                               split_k=auto_split_k(o, i_sh, B, tile_n), tile_n=tile_n)
+                db = torch.zeros(o, device=dev, dtype=torch.float32)
+                colsum_bf16(gv, db)
             grads[2 * l], grads[2 * l + 1] = dW, db
             if not need_dx:
                 break

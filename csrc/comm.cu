@@ -329,6 +329,48 @@ __global__ void __launch_bounds__(512) reduce_slots_kernel(CommDev c, size_t slo
   block_barrier(c, channel);  // slots may be overwritten / pushed results are visible
 }
 
+// ---- reduce-scatter (optionally all-reduce) of column-split GEMM partials INSIDE the switch (NVLS).
+// Every rank's GEMM wrote its full partial [rows, world*width] (bf16) at the same heap offset.  Rank r
+// owns columns [r*width, (r+1)*width): one multimem.ld_reduce per 16 bytes returns the sum over all
+// ranks (fp32 accumulation in the switch), so a rank RECEIVES rows*width*2 bytes instead of the
+// (world-1) slots the push variant stores into it; bias/activation are applied on the way to the
+// local output, and `bcast` multimem.st's the result back into every rank's buffer (all-reduce).
+__global__ void __launch_bounds__(512) reduce_cols_nvls_kernel(CommDev c, size_t part_off, int rows, int width8, float scale,
+                                                               const float* bias, int act, __nv_bfloat16* out_local, size_t out_pitch,
+                                                               int bcast, int channel) {
+  const int rank = my_rank(c);
+  const size_t total = static_cast<size_t>(rows) * width8;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const size_t row_vecs = static_cast<size_t>(width8) * c.world;
+  block_barrier(c, channel);  // every rank's partial is complete and visible
+  for (size_t i = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total; i += stride) {
+    const size_t row = i / width8, c8 = i - row * width8;
+    uint8_t* p = c.mc_heap + part_off + (row * row_vecs + static_cast<size_t>(rank) * width8 + c8) * 16;
+    uint32_t x, y, z, w;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(x), "=r"(y), "=r"(z), "=r"(w) : "l"(p) : "memory");
+    float v[8];
+    float2 f;
+    f = unpack_bf16x2(x); v[0] = f.x; v[1] = f.y;
+    f = unpack_bf16x2(y); v[2] = f.x; v[3] = f.y;
+    f = unpack_bf16x2(z); v[4] = f.x; v[5] = f.y;
+    f = unpack_bf16x2(w); v[6] = f.x; v[7] = f.y;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      float t = v[e] * scale;
+      if (bias != nullptr) t += bias[(static_cast<size_t>(rank) * width8 + c8) * 8 + e];
+      if (act == 1) t = tanh_f32(t);
+      else if (act == 2) t = fmaxf(t, 0.f);
+      v[e] = t;
+    }
+    const uint4 o = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+    if (out_local != nullptr) *reinterpret_cast<uint4*>(out_local + row * out_pitch + c8 * 8) = o;
+    if (bcast)
+      asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(o.x), "r"(o.y), "r"(o.z), "r"(o.w) : "memory");
+  }
+  block_barrier(c, channel);  // partials may be overwritten / broadcast results are visible
+}
+
 // Slab-major staging (GEMM rs_slab_major): slot q holds ceil(rows/32) x (width/64) slabs of 4 KB, each a
 // 32-row x 64-column tile in the SWIZZLE_128B order of the GEMM's staging buffer (16-byte chunk j of
 // slab row rr sits at chunk position j ^ (rr & 7)).  Threads walk the slots linearly (fully
@@ -628,6 +670,23 @@ extern "C" int tadnn_reduce_scatter_cols(tadnn_comm* c, unsigned long long off_b
   else
     reduce_scatter_cols_kernel<1><<<blocks, 512, 0, stream>>>(c->dev, off_bytes, dst, dst_pitch, rows, width, scale, bias, act, channel);
   TADNN_LAUNCH_CHECK("reduce_scatter_cols");
+  return 0;
+}
+
+extern "C" int tadnn_reduce_cols_nvls(tadnn_comm* c, unsigned long long part_off, int rows, int width, float scale, const float* bias,
+                                      int act, void* out_local, unsigned long long out_pitch, int bcast, int max_blocks, int channel,
+                                      tadnn_stream_t stream) {
+  if (int rc = validate(c, channel, "reduce_cols_nvls")) return rc;
+  TADNN_REQUIRE(c->dev.mc_heap != nullptr, "reduce_cols_nvls: this context has no multicast mapping (NVLS unavailable)");
+  TADNN_REQUIRE(rows > 0 && width > 0 && width % 8 == 0, "reduce_cols_nvls: width must be a positive multiple of 8");
+  TADNN_REQUIRE(part_off % 16 == 0, "reduce_cols_nvls: offset must be 16-byte aligned");
+  TADNN_REQUIRE(part_off + 2ull * rows * width * c->world <= c->heap_bytes, "reduce_cols_nvls: partials exceed the heap");
+  TADNN_REQUIRE(out_local == nullptr || ((reinterpret_cast<uintptr_t>(out_local) & 15) == 0 && out_pitch % 8 == 0),
+                "reduce_cols_nvls: out_local must be 16-byte aligned with a pitch multiple of 8");
+  const int blocks = pick_blocks(static_cast<size_t>(rows) * (width / 8), max_blocks, 148);
+  reduce_cols_nvls_kernel<<<blocks, 512, 0, static_cast<cudaStream_t>(stream)>>>(
+      c->dev, part_off, rows, width / 8, scale, bias, act, static_cast<__nv_bfloat16*>(out_local), out_pitch, bcast, channel);
+  TADNN_LAUNCH_CHECK("reduce_cols_nvls");
   return 0;
 }
 

@@ -30,6 +30,8 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--out", default="gpurun_out")
+    ap.add_argument("--reduce", default="", choices=["", "push", "nvls"], help="forward reduction of FusedMPMLP (default: its own default)")
+    ap.add_argument("--chunks", type=int, default=0, help="row chunks of the NVLS pipeline")
     ap.add_argument("--phases", action="store_true", help="also time forward / backward / update separately")
     a = ap.parse_args()
     if a.impl == "nccl":
@@ -48,6 +50,10 @@ def main():
         sizes, B = [1024, 2048, 10], (a.batch or 8192)
     if a.impl == "tadnn":
         model = FusedMPMLP(sizes, mpi=h).to(dev)
+        if a.reduce:
+            model.reduce_mode = a.reduce
+        if a.chunks:
+            model.nvls_chunks = a.chunks
     else:
         model = nn.Sequential()
         for l in range(len(sizes) - 1):
@@ -122,14 +128,15 @@ def main():
     t_compute = flops / (peaks["bf16_tflops_sustained"] * 1e12) * 1e3
     t_link = nvl / 770e9 * 1e3
     if rank == 0:
-        res = {"config": a.config, "impl": a.impl, "world": P, "batch": B, "sizes": sizes, "ms_per_step": ms,
+        res = {"config": a.config, "impl": a.impl, "reduce": (model.reduce_mode if a.impl == "tadnn" else None),
+               "chunks": (model.nvls_chunks if a.impl == "tadnn" else None), "world": P, "batch": B, "sizes": sizes, "ms_per_step": ms,
                "samples_per_s": B / ms * 1e3, "tflops_per_gpu": flops / ms / 1e9,
                "roofline_ms": max(t_compute, t_link), "compute_ms_at_measured_peak": t_compute,
                "nvlink_ms_at_770GBs": t_link, "fraction_of_roofline": max(t_compute, t_link) / ms,
                "loss": float(loss), "phases": phases}
         print(json.dumps(res), flush=True)
         os.makedirs(a.out, exist_ok=True)
-        with open(os.path.join(a.out, f"mp_{a.config}_{a.impl}_P{P}.json"), "w") as f:
+        with open(os.path.join(a.out, f"mp_{a.config}_{a.impl}{('_' + a.reduce + str(a.chunks)) if a.reduce else ''}_P{P}.json"), "w") as f:
             json.dump(res, f)
     h.stop()
 

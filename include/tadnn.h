@@ -183,6 +183,16 @@ int tadnn_reduce_slots(tadnn_comm* c, unsigned long long slots_off, int rows, in
                        unsigned long long push_off, int do_push, int slab_major, int max_blocks,
                        int channel, tadnn_stream_t stream);
 
+/* NVLS form of the GEMM -> reduce-scatter finalize: every rank's GEMM wrote its full partial
+ * [rows, world*width] bf16 at heap offset part_off; this rank reads the switch-reduced sum of ITS
+ * column block (multimem.ld_reduce, fp32 accumulation), applies scale/bias/act and writes out_local
+ * [rows, width]; bcast != 0 also multimem.st's the result into every rank's buffer (all-reduce).
+ * Needs the VMM + multicast heap (tadnn_comm_mc_bind).  Replaces the blocking allreduceTensor of the
+ * layer output (nodemodule.lua:49,97). */
+int tadnn_reduce_cols_nvls(tadnn_comm* c, unsigned long long part_off, int rows, int width, float scale,
+                           const float* bias, int act, void* out_local, unsigned long long out_pitch,
+                           int bcast, int max_blocks, int channel, tadnn_stream_t stream);
+
 /* Emulated (single launch, no cross-launch waiting) variants for 1-GPU numerics tests on a
  * tadnn_comm_create_local() set: performs rank `as_rank`'s share of the math with all
  * barriers skipped. */

@@ -118,9 +118,14 @@ def main():
 
     # ---- fused model-parallel MLP (GEMM epilogue -> peer staging slots -> reduce) vs dense fp32
     from tadnn.parallel.tp import FusedMPMLP
-    for sizes, B in (([1024, 2048, 10], 96), ([512, 1024, 1024, 512], 200)):
+    cases = [([1024, 2048, 10], 96, "push", 1), ([512, 1024, 1024, 512], 200, "push", 1)]
+    if ctx.has_multicast:  # in-switch (multimem.ld_reduce) form of the same reduction, unchunked and row-pipelined
+        cases += [([512, 1024, 1024, 512], 200, "nvls", 1), ([1024, 2048, 1024, 10], 1536, "nvls", 3)]
+    for sizes, B, mode, chunks in cases:
         g = torch.Generator(device="cpu").manual_seed(77)
         mlp = FusedMPMLP(sizes, mpi=h).to(dev)
+        mlp.reduce_mode, mlp.nvls_chunks = mode, chunks
+        tag = f"fused MP-MLP[{mode}x{chunks}] {sizes}"
         dense_W, dense_b = [], []
         for l in range(len(sizes) - 1):
             Wd = (torch.rand(sizes[l + 1], sizes[l], generator=g) - 0.5) * (2.0 / sizes[l] ** 0.5)
@@ -144,18 +149,18 @@ def main():
         ref_loss = ((a - tgt) ** 2).mean()
         ref_loss.backward()
         torch.cuda.synchronize()
-        expect(f"fused MP-MLP {sizes} forward", y, a.detach(), 3e-2)
+        expect(f"{tag} forward", y, a.detach(), 3e-2)
         for l in range(len(sizes) - 1):
             sh = sizes[l] // P
             gw_ref = dense_W[l].grad[:, rank * sh:(rank + 1) * sh]
             rel = ((mlp.weights[l].grad - gw_ref).norm() / (gw_ref.norm() + 1e-12)).item()
             checks += 1
             if not rel < 4e-2:
-                fails.append(f"fused MP-MLP {sizes} layer {l} dW rel err {rel:.3e}")
+                fails.append(f"{tag} layer {l} dW rel err {rel:.3e}")
             relb = ((mlp.biases[l].grad - dense_b[l].grad).norm() / (dense_b[l].grad.norm() + 1e-12)).item()
             checks += 1
             if not relb < 4e-2:
-                fails.append(f"fused MP-MLP {sizes} layer {l} db rel err {relb:.3e}")
+                fails.append(f"{tag} layer {l} db rel err {relb:.3e}")
 
     # ---- device barrier stress
     for _ in range(500):

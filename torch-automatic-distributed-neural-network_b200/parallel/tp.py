@@ -70,6 +70,17 @@ class _Plan:
         self.gfull2_off = ctx.alloc(2 * B * allo_pad)                 # second buffer: the all-gather of layer l-1's
         #                                                               gradient lands here while layer l's wgrad still reads the first
         self.small = ctx.empty((B * allo_pad,), torch.float32)        # small-layer partial sums (all-reduced in place)
+        self._ctx, self._maxo = ctx, maxo
+        self._part2 = None
+
+    def part_off(self, parity: int) -> int:
+        """NVLS mode: [B, o] bf16 partial-product buffers, double-buffered over layers (a peer may still be
+        reading layer l's partials through the switch while this rank's layer l+1 GEMM already writes)."""
+        if parity == 0:
+            return self.slots_off
+        if self._part2 is None:
+            self._part2 = self._ctx.alloc(2 * self.Bpad * self._maxo)
+        return self._part2
 
 
 class _Fn(torch.autograd.Function):
@@ -89,13 +100,43 @@ class _Fn(torch.autograd.Function):
         acts = [a]
         wbs = []
         out = None
+        use_nvls = P > 1 and sc.has_multicast and mod.reduce_mode == "nvls"
         for l in range(L):
             W, b = params[2 * l], params[2 * l + 1]
             o = mod.sizes[l + 1]
             last = l == L - 1
             wb = _cast_bf16(W)
             wbs.append(wb)
-            if o % (64 * P) == 0:
+            if o % (64 * P) == 0 and use_nvls:
+                # NVLS form: plain (2-CTA) GEMM into the own heap, then every rank pulls the switch-reduced
+                # sum of its column block.  Row chunks pipeline the two: chunk c's reduction runs on the
+                # side stream while the tensor cores are already on chunk c+1.
+                w = o // P
+                poff = plan.part_off(l & 1)
+                part = sc.tensor(poff, (B, o), torch.bfloat16)
+                nxt = torch.empty((B, w), device=x.device, dtype=torch.bfloat16)
+                nch = max(1, min(mod.nvls_chunks, B // 512))
+                bounds = [B * c // nch // 128 * 128 for c in range(nch)] + [B]
+                side = mod._side_stream()
+                main = torch.cuda.current_stream()
+                if nch > 1:
+                    nxt.record_stream(side)
+                for c in range(nch):
+                    r0, r1 = bounds[c], bounds[c + 1]
+                    gemm_bf16(a[r0:r1], wb, bias=b, out=part[r0:r1])
+                    if nch > 1:
+                        side.wait_event(main.record_event())
+                    with torch.cuda.stream(side if nch > 1 else main):
+                        _native.check(lib.tadnn_reduce_cols_nvls(
+                            sc.handle, C.c_ulonglong(poff + r0 * o * 2), r1 - r0, w, C.c_float(1.0), None, 0 if last else 1,
+                            C.c_void_p(nxt[r0:].data_ptr()), C.c_ulonglong(w), int(last), 0, _symm.CH_TP,
+                            C.c_void_p(_native.stream_ptr())), "tadnn_reduce_cols_nvls")
+                if nch > 1:
+                    main.wait_event(side.record_event())
+                if last:
+                    out = part.float()  # the owners multimem.st their column blocks into every rank's buffer
+                a = nxt
+            elif o % (64 * P) == 0:
                 w = o // P
                 push = [sc.heap_ptrs[q] + plan.slots_off + r * B * w * 2 for q in range(P)]  # slot r of rank q: [B, w]
                 # every rank starts its tile sweep at a different owner's column block: at any moment the
@@ -243,6 +284,30 @@ class FusedMPMLP(torch.nn.Module):
         return self
 
     # ------------------------------------------------------------------
+    # How the K-split partial products of a wide layer are summed across ranks:
+    #   "push": the GEMM epilogue TMA-stores each column block into its owner's staging slot over NVLink,
+    #           reduce_slots sums the slots locally (works on any P2P-capable box);
+    #   "nvls": the GEMM writes locally, the owner pulls the sum through the switch (multimem.ld_reduce),
+    #           optionally pipelined over `nvls_chunks` row chunks.  Needs the VMM + multicast heap.
+    @property
+    def reduce_mode(self) -> str:
+        import os
+        return getattr(self, "_reduce_mode", None) or os.environ.get("TADNN_MP_REDUCE", "push")
+
+    @reduce_mode.setter
+    def reduce_mode(self, v: str) -> None:
+        assert v in ("push", "nvls")
+        self._reduce_mode = v
+
+    @property
+    def nvls_chunks(self) -> int:
+        import os
+        return int(getattr(self, "_nvls_chunks", 0) or os.environ.get("TADNN_MP_NVLS_CHUNKS", "2"))
+
+    @nvls_chunks.setter
+    def nvls_chunks(self, v: int) -> None:
+        self._nvls_chunks = int(v)
+
     def _handle(self):
         return self._mpi if self._mpi is not None else _mpi.current()
 

@@ -7,9 +7,11 @@ CIFAR-10-shaped CNN, automatic data parallelism through parallelize().
 Same 8 flags and defaults as the Lua script (:29-43), same results-file fields (:277-299), the
 confusion matrix of :266-275.  There is no network on this box, so the dataset is synthetic
 CIFAR-shaped data (class-dependent mean, learnable); -data selects 32000/10000 instead of
-4000/2000 samples as in the reference (:124-130).  Preprocessing (YUV + contrast normalisation,
-:182-216) is skipped for synthetic data.  --miniBatch > 1 is the B200 extension: the
-reference trains one sample per step.
+4000/2000 samples as in the reference (:124-130).  Preprocessing (rgb2yuv, U/V standardisation with
+the training shard's statistics, Y contrast normalisation, :182-216) runs after parallelize() as in
+the reference — through the native kernels of csrc/preprocess.cu on a GPU, the tensor implementation
+on the CPU; --preprocess none skips it.  --miniBatch > 1 is the B200 extension: the reference trains
+one sample per step.
 """
 import argparse
 import os
@@ -23,6 +25,7 @@ import tadnn.mpi as mpi  # noqa: E402
 from tadnn import nn  # noqa: E402
 from tadnn.models import CifarCNN  # noqa: E402
 from tadnn.utils import config as cfg  # noqa: E402
+from tadnn.utils import preprocess as prep  # noqa: E402
 from tadnn.utils.confusion import ConfusionMatrix  # noqa: E402
 from tadnn.utils.logging import log, write_results_file  # noqa: E402
 from tadnn.utils.timing import Tic  # noqa: E402
@@ -56,6 +59,14 @@ def main():
         train_x, test_x = train_x.bfloat16(), test_x.bfloat16()
     # :172 — the one call
     train_x, train_y, trsize = automation.parallelize(train_x, train_y, model, opt.trsize, h, None, opt.batchSize)
+    if opt.preprocess == "yuv":
+        # :182-216 — statistics come from this rank's training shard and are applied to the test set
+        if use_gpu:
+            tr, te = prep.preprocess_cuda(train_x.to(dev).float().contiguous(), test_x.to(dev).float().contiguous(),
+                                          out_dtype=torch.bfloat16)
+            train_x, test_x = tr.cpu(), te.cpu()
+        else:
+            train_x, test_x = prep.preprocess(train_x.float().contiguous(), test_x.float())
     t1 = tic.toc()
     tic.tic()
     if opt.miniBatch > 1:

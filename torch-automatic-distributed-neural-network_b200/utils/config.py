@@ -22,6 +22,10 @@ ENV_SWITCHES = {
     "TADNN_FORCE_PATH": "nccl = never build the symmetric-memory context (baseline path)",
     "TADNN_FORCE_ALGO": "1 one-shot / 2 two-shot / 3 NVLS for every symmetric all-reduce",
     "TADNN_DP_OVERLAP": "0 = do not overlap the gradient sync with backward",
+    "TADNN_MP_REDUCE": "push (default) / nvls: how FusedMPMLP sums the K-split partial products (parallel/tp.py)",
+    "TADNN_MP_NVLS_CHUNKS": "row chunks of the NVLS reduction pipeline (default 2)",
+    "TADNN_NVLS": "0 = never create the multicast object (VMM heap without NVLS)",
+    "TADNN_NVTX": "1 = NVTX ranges around the training-step phases",
     "TADNN_SYMM_HEAP_MB": "size of the symmetric heap per GPU (default 1024)",
     "TADNN_SYMM_STAGING_MB": "staging area inside the heap for tensors that live outside it (default 128)",
 }
@@ -43,6 +47,7 @@ class TrainConfig:
     dtype: str = "bf16"
     model: str = "cifar_cnn"
     results_dir: str = "."
+    preprocess: str = "yuv"       # "yuv": rgb2yuv + contrast normalisation as in the example (:182-216); "none": skip
 
     @property
     def trsize(self) -> int:
@@ -66,6 +71,8 @@ def add_reference_flags(ap: argparse.ArgumentParser) -> argparse.ArgumentParser:
     ap.add_argument("--miniBatch", type=int, default=d.miniBatch)
     ap.add_argument("--dtype", default=d.dtype, choices=["bf16", "fp32"])
     ap.add_argument("--results-dir", default=d.results_dir)
+    ap.add_argument("--preprocess", default=d.preprocess, choices=["yuv", "none"],
+                    help="dataset preprocessing of the example (rgb2yuv, U/V standardisation, Y contrast normalisation)")
     return ap
 
 

@@ -44,10 +44,8 @@ bool load(F& fn, const char* name) {
 }
 
 Drv& drv() {
-  static Drv d;
-  static bool tried = false;
-  if (!tried) {
-    tried = true;
+  static Drv d = [] {  // C++11 magic static: initialised once, thread-safe
+    Drv d;
     d.ok = load(d.MemCreate, "cuMemCreate") && load(d.MemRelease, "cuMemRelease") &&
            load(d.MemAddressReserve, "cuMemAddressReserve") && load(d.MemAddressFree, "cuMemAddressFree") &&
            load(d.MemMap, "cuMemMap") && load(d.MemUnmap, "cuMemUnmap") && load(d.MemSetAccess, "cuMemSetAccess") &&
@@ -56,7 +54,8 @@ Drv& drv() {
            load(d.McAddDevice, "cuMulticastAddDevice") && load(d.McBindMem, "cuMulticastBindMem") &&
            load(d.McGetGranularity, "cuMulticastGetGranularity") && load(d.DeviceGetAttribute, "cuDeviceGetAttribute") &&
            load(d.DeviceGet, "cuDeviceGet");
-  }
+    return d;
+  }();
   return d;
 }
 
@@ -79,15 +78,31 @@ CUmemAllocationProp heap_prop(int device) {
   return prop;
 }
 
+// Reserve a VA range, map `h` into it read-write for `device`.  On failure nothing stays reserved or
+// mapped and *va is 0.
 int map_rw(Drv& d, CUdeviceptr* va, size_t bytes, size_t gran, CUmemGenericAllocationHandle h, int device) {
-  TADNN_CHECK_CU(d.MemAddressReserve(va, bytes, gran, 0, 0));
-  TADNN_CHECK_CU(d.MemMap(*va, bytes, 0, h, 0));
+  *va = 0;
+  CUdeviceptr p = 0;
+  TADNN_CHECK_CU(d.MemAddressReserve(&p, bytes, gran, 0, 0));
+  CUresult r = d.MemMap(p, bytes, 0, h, 0);
+  if (r != CUDA_SUCCESS) {
+    d.MemAddressFree(p, bytes);
+    set_error("%s:%d: cuMemMap -> CUresult %d", __FILE__, __LINE__, static_cast<int>(r));
+    return 1;
+  }
   CUmemAccessDesc acc;
   memset(&acc, 0, sizeof(acc));
   acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
   acc.location.id = device;
   acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
-  TADNN_CHECK_CU(d.MemSetAccess(*va, bytes, &acc, 1));
+  r = d.MemSetAccess(p, bytes, &acc, 1);
+  if (r != CUDA_SUCCESS) {
+    d.MemUnmap(p, bytes);
+    d.MemAddressFree(p, bytes);
+    set_error("%s:%d: cuMemSetAccess -> CUresult %d", __FILE__, __LINE__, static_cast<int>(r));
+    return 1;
+  }
+  *va = p;
   return 0;
 }
 
@@ -111,13 +126,8 @@ extern "C" int tadnn_multicast_supported(int* out) {
   return 0;
 }
 
-extern "C" int tadnn_comm_create_vmm(int rank, int world, unsigned long long heap_bytes, tadnn_comm** out) {
-  TADNN_REQUIRE(out != nullptr, "comm_create_vmm: null out");
-  TADNN_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, "comm_create_vmm: bad rank/world %d/%d", rank, world);
+static int create_vmm_into(tadnn_comm* c, int rank, int world, unsigned long long heap_bytes) {
   Drv& d = drv();
-  TADNN_REQUIRE(d.ok, "comm_create_vmm: the CUDA driver does not export the VMM/multicast entry points");
-  TADNN_CHECK_CUDA(cudaFree(nullptr));
-  tadnn_comm* c = new tadnn_comm();
   c->rank = rank; c->world = world; c->vmm = true; c->owns = true;
   TADNN_CHECK_CUDA(cudaGetDevice(&c->device));
   heap_bytes = (heap_bytes + 1023ull) & ~1023ull;
@@ -151,6 +161,21 @@ extern "C" int tadnn_comm_create_vmm(int rank, int world, unsigned long long hea
   c->dev.pad[rank] = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(c->base) + heap_bytes);
   c->peer_handles.assign(world, 0);
   c->peer_vas.assign(world, nullptr);
+  return 0;
+}
+
+extern "C" int tadnn_comm_create_vmm(int rank, int world, unsigned long long heap_bytes, tadnn_comm** out) {
+  TADNN_REQUIRE(out != nullptr, "comm_create_vmm: null out");
+  *out = nullptr;
+  TADNN_REQUIRE(world >= 1 && world <= kMaxRanks && rank >= 0 && rank < world, "comm_create_vmm: bad rank/world %d/%d", rank, world);
+  TADNN_REQUIRE(drv().ok, "comm_create_vmm: the CUDA driver does not export the VMM/multicast entry points");
+  TADNN_CHECK_CUDA(cudaFree(nullptr));
+  tadnn_comm* c = new tadnn_comm();
+  if (int rc = create_vmm_into(c, rank, world, heap_bytes)) {
+    tadnn_comm_vmm_release(c);  // unmaps / releases whatever was set up before the failure
+    delete c;
+    return rc;
+  }
   *out = c;
   return 0;
 }
@@ -167,17 +192,18 @@ extern "C" int tadnn_comm_import_peer_fd(tadnn_comm* c, int peer, int fd) {
   TADNN_REQUIRE(c && c->vmm && peer >= 0 && peer < c->world && peer != c->rank, "comm_import_peer_fd: bad argument");
   Drv& d = drv();
   CUmemGenericAllocationHandle h;
-  TADNN_CHECK_CU(d.MemImport(&h, reinterpret_cast<void*>(static_cast<intptr_t>(fd)), CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR));
+  const CUresult ir = d.MemImport(&h, reinterpret_cast<void*>(static_cast<intptr_t>(fd)), CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+  close(fd);  // this call owns the descriptor; the driver keeps its own reference after a successful import
+  TADNN_REQUIRE(ir == CUDA_SUCCESS, "comm_import_peer_fd: cuMemImportFromShareableHandle -> CUresult %d", static_cast<int>(ir));
+  c->peer_handles[peer] = h;  // recorded first so that vmm_release frees it if the mapping fails
   CUmemAllocationProp prop = heap_prop(c->device);
   size_t gran = 0;
   TADNN_CHECK_CU(d.MemGetGranularity(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED));
   CUdeviceptr va = 0;
   if (int rc = map_rw(d, &va, c->alloc_bytes, gran, h, c->device)) return rc;
-  c->peer_handles[peer] = h;
   c->peer_vas[peer] = reinterpret_cast<void*>(va);
   c->dev.heap[peer] = reinterpret_cast<uint8_t*>(va);
   c->dev.pad[peer] = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(va) + c->heap_bytes);
-  close(fd);
   return 0;
 }
 
@@ -202,9 +228,10 @@ extern "C" int tadnn_comm_mc_create(tadnn_comm* c, int* fd) {
 extern "C" int tadnn_comm_mc_import(tadnn_comm* c, int fd) {
   TADNN_REQUIRE(c && c->vmm, "comm_mc_import: not a VMM context");
   CUmemGenericAllocationHandle h;
-  TADNN_CHECK_CU(drv().MemImport(&h, reinterpret_cast<void*>(static_cast<intptr_t>(fd)), CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR));
-  c->mc_handle = h;
+  const CUresult ir = drv().MemImport(&h, reinterpret_cast<void*>(static_cast<intptr_t>(fd)), CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
   close(fd);
+  TADNN_REQUIRE(ir == CUDA_SUCCESS, "comm_mc_import: cuMemImportFromShareableHandle -> CUresult %d", static_cast<int>(ir));
+  c->mc_handle = h;
   return 0;
 }
 

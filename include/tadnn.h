@@ -127,7 +127,10 @@ int tadnn_comm_destroy(tadnn_comm* c);
  * POSIX file descriptor; where the driver exposes NVLS a multicast object over all heaps is mapped
  * and the multimem all-reduce (algo 3) becomes available.  Sequence per rank: create_vmm ->
  * export_fd (send the fd to every peer) -> import_peer_fd for every peer; optional multicast:
- * rank 0 mc_create (send fd) / others mc_import -> mc_add_device -> host barrier -> mc_bind. */
+ * rank 0 mc_create (send fd) / others mc_import -> mc_add_device -> host barrier -> mc_bind.
+ * Descriptor ownership: export_fd / mc_create return a descriptor the caller closes after sending it;
+ * import_peer_fd / mc_import take ownership of theirs and close it whether or not the import succeeds.
+ * A failed create_vmm leaves nothing allocated or mapped. */
 int tadnn_multicast_supported(int* out);
 int tadnn_comm_create_vmm(int rank, int world, unsigned long long heap_bytes, tadnn_comm** out);
 int tadnn_comm_export_fd(tadnn_comm* c, int* fd);

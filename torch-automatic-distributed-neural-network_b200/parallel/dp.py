@@ -109,7 +109,6 @@ class SyncState:
         buckets = []
         for g in self.flat.groups.values():
             es = g.region.element_size()
-            ends = [off + p.numel() for p, off in zip(g.params, g.offsets)]
             hi = g.half
             ids: List[int] = []
             for i in range(len(g.params) - 1, -1, -1):
@@ -122,7 +121,6 @@ class SyncState:
                                     "count": hi - lo_al, "ids": set(ids), "left": 0})
                     hi = lo_al
                     ids = []
-            del ends
         return buckets
 
     def _on_grad(self, p):

@@ -76,6 +76,7 @@ class FlatBuffer:
                         gv.copy_(p.grad)
                     p.data = pv
                     p.grad = gv
+        self._where = {id(p): (g, off) for g in self.groups.values() for p, off in zip(g.params, g.offsets)}
         model._tadnn_flat = self
 
     # ------------------------------------------------------------------ views
@@ -97,9 +98,7 @@ class FlatBuffer:
         return g.region[g.half:]
 
     def grad_view(self, p: torch.nn.Parameter) -> torch.Tensor:
-        g = self.groups[p.dtype]
-        i = next(k for k, q in enumerate(g.params) if q is p)
-        off = g.offsets[i]
+        g, off = self._where[id(p)]
         return g.region[g.half + off:g.half + off + p.numel()].view(p.shape)
 
     def rehome_grads(self) -> int:

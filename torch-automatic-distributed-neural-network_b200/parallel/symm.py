@@ -1,15 +1,21 @@
 """Symmetric-memory context: one peer-mapped heap per GPU + the collective kernels on it.
 
 This is the B200 replacement for the TorchMPI library the reference links against
-(SURVEY §2.4): every rank ``cudaMalloc``s an identically sized heap (followed by a signal
-pad), exchanges CUDA-IPC handles through ``torch.distributed`` (plumbing only) and maps its
-peers' heaps, after which hand-written sm_100a kernels (csrc/comm.cu) do every collective
-with plain loads/stores over NVLink 5 / NVSwitch — no NCCL on this path.
+(SURVEY §2.4): every rank allocates an identically sized heap (followed by a signal pad) and
+maps its peers' heaps, after which hand-written sm_100a kernels (csrc/comm.cu) do every
+collective with plain loads/stores over NVLink 5 / NVSwitch — no NCCL on this path.
+
+Two backends (``TADNN_SYMM_BACKEND=auto|vmm|ipc``).  ``vmm`` (preferred): ``cuMemCreate`` heaps
+shared as POSIX file descriptors over an AF_UNIX socket, plus — where the driver exposes NVLS — a
+multicast object bound over all heaps, which enables the ``multimem`` all-reduce and the in-switch
+reduce-scatter (csrc/comm_vmm.cu).  ``ipc``: ``cudaMalloc`` + CUDA-IPC handles exchanged through
+``torch.distributed`` (plumbing only); chosen automatically if any rank fails the VMM bring-up.
 
 Allocation is a symmetric bump allocator: all ranks must call ``alloc`` in the same order
 with the same sizes (they do: the callers are SPMD).  ``tensor()`` returns a zero-copy
 ``torch.Tensor`` view of heap memory, so model parameters and gradients can *live* in the
-heap (tadnn.parallel.fusion) and be reduced in place.
+heap (tadnn.parallel.fusion) and be reduced in place.  The allocator never frees: long-lived
+buffers only (flat model buffers, per-batch-size layer plans); size it with ``TADNN_SYMM_HEAP_MB``.
 """
 from __future__ import annotations
 
@@ -153,18 +159,30 @@ class SymmContext:
             if self.rank == 0:
                 tok[0] = f"{os.getpid()}-{int.from_bytes(os.urandom(4), 'little')}"
             dist.broadcast_object_list(tok, src=0)
-            rc = lib.tadnn_comm_create_vmm(C.c_int(self.rank), C.c_int(self.world), C.c_ulonglong(self.heap_bytes),
-                                           C.byref(self.handle))
-            if rc != 0:
-                return False, lib.tadnn_last_error().decode()
+            def agree(ok: bool) -> bool:
+                # every phase ends in a vote, so that all ranks leave this function at the same point
+                allok: list = [None] * self.world
+                dist.all_gather_object(allok, bool(ok))
+                return all(allok)
+
+            why = ""
             fd = C.c_int(-1)
-            if lib.tadnn_comm_export_fd(self.handle, C.byref(fd)) != 0:
-                return False, lib.tadnn_last_error().decode()
+            ok = lib.tadnn_comm_create_vmm(C.c_int(self.rank), C.c_int(self.world), C.c_ulonglong(self.heap_bytes),
+                                           C.byref(self.handle)) == 0
+            ok = ok and lib.tadnn_comm_export_fd(self.handle, C.byref(fd)) == 0
+            if not ok:
+                why = lib.tadnn_last_error().decode()
+            if not agree(ok):
+                if fd.value >= 0:
+                    os.close(fd.value)
+                return False, why or "a peer failed to create its VMM heap"
             got = self._fd_exchange(tok[0] + "-heap", {q: fd.value for q in range(self.world) if q != self.rank})
             os.close(fd.value)
-            for q, pfd in got.items():
+            for q, pfd in got.items():  # import_peer_fd owns (and closes) the descriptor in every case
                 if lib.tadnn_comm_import_peer_fd(self.handle, C.c_int(q), C.c_int(pfd)) != 0:
-                    return False, lib.tadnn_last_error().decode()
+                    ok, why = False, lib.tadnn_last_error().decode()
+            if not agree(ok):
+                return False, why or "a peer failed to import a heap"
             # multicast (optional): failure here keeps the VMM heap, just without NVLS
             mc = C.c_int(0)
             lib.tadnn_multicast_supported(C.byref(mc))

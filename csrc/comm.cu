@@ -429,6 +429,9 @@ int validate(const tadnn_comm* c, int channel, const char* what) {
   TADNN_REQUIRE(c != nullptr, "%s: null comm", what);
   TADNN_REQUIRE(channel >= 0 && channel < kChannels, "%s: channel %d out of range [0,%d)", what, channel, kChannels);
   TADNN_REQUIRE(!c->local_set || c->dev.rank < 0, "%s: a local (single-GPU) comm set can only be used through the *_emulated entry points", what);
+  for (int r = 0; r < c->world; ++r)
+    TADNN_REQUIRE(c->dev.heap[r] != nullptr && c->dev.pad[r] != nullptr,
+                  "%s: the heap of rank %d is not mapped yet (tadnn_comm_open_peers / tadnn_comm_import_peer_fd first)", what, r);
   return 0;
 }
 
@@ -502,13 +505,23 @@ extern "C" int tadnn_comm_create(int rank, int world, unsigned long long heap_by
   TADNN_REQUIRE(out != nullptr, "comm_create: null out");
   TADNN_REQUIRE(world >= 1 && world <= kMaxRanks, "comm_create: world %d not in [1,%d]", world, kMaxRanks);
   TADNN_REQUIRE(rank >= 0 && rank < world, "comm_create: rank %d not in [0,%d)", rank, world);
+  *out = nullptr;
   heap_bytes = (heap_bytes + 1023ull) & ~1023ull;
+  int device = 0;
+  void* base = nullptr;
+  TADNN_CHECK_CUDA(cudaGetDevice(&device));
+  TADNN_CHECK_CUDA(cudaMalloc(&base, heap_bytes + kPadBytes));
+  cudaError_t e = cudaMemset(static_cast<uint8_t*>(base) + heap_bytes, 0, kPadBytes);
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    cudaFree(base);
+    set_error("comm_create: zeroing the signal pad failed: %s", cudaGetErrorString(e));
+    return 1;
+  }
   tadnn_comm* c = new tadnn_comm();
   c->rank = rank; c->world = world; c->heap_bytes = heap_bytes;
-  TADNN_CHECK_CUDA(cudaGetDevice(&c->device));
-  TADNN_CHECK_CUDA(cudaMalloc(&c->base, heap_bytes + kPadBytes));
-  TADNN_CHECK_CUDA(cudaMemset(static_cast<uint8_t*>(c->base) + heap_bytes, 0, kPadBytes));
-  TADNN_CHECK_CUDA(cudaDeviceSynchronize());
+  c->device = device;
+  c->base = base;
   c->owns = true;
   memset(&c->dev, 0, sizeof(c->dev));
   c->dev.rank = rank; c->dev.world = world;
@@ -523,7 +536,10 @@ extern "C" int tadnn_comm_create_local(int world, unsigned long long heap_bytes,
   TADNN_REQUIRE(world >= 1 && world <= kMaxRanks, "comm_create_local: world %d not in [1,%d]", world, kMaxRanks);
   for (int r = 0; r < world; ++r) {
     int rc = tadnn_comm_create(r, world, heap_bytes, &out[r]);
-    if (rc) return rc;
+    if (rc) {  // nothing half-built is handed back
+      for (int q = 0; q < r; ++q) { tadnn_comm_destroy(out[q]); out[q] = nullptr; }
+      return rc;
+    }
     out[r]->local_set = true;
   }
   for (int r = 0; r < world; ++r)
@@ -535,7 +551,8 @@ extern "C" int tadnn_comm_create_local(int world, unsigned long long heap_bytes,
 }
 
 extern "C" int tadnn_comm_ipc_handle(tadnn_comm* c, void* host_out64) {
-  TADNN_REQUIRE(c && c->owns && !c->vmm, "comm_ipc_handle: context does not own a cudaMalloc heap");
+  TADNN_REQUIRE(c && host_out64, "comm_ipc_handle: null argument");
+  TADNN_REQUIRE(c->owns && !c->vmm, "comm_ipc_handle: context does not own a cudaMalloc heap");
   static_assert(sizeof(cudaIpcMemHandle_t) == TADNN_IPC_HANDLE_BYTES, "IPC handle size");
   cudaIpcMemHandle_t h;
   TADNN_CHECK_CUDA(cudaIpcGetMemHandle(&h, c->base));

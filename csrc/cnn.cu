@@ -847,8 +847,8 @@ extern "C" int tadnn_head_forward(const tadnn_head_args* h, void* workspace, tad
   const int cap = sm_count() * 2 < 1024 ? sm_count() * 2 : 1024;
   if (blocks > cap) blocks = cap;
   const size_t smem = head_fwd_smem(h->D, h->H, h->NC);
-  static bool attr = false;
-  if (!attr) { TADNN_CHECK_CUDA(cudaFuncSetAttribute(head_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)); attr = true; }
+  static std::atomic<unsigned long long> attr{0};
+  if (int rc = ensure_dyn_smem(head_fwd_kernel, 96 * 1024, attr)) return rc;
   TADNN_REQUIRE(smem <= 96 * 1024, "head_forward: shared memory %zu too large", smem);
   head_fwd_kernel<<<blocks, 256, smem, stream>>>(a);
   TADNN_LAUNCH_CHECK("head_fwd");
@@ -916,8 +916,8 @@ extern "C" int tadnn_head_backward(const tadnn_head_args* h, tadnn_stream_t stre
   int blocks = (h->B + kHeadChunk - 1) / kHeadChunk;
   if (blocks > sm_count()) blocks = sm_count();
   const size_t smem = head_bwd_smem(h->D, h->H, h->NC);
-  static bool attr = false;
-  if (!attr) { TADNN_CHECK_CUDA(cudaFuncSetAttribute(head_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024)); attr = true; }
+  static std::atomic<unsigned long long> attr{0};
+  if (int rc = ensure_dyn_smem(head_bwd_kernel, 160 * 1024, attr)) return rc;
   TADNN_REQUIRE(smem <= 160 * 1024, "head_backward: shared memory %zu too large", smem);
   head_bwd_kernel<<<blocks, 256, smem, stream>>>(a);
   TADNN_LAUNCH_CHECK("head_bwd");

@@ -8,6 +8,8 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <atomic>
+
 #include "../include/tadnn.h"
 
 namespace tadnn {
@@ -49,6 +51,21 @@ int  note_launch(const char* kernel_name);   // bumps the launch counter; return
 inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 
 int sm_count();  // cached multiProcessorCount of the current device
+
+// Opt a kernel into more than 48 KB of dynamic shared memory, once per (call site, device): `done` is a
+// call-site static holding one bit per device ordinal, so a process that drives several GPUs sets the
+// attribute on each of them, and concurrent first calls are harmless (the attribute is idempotent).
+template <typename K>
+inline int ensure_dyn_smem(K kern, int bytes, std::atomic<unsigned long long>& done) {
+  int dev = 0;
+  TADNN_CHECK_CUDA(cudaGetDevice(&dev));
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (!(done.load(std::memory_order_acquire) & bit)) {
+    TADNN_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes));
+    done.fetch_or(bit, std::memory_order_release);
+  }
+  return 0;
+}
 
 // ---- device helpers ---------------------------------------------------------
 __device__ __forceinline__ float bf16_to_f32(__nv_bfloat16 v) { return __bfloat162float(v); }

@@ -497,8 +497,8 @@ extern "C" int tadnn_conv1_pool_forward(const void* x, const void* w_packed, con
                                         tadnn_stream_t stream) {
   TADNN_REQUIRE(B > 0 && B <= 20000000, "conv1_pool_forward: batch %d out of range", B);
   TADNN_REQUIRE(((reinterpret_cast<uintptr_t>(w_packed) | reinterpret_cast<uintptr_t>(p1)) & 15) == 0, "conv1_pool_forward: operands must be 16-byte aligned");
-  static bool attr = false;
-  if (!attr) { TADNN_CHECK_CUDA(cudaFuncSetAttribute(conv1_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kFwdSmem)); attr = true; }
+  static std::atomic<unsigned long long> attr{0};
+  if (int rc = ensure_dyn_smem(conv1_fwd_kernel, kFwdSmem, attr)) return rc;
   Conv1Args a;
   memset(&a, 0, sizeof(a));
   a.x = static_cast<const __nv_bfloat16*>(x); a.w = static_cast<const __nv_bfloat16*>(w_packed); a.bias = bias;
@@ -516,12 +516,9 @@ extern "C" int tadnn_conv1_pool_backward(const void* x, const void* dp1, int dp1
   TADNN_REQUIRE(dp1_h >= 1 && dp1_h <= kPH && dp1_w >= 1 && dp1_w <= kPW, "conv1_pool_backward: dp1 extent %dx%d out of range", dp1_h, dp1_w);
   TADNN_REQUIRE(((reinterpret_cast<uintptr_t>(dp1) | reinterpret_cast<uintptr_t>(p1) | reinterpret_cast<uintptr_t>(idx1)) & 15) == 0,
                 "conv1_pool_backward: operands must be 16-byte aligned");
-  static bool attr = false;
-  if (!attr) {
-    TADNN_CHECK_CUDA(cudaFuncSetAttribute(conv1_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
-    TADNN_CHECK_CUDA(cudaFuncSetAttribute(conv1_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBwdSmem));
-    attr = true;
-  }
+  static std::atomic<unsigned long long> attr_full{0}, attr_compact{0};
+  if (int rc = ensure_dyn_smem(conv1_bwd_kernel<false>, kBwdSmem, attr_full)) return rc;
+  if (int rc = ensure_dyn_smem(conv1_bwd_kernel<true>, kBwdSmem, attr_compact)) return rc;
   Conv1Args a;
   memset(&a, 0, sizeof(a));
   a.x = static_cast<const __nv_bfloat16*>(x); a.dp1 = static_cast<const __nv_bfloat16*>(dp1);

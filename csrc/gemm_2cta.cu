@@ -305,8 +305,8 @@ extern "C" int tadnn_gemm_bf16_2cta(const void* A, int lda, const void* B, int l
   if (int rc = make_tmap2(&ta, A, M, K, lda, BM)) return rc;
   if (int rc = make_tmap2(&tb, B, N, K, ldb, BNH)) return rc;
   if (int rc = make_tmap2(&tc, C, M, N, ldc, 32)) return rc;
-  static bool attr = false;
-  if (!attr) { TADNN_CHECK_CUDA(cudaFuncSetAttribute(gemm_bf16_2cta_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemBytes)); attr = true; }
+  static std::atomic<unsigned long long> attr{0};
+  if (int rc = ensure_dyn_smem(gemm_bf16_2cta_kernel, kSmemBytes, attr)) return rc;
   Args2 p;
   p.M = M; p.N = N; p.K = K; p.bias = bias; p.act = act; p.alpha = alpha;
   const int num_m = ceil_div(M, 2 * BM), num_n = ceil_div(N, BN);

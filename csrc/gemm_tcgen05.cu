@@ -501,11 +501,8 @@ int launch(const tadnn_gemm_args* a, const DevArgs& d, cudaStream_t stream) {
   rc = B_MN ? make_tmap(&tb, a->B, a->K, a->N, a->ldb, BK) : make_tmap(&tb, a->B, a->N, a->K, a->ldb, BN);
   if (rc) return rc;
   auto kern = gemm_bf16_tcgen05_kernel<A_MN, B_MN, BN, AUX>;
-  static bool attr_set = false;  // per instantiation
-  if (!attr_set) {
-    TADNN_CHECK_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, C::kSmemBytes));
-    attr_set = true;
-  }
+  static std::atomic<unsigned long long> attr_set{0};  // per instantiation, one bit per device
+  if (int arc = ensure_dyn_smem(kern, C::kSmemBytes, attr_set)) return arc;
   const int num_m = ceil_div(a->M, BM), num_n = ceil_div(a->N, BN);
   const int splits = d.split_k > 1 ? d.split_k : 1;
   const int work = num_m * num_n * splits;

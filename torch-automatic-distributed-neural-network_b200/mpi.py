@@ -18,6 +18,9 @@ Backends
   bootstrap/baseline).  CUDA tensors are reduced by the hand-written sm_100a kernels in
   ``tadnn.parallel.symm`` when a symmetric-memory context is up; NCCL is the baseline path
   (``TADNN_FORCE_PATH=nccl``).
+* ``handle.split(color, key)`` / ``mesh(tp_size)`` — sub-communicators with the same API (both
+  backends), which is what lets ``parallelize`` (over the DP communicator) and the ``MP*`` layers
+  (over the TP communicator) be combined; the reference has one communicator and cannot.
 * ``FakeWorld`` / ``FakeMPI`` — P ranks as P threads of one process with a list-of-tensors
   communicator; deterministic; used by the oracle and the unit tests.
 """
@@ -34,7 +37,7 @@ import torch
 __all__ = [
     "TorchMPI", "FakeMPI", "FakeWorld", "start", "stop", "rank", "size", "barrier",
     "allreduceTensor", "allgatherTensor", "broadcastTensor", "current", "set_current",
-    "started",
+    "started", "mesh",
 ]
 
 _tls = threading.local()
@@ -107,7 +110,8 @@ class TorchMPI(_Handle):
         self._started = False
         self._owns_pg = False
         self._use_gpu = False
-        self._group = None
+        self._group = None   # None = the world; else the torch.distributed group of a split() handle
+        self._ranks: Optional[List[int]] = None  # global ranks of the group's members, in group-rank order
         self.symm = None  # tadnn.parallel.symm.SymmContext once the GPU fabric is up
 
     # -- lifecycle -------------------------------------------------------------
@@ -153,8 +157,39 @@ class TorchMPI(_Handle):
             _default = self
         return self
 
+    def split(self, color: int, key: Optional[int] = None) -> "TorchMPI":
+        """``MPI_Comm_split``: ranks that pass the same ``color`` form a new communicator, ordered by
+        ``key`` (default: the rank in this one).  Collective over this handle.  The sub-handle has the
+        same API (group-relative ``rank()``/``size()``); its collectives go through ``torch.distributed``
+        on the sub-group (gloo / NCCL) — the symmetric-memory kernels serve the world communicator.
+        Not in the reference (its DP and MP paths share the world communicator); this is
+        what makes a DP x TP mesh expressible: see :func:`mesh`."""
+        import torch.distributed as dist
+        assert self._started, "split() needs a started handle"
+        P = self.size()
+        me = (int(color), int(self.rank() if key is None else key), dist.get_rank())
+        everyone: list = [None] * P
+        dist.all_gather_object(everyone, me, group=self._group)
+        ranks = [g for _c, _k, g in sorted(e for e in everyone if e[0] == me[0])]
+        sub = TorchMPI()
+        sub._started, sub._use_gpu = True, self._use_gpu
+        sub._ranks = ranks
+        # only the members create their group (no world-wide call needed, so sub-handles can be split again)
+        sub._group = dist.new_group(ranks, use_local_synchronization=True) if len(ranks) > 1 else None
+        if self.needInterNodeCollectives:
+            hosts: list = [None] * len(ranks)
+            if sub._group is not None:
+                dist.all_gather_object(hosts, socket.gethostname(), group=sub._group)
+            sub.needInterNodeCollectives = len(set(hosts)) > 1
+        return sub
+
     def stop(self):
         import torch.distributed as dist
+        if self._ranks is not None:  # a split() handle: drop the sub-group only
+            if self._group is not None and dist.is_initialized():
+                dist.destroy_process_group(self._group)
+            self._group, self._started = None, False
+            return
         if self.symm is not None:
             self.symm.close()
             self.symm = None
@@ -177,11 +212,19 @@ class TorchMPI(_Handle):
     # -- queries ---------------------------------------------------------------
     def rank(self) -> int:
         import torch.distributed as dist
+        if self._ranks is not None:
+            return self._ranks.index(dist.get_rank())
         return dist.get_rank() if dist.is_initialized() else 0
 
     def size(self) -> int:
         import torch.distributed as dist
+        if self._ranks is not None:
+            return len(self._ranks)
         return dist.get_world_size() if dist.is_initialized() else 1
+
+    def global_rank(self, group_rank: int) -> int:
+        """World rank of member ``group_rank`` of this communicator."""
+        return self._ranks[group_rank] if self._ranks is not None else group_rank
 
     def device(self) -> torch.device:
         return torch.device("cuda", torch.cuda.current_device()) if self._use_gpu else torch.device("cpu")
@@ -189,14 +232,14 @@ class TorchMPI(_Handle):
     # -- collectives -----------------------------------------------------------
     def barrier(self):
         import torch.distributed as dist
-        if dist.is_initialized() and dist.get_world_size() > 1:
+        if dist.is_initialized() and self.size() > 1:
             if self._use_gpu:
                 torch.cuda.synchronize()
                 if self.symm is not None:
                     self.symm.barrier()
                     torch.cuda.synchronize()
                     return
-            dist.barrier()
+            dist.barrier(group=self._group)
 
     def allreduceTensor(self, t: torch.Tensor) -> torch.Tensor:
         """In-place sum over all ranks (nodemodule.lua:52, datamodule.lua:216)."""
@@ -207,10 +250,10 @@ class TorchMPI(_Handle):
             self.symm.allreduce_(t, scale=1.0)
             return t
         if t.is_contiguous():
-            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self._group)
         else:
             c = t.contiguous()
-            dist.all_reduce(c, op=dist.ReduceOp.SUM)
+            dist.all_reduce(c, op=dist.ReduceOp.SUM, group=self._group)
             t.copy_(c)
         return t
 
@@ -226,7 +269,7 @@ class TorchMPI(_Handle):
             self.symm.allgather_lastdim(inp, out)
             return out
         parts = [torch.empty_like(inp, memory_format=torch.contiguous_format) for _ in range(P)]
-        dist.all_gather(parts, inp.contiguous())
+        dist.all_gather(parts, inp.contiguous(), group=self._group)
         out.copy_(torch.cat(parts, dim=-1).reshape(out.shape))
         return out
 
@@ -234,11 +277,12 @@ class TorchMPI(_Handle):
         import torch.distributed as dist
         if self.size() == 1:
             return t
+        src = self.global_rank(root)  # torch.distributed wants the world rank of the source
         if t.is_contiguous():
-            dist.broadcast(t, src=root)
+            dist.broadcast(t, src=src, group=self._group)
         else:
             c = t.contiguous()
-            dist.broadcast(c, src=root)
+            dist.broadcast(c, src=src, group=self._group)
             t.copy_(c)
         return t
 
@@ -258,6 +302,7 @@ class FakeWorld:
         self.calls = {"allreduce": 0, "allgather": 0, "broadcast": 0, "barrier": 0}
         self.bytes = 0
         self._stat_lock = threading.Lock()
+        self._subworlds: dict = {}  # (split epoch, color) -> FakeWorld shared by that colour's ranks
 
     def handle(self, rank: int) -> "FakeMPI":
         return FakeMPI(rank, self)
@@ -304,6 +349,27 @@ class FakeMPI(_Handle):
         self._rank = rank
         self._world = world
         self.symm = None
+        self._nsplit = 0
+
+    def split(self, color: int, key: Optional[int] = None) -> "FakeMPI":
+        """``MPI_Comm_split`` among the threads of this FakeWorld (see :meth:`TorchMPI.split`)."""
+        w = self._world
+        w._slots[self._rank] = (int(color), int(self._rank if key is None else key), self._rank)
+        w._bar.wait()
+        everyone = list(w._slots)
+        w._bar.wait()
+        ranks = [r for _c, _k, r in sorted(e for e in everyone if e[0] == int(color))]
+        epoch = self._nsplit  # every rank splits in the same order, so the counter agrees
+        self._nsplit += 1
+        with w._stat_lock:
+            sub = w._subworlds.setdefault((epoch, int(color)), FakeWorld(len(ranks)))
+        h = FakeMPI(ranks.index(self._rank), sub)
+        h._ranks = ranks
+        return h
+
+    def global_rank(self, group_rank: int) -> int:
+        ranks = getattr(self, "_ranks", None)
+        return ranks[group_rank] if ranks is not None else group_rank
 
     started = True
     use_gpu = False
@@ -421,6 +487,20 @@ def allgatherTensor(inp, out):
 
 def broadcastTensor(root, t):
     return current().broadcastTensor(root, t)
+
+
+def mesh(tp_size: int, handle=None):
+    """Split ``handle`` (default: the current one) into a DP x TP mesh and return ``(dp, tp)``:
+    ``tp`` joins ``tp_size`` consecutive ranks (the model-parallel group: pass it to the ``MP*`` layers),
+    ``dp`` joins the ranks that hold the same shard in every such group (pass it to ``parallelize`` /
+    ``synchronizeModel``).  The reference cannot combine its two modes because both use the world
+    communicator (SURVEY §2.3 "Hybrid DP x TP"); with two communicators they compose."""
+    h = handle if handle is not None else current()
+    P, r = h.size(), h.rank()
+    assert tp_size >= 1 and P % tp_size == 0, f"world size {P} is not a multiple of tp_size {tp_size}"
+    tp = h.split(r // tp_size, r % tp_size)
+    dp = h.split(r % tp_size, r // tp_size)
+    return dp, tp
 
 
 def __getattr__(name):  # module-level attribute access for the two TorchMPI fields

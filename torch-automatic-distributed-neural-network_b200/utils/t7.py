@@ -228,6 +228,42 @@ class _Writer:
         self.memo: Dict[int, int] = {}
         self.keep = []  # keep ids alive
         self.next = 1
+        # storage sharing (Torch7 memoises storages, so views of one buffer -- e.g. everything behind
+        # getParameters() -- stay views after a save/load): key -> [lo, hi, referenced elements], then
+        # key -> T7Storage of that window once it has been materialised
+        self.windows: Dict[Any, list] = {}
+        self.storages: Dict[Any, "T7Storage"] = {}
+
+    @staticmethod
+    def _skey(t: torch.Tensor):
+        return (t.untyped_storage().data_ptr(), t.dtype, str(t.device))
+
+    @staticmethod
+    def _extent(t: torch.Tensor):
+        lo = t.storage_offset()
+        return lo, lo + 1 + sum((n - 1) * st for n, st in zip(t.shape, t.stride()))
+
+    def plan(self, o, seen=None):
+        """Pre-pass over the object graph: the element window of every underlying storage that the
+        tensors to be written actually cover."""
+        seen = set() if seen is None else seen
+        if id(o) in seen:
+            return
+        seen.add(id(o))
+        if isinstance(o, torch.Tensor):
+            if o.numel() > 0:
+                lo, hi = self._extent(o)
+                w = self.windows.setdefault(self._skey(o), [lo, hi, 0])
+                w[0], w[1], w[2] = min(w[0], lo), max(w[1], hi), w[2] + o.numel()
+        elif isinstance(o, dict):
+            for k, v in o.items():
+                self.plan(k, seen)
+                self.plan(v, seen)
+        elif isinstance(o, (list, tuple)) and not isinstance(o, torch.Size):
+            for v in o:
+                self.plan(v, seen)
+        elif isinstance(o, T7Object):
+            self.plan(o.fields, seen)
 
     def ints(self, vals):
         if self.ascii:
@@ -324,29 +360,48 @@ class _Writer:
         self.ints([TYPE_TORCH])
         if self._index(t) is None:
             return
-        src = t.detach().cpu()
-        if src.dtype == torch.bfloat16:
-            src = src.float()
-        a = src.contiguous().numpy()
-        kind = _NP_TO_T7[a.dtype]
+        src = t.detach()
+        if src.dim() == 0:
+            src = src.reshape(1)  # Torch7 has no 0-dimensional tensors: a scalar becomes a 1-element vector
+        nd = src.dim() if src.numel() > 0 else 0
+        key = self._skey(src) if nd > 0 else None
+        win = self.windows.get(key) if nd > 0 else None
+        # share the underlying storage unless the window is mostly data nobody references (a small
+        # tensor carved out of a big arena): then the tensor gets a compact storage of its own
+        share = win is not None and (win[1] - win[0]) <= 4 * win[2] + 1024
+        if nd > 0 and share:
+            st = self.storages.get(key)
+            if st is None:
+                flat = torch.as_strided(src, (win[1] - win[0],), (1,), win[0]).cpu()
+                if flat.dtype == torch.bfloat16:
+                    flat = flat.float()
+                a = flat.contiguous().numpy()
+                st = self.storages[key] = T7Storage(a, _NP_TO_T7[a.dtype])
+            kind, shape, strides, off = st.kind, list(src.shape), list(src.stride()), src.storage_offset() - win[0] + 1
+        else:
+            c = src.cpu()
+            if c.dtype == torch.bfloat16:
+                c = c.float()
+            a = c.contiguous().numpy()
+            kind = _NP_TO_T7[a.dtype]
+            shape, strides, off = list(a.shape), [int(x // a.itemsize) for x in a.strides], 1
+            st = T7Storage(a.reshape(-1), kind) if nd > 0 else None
         self.string("V 1")
         self.string(f"torch.{kind}Tensor")
-        nd = a.ndim if a.size > 0 else 0
         self.ints([nd])
         if nd == 0:
             self.longs([1])  # storageOffset
             self.obj(None)
             return
-        self.longs(list(a.shape))
-        strides = [int(s // a.itemsize) for s in a.strides]
+        self.longs(shape)
         self.longs(strides)
-        self.longs([1])
-        st = T7Storage(a.reshape(-1), kind)
+        self.longs([off])
         self.obj(st)
 
 
 def dumps(obj, mode: str = "binary") -> bytes:
     w = _Writer(mode == "ascii")
+    w.plan(obj)
     w.obj(obj)
     return w.out.getvalue()
 

@@ -5,8 +5,9 @@ CIFAR-10-shaped CNN, automatic data parallelism through parallelize().
     python examples/cifar_dp.py                       # CPU, 1 rank, reference defaults (tiny)
 
 Same 8 flags and defaults as the Lua script (:29-43), same results-file fields (:277-299), the
-confusion matrix of :266-275.  There is no network on this box, so the dataset is synthetic
-CIFAR-shaped data (class-dependent mean, learnable); -data selects 32000/10000 instead of
+confusion matrix of :266-275.  --dataDir points at the reference's dataset files
+(cifar-10-batches-t7/*.t7, :133-169); without it (there is no network on this box) the dataset is
+synthetic CIFAR-shaped data (class-dependent mean, learnable).  -data selects 32000/10000 instead of
 4000/2000 samples as in the reference (:124-130).  Preprocessing (rgb2yuv, U/V standardisation with
 the training shard's statistics, Y contrast normalisation, :182-216) runs after parallelize() as in
 the reference — through the native kernels of csrc/preprocess.cu on a GPU, the tensor implementation
@@ -26,6 +27,7 @@ from tadnn import nn  # noqa: E402
 from tadnn.models import CifarCNN  # noqa: E402
 from tadnn.utils import config as cfg  # noqa: E402
 from tadnn.utils import preprocess as prep  # noqa: E402
+from tadnn.utils.cifar import load_cifar10_t7  # noqa: E402
 from tadnn.utils.confusion import ConfusionMatrix  # noqa: E402
 from tadnn.utils.logging import log, write_results_file  # noqa: E402
 from tadnn.utils.timing import Tic  # noqa: E402
@@ -53,8 +55,12 @@ def main():
     model = CifarCNN(seed=opt.seed)
     if use_gpu:
         model = model.to(dev)            # :239-245 (moved before parallelize so the flat buffer is symmetric)
-    train_x, train_y = synthetic_cifar(opt.trsize, opt.seed)
-    test_x, test_y = synthetic_cifar(opt.tesize, opt.seed + 1)
+    if opt.dataDir:
+        # :133-169 — the Torch7 batch files the reference downloads; here they must already be on disk
+        train_x, train_y, test_x, test_y = load_cifar10_t7(opt.dataDir, opt.trsize, opt.tesize)
+    else:
+        train_x, train_y = synthetic_cifar(opt.trsize, opt.seed)
+        test_x, test_y = synthetic_cifar(opt.tesize, opt.seed + 1)
     if use_gpu:
         train_x, test_x = train_x.bfloat16(), test_x.bfloat16()
     # :172 — the one call

@@ -1,4 +1,6 @@
 """Preprocessing (cifar example :182-216) and checkpoint/resume utilities."""
+import os
+
 import torch
 
 import tadnn
@@ -60,3 +62,26 @@ def test_checkpoint_per_rank_for_model_parallel(tmp_path):
         return (m(x) - m2(x)).abs().max().item()
 
     assert max(world.run(body)) == 0.0
+
+
+def test_cifar10_t7_batches_roundtrip_and_errors(tmp_path):
+    """The on-disk format of the reference's dataset (sgd-torchad_nn-cifar.lua:133-169): ASCII .t7 tables,
+    data [3072, n] bytes with one image per column, labels [1, n]."""
+    import pytest
+    from tadnn.utils import cifar, t7
+    g = torch.Generator().manual_seed(0)
+    trx = torch.randint(0, 256, (250, 3, 32, 32), generator=g, dtype=torch.uint8)
+    try_ = torch.randint(0, 10, (250,), generator=g)
+    tex = torch.randint(0, 256, (60, 3, 32, 32), generator=g, dtype=torch.uint8)
+    tey = torch.randint(0, 10, (60,), generator=g)
+    d = cifar.write_cifar10_t7(str(tmp_path), trx, try_, tex, tey, batch=100)
+    raw = t7.load(os.path.join(d, "data_batch_2.t7"), "ascii")
+    assert tuple(raw["data"].shape) == (3072, 100) and raw["data"].dtype == torch.uint8  # one image per column
+    assert torch.equal(raw["data"][:, 0], trx[100].reshape(-1))
+    a, b, c, e = cifar.load_cifar10_t7(str(tmp_path), 230, 50)  # spans three training batches
+    assert torch.equal(a, trx[:230].float()) and torch.equal(b, try_[:230])
+    assert torch.equal(c, tex[:50].float()) and torch.equal(e, tey[:50]) and e.dtype == torch.int64
+    with pytest.raises(ValueError):
+        cifar.load_cifar10_t7(str(tmp_path), 251, 50)
+    with pytest.raises(FileNotFoundError):
+        cifar.load_cifar10_t7(str(tmp_path / "nowhere"), 10, 10)

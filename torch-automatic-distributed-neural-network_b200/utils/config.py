@@ -47,6 +47,7 @@ class TrainConfig:
     dtype: str = "bf16"
     model: str = "cifar_cnn"
     results_dir: str = "."
+    dataDir: Optional[str] = None  # directory with cifar-10-batches-t7 (the reference's dataset files); None = synthetic
     preprocess: str = "yuv"       # "yuv": rgb2yuv + contrast normalisation as in the example (:182-216); "none": skip
 
     @property
@@ -71,6 +72,9 @@ def add_reference_flags(ap: argparse.ArgumentParser) -> argparse.ArgumentParser:
     ap.add_argument("--miniBatch", type=int, default=d.miniBatch)
     ap.add_argument("--dtype", default=d.dtype, choices=["bf16", "fp32"])
     ap.add_argument("--results-dir", default=d.results_dir)
+    ap.add_argument("--dataDir", default=d.dataDir,
+                    help="directory holding cifar-10-batches-t7 (Torch7 ASCII batches, as the reference reads them); "
+                         "default: synthetic CIFAR-shaped data")
     ap.add_argument("--preprocess", default=d.preprocess, choices=["yuv", "none"],
                     help="dataset preprocessing of the example (rgb2yuv, U/V standardisation, Y contrast normalisation)")
     return ap

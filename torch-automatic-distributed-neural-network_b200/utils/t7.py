@@ -20,6 +20,7 @@ from __future__ import annotations
 
 import io
 import struct
+import warnings
 from typing import Any, Dict, Optional
 
 import numpy as np
@@ -135,6 +136,23 @@ class _Reader:
     def array(self, n: int, np_dtype) -> np.ndarray:
         dt = np.dtype(np_dtype)
         if self.ascii:
+            if n >= 64:
+                # Torch7 writes an array as one line of space-separated numbers: parse the line in C
+                # (a CIFAR batch is 30.7 M tokens; the per-token loop below would take a minute)
+                b, i = self.b, self.pos
+                while i < len(b) and b[i] in b" \t\r\n":
+                    i += 1
+                nl = b.find(b"\n", i)
+                nl = len(b) if nl < 0 else nl
+                with warnings.catch_warnings():
+                    warnings.simplefilter("ignore")
+                    try:
+                        a = np.fromstring(b[i:nl], dtype=np.float64 if dt.kind == "f" else np.int64, sep=" ")
+                    except Exception:  # noqa: BLE001 - any parser problem: take the token loop
+                        a = None
+                if a is not None and a.size == n:
+                    self.pos = nl
+                    return a.astype(dt)
             if dt.kind == "f":
                 return np.array([float(self._token()) for _ in range(n)], dtype=dt)
             return np.array([int(self._token()) for _ in range(n)], dtype=dt)

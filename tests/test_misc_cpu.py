@@ -92,3 +92,13 @@ def test_fake_world_collective_mismatch_times_out_cleanly():
         assert False
     except RuntimeError as e:
         assert "rank 0 died" in str(e)
+
+
+def test_python_dash_m_tadnn_describes_the_installation():
+    import json
+    p = subprocess.run([sys.executable, "-m", "tadnn"], capture_output=True, text=True, timeout=300, cwd=ROOT,
+                       env=dict(os.environ, TADNN_PRINT_DIMS="1"))
+    assert p.returncode == 0, p.stderr[-1500:]
+    d = json.loads(p.stdout)
+    assert d["native"]["built"] and d["native"]["missing_entry_points"] == [] and d["native"]["entry_points"] > 50
+    assert d["env"] == {"TADNN_PRINT_DIMS": "1"} and "gpus" in d["devices"]

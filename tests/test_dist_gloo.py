@@ -52,7 +52,17 @@ def _worker(rank, world, port, out_dir):
     h.start(False, backend="gloo", rank=rank, world_size=world)
     tmpi.set_current(h)
     flat, n, syncs = _train(h)
-    torch.save({"flat": flat, "n": n, "syncs": syncs, "sel": callable(
+    # async half of the selector table (TorchMPI's handle API): start, overlap host work, then syncHandle
+    t = torch.full((1000,), float(rank + 1))
+    b = torch.full((7,), float(rank))
+    ha = h.collectiveSelector["cpu"]["singlenode"]["async"]["allreduceTensor"](t)
+    hb = h.collectiveSelector["cpu"]["singlenode"]["async"]["broadcastTensor"](1, b)
+    busy = sum(i for i in range(1000))  # host work while the collectives are in flight
+    h.syncHandle(ha)
+    h.syncHandle(hb)
+    async_ok = bool(busy and torch.all(t == sum(range(1, world + 1))) and torch.all(b == 1.0)
+                    and type(ha).__name__ == "_WorkHandle")
+    torch.save({"flat": flat, "n": n, "syncs": syncs, "async_ok": async_ok, "sel": callable(
         tadnn.selectCollective(flat, "sync", "allreduceTensor", h)), "inter": h.needInterNodeCollectives},
         os.path.join(out_dir, f"r{rank}.pt"))
     h.stop()
@@ -66,6 +76,7 @@ def test_mlp_dp_gloo_world2_matches_fakeworld(tmp_path):
     r1 = torch.load(tmp_path / "r1.pt")
     assert r0["n"] == r1["n"] == 6 and r0["syncs"] == r1["syncs"] == 3
     assert r0["sel"] and r0["inter"] is False
+    assert r0["async_ok"] and r1["async_ok"]
     assert torch.allclose(r0["flat"], r1["flat"], atol=1e-6)  # last sample synced (counter == size)
     fake = tmpi.FakeWorld(2).run(_train)
     assert torch.allclose(fake[0][0], r0["flat"], atol=1e-5)

@@ -91,12 +91,31 @@ class _Handle:
     def broadcast_tensor(self, root, t):
         return self.broadcastTensor(root, t)
 
-    def syncHandle(self, h):  # TorchMPI async API; our async collectives complete in-stream
-        return h
+    def syncHandle(self, h):
+        """TorchMPI's ``mpi.syncHandle(handle)``: block until the asynchronous collective is complete."""
+        return h.wait() if h is not None else None
 
 
 class _DoneHandle:
+    """Handle of a collective that needs no further waiting: FakeWorld collectives are synchronous, and
+    a CUDA collective is already asynchronous with respect to the host (it is ordered on the stream)."""
+
     def wait(self):
+        return self
+
+
+class _WorkHandle(_DoneHandle):
+    """An in-flight ``torch.distributed`` operation (CPU / gloo)."""
+
+    def __init__(self, work, after=None):
+        self._work, self._after = work, after
+
+    def wait(self):
+        if self._work is not None:
+            self._work.wait()
+            self._work = None
+            if self._after is not None:
+                self._after()
         return self
 
 
@@ -113,6 +132,25 @@ class TorchMPI(_Handle):
         self._group = None   # None = the world; else the torch.distributed group of a split() handle
         self._ranks: Optional[List[int]] = None  # global ranks of the group's members, in group-rank order
         self.symm = None  # tadnn.parallel.symm.SymmContext once the GPU fabric is up
+
+    def _make_async(self, fn):
+        """The ``async`` half of the selector table.  CPU tensors: the collective is started with
+        ``async_op=True`` and the handle's ``wait()`` / ``mpi.syncHandle`` completes it, so host work can
+        overlap the transfer.  CUDA tensors: the collective is enqueued on the current stream like the
+        sync variant — the host does not block either way, and stream order gives the dependency."""
+        name = fn.__name__
+
+        def run(*a, **k):
+            import torch.distributed as dist
+            t = a[1] if name == "broadcastTensor" else a[0]
+            if (name in ("allreduceTensor", "broadcastTensor") and torch.is_tensor(t) and not t.is_cuda
+                    and t.is_contiguous() and dist.is_initialized() and self.size() > 1):
+                if name == "allreduceTensor":
+                    return _WorkHandle(dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self._group, async_op=True))
+                return _WorkHandle(dist.broadcast(t, src=self.global_rank(a[0]), group=self._group, async_op=True))
+            fn(*a, **k)
+            return _DoneHandle()
+        return run
 
     # -- lifecycle -------------------------------------------------------------
     def start(self, use_gpu: bool = True, backend: Optional[str] = None, *, rank: Optional[int] = None,

@@ -48,7 +48,7 @@ def _same(a, b):
     return a == b
 
 
-@settings(max_examples=150, deadline=None)
+@settings(max_examples=150, deadline=None, derandomize=True)
 @given(obj=values, mode=st.sampled_from(["binary", "ascii"]))
 def test_roundtrip_of_arbitrary_nested_values(obj, mode):
     back = t7.loads(t7.dumps(obj, mode), mode)
@@ -67,7 +67,7 @@ def test_shared_tensor_is_written_once_and_stays_shared(mode):
     assert back["view"][2] == -7.0           # a view of the same storage
 
 
-@settings(max_examples=80, deadline=None)
+@settings(max_examples=150, deadline=None, derandomize=True)
 @given(obj=values, cut=st.floats(0.0, 0.98))
 def test_truncated_binary_input_raises(obj, cut):
     blob = t7.dumps(obj, "binary")
@@ -82,7 +82,7 @@ def test_truncated_binary_input_raises(obj, cut):
     assert not isinstance(obj, dict) and not torch.is_tensor(obj) or _same(obj, back)
 
 
-@settings(max_examples=60, deadline=None)
+@settings(max_examples=150, deadline=None, derandomize=True)
 @given(junk=st.binary(min_size=0, max_size=64))
 def test_random_bytes_never_hang_or_crash_the_interpreter(junk):
     try:

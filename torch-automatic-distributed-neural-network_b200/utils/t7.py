@@ -129,6 +129,8 @@ class _Reader:
         if self.ascii:
             if self.pos < len(self.b) and self.b[self.pos:self.pos + 1] in (b"\n", b" "):
                 self.pos += 1
+        if n < 0 or self.pos + n > len(self.b):
+            raise EOFError(f".t7 stream ends inside a {n}-byte string at byte {self.pos}")
         s = self.b[self.pos:self.pos + n]
         self.pos += n
         return s.decode("latin-1")

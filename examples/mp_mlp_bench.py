@@ -32,6 +32,7 @@ def main():
     ap.add_argument("--out", default="gpurun_out")
     ap.add_argument("--reduce", default="", choices=["", "push", "nvls"], help="forward reduction of FusedMPMLP (default: its own default)")
     ap.add_argument("--chunks", type=int, default=0, help="row chunks of the NVLS pipeline")
+    ap.add_argument("--fused-loss", action="store_true", help="bf16 model output + the fused MSE kernel (ops/loss.py) instead of fp32 torch ops")
     ap.add_argument("--phases", action="store_true", help="also time forward / backward / update separately")
     a = ap.parse_args()
     if a.impl == "nccl":
@@ -65,9 +66,14 @@ def main():
     xs = [torch.randn(B, sizes[0], device=dev).bfloat16() for _ in range(4)]
     tg = torch.randn(B, sizes[-1], device=dev)
 
+    fused_loss = a.fused_loss and a.impl == "tadnn"
+    if fused_loss:
+        from tadnn.ops.loss import mse_fused
+        model.out_bf16 = True
+
     def step(i):
         y = model(xs[i % 4]) if a.impl == "tadnn" else torch.nn.Sequential.forward(model, xs[i % 4])
-        loss = ((y.float() - tg) ** 2).mean()
+        loss = mse_fused(y, tg) if fused_loss else ((y.float() - tg) ** 2).mean()
         loss.backward()
         with torch.no_grad():
             torch._foreach_add_(params, [p.grad for p in params], alpha=-1e-4)
@@ -128,7 +134,7 @@ def main():
     t_compute = flops / (peaks["bf16_tflops_sustained"] * 1e12) * 1e3
     t_link = nvl / 770e9 * 1e3
     if rank == 0:
-        res = {"config": a.config, "impl": a.impl, "reduce": (model.reduce_mode if a.impl == "tadnn" else None),
+        res = {"config": a.config, "impl": a.impl, "fused_loss": bool(a.fused_loss), "reduce": (model.reduce_mode if a.impl == "tadnn" else None),
                "chunks": (model.nvls_chunks if a.impl == "tadnn" else None), "world": P, "batch": B, "sizes": sizes, "ms_per_step": ms,
                "samples_per_s": B / ms * 1e3, "tflops_per_gpu": flops / ms / 1e9,
                "roofline_ms": max(t_compute, t_link), "compute_ms_at_measured_peak": t_compute,

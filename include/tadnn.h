@@ -323,6 +323,13 @@ int tadnn_linear_smalln_dgrad(const void* g, int ldg, const void* W, int ldw, co
 int tadnn_linear_smalln_wgrad(const void* g, int ldg, const void* x, int ldx, float* dW, int lddw, float* db,
                               int M, int N, int K, int accumulate, tadnn_stream_t stream);
 
+/* ---- fused MSE criterion (csrc/loss.cu) ----------------------------------------------------------
+ * nn.MSECriterion forward + updateGradInput (datamodule.lua:139-141) in one pass over a bf16 output:
+ * loss[0] = scale_loss * sum (y - t)^2, grad = scale_grad * (y - t) as bf16 (grad may be NULL).
+ * target is bf16 (target_fp32 = 0) or fp32 (1).  All pointers 16-byte aligned. */
+int tadnn_mse_loss_grad(const void* y, const void* target, int target_fp32, void* grad, float* loss,
+                        long long n, float scale_loss, float scale_grad, tadnn_stream_t stream);
+
 /* ---- dataset preprocessing (csrc/preprocess.cu) -------------------------------------------------
  * cifar_example/sgd-torchad_nn-cifar.lua:182-216: rgb2yuv, U/V standardised with the training
  * shard's mean/std, Y through SpatialContrastiveNormalization(1, gaussian1D(7)).  rgb is fp32

@@ -11,3 +11,4 @@ if ROOT not in sys.path:
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
     config.addinivalue_line("markers", "multigpu: needs >= 2 CUDA devices")
+    config.addinivalue_line("markers", "wip: GPU test of code that has not had its first run on a B200 yet (not part of -m gpu)")

@@ -134,7 +134,7 @@ class _Fn(torch.autograd.Function):
                 if nch > 1:
                     main.wait_event(side.record_event())
                 if last:
-                    out = part.float()  # the owners multimem.st their column blocks into every rank's buffer
+                    out = mod._finish(part)  # the owners multimem.st their column blocks into every rank's buffer
                 a = nxt
             elif o % (64 * P) == 0:
                 w = o // P
@@ -149,7 +149,7 @@ class _Fn(torch.autograd.Function):
                     C.c_void_p(nxt.data_ptr()), C.c_ulonglong(w), C.c_ulonglong(plan.gfull_off), int(last), 0, 0,
                     _symm.CH_TP, st), "tadnn_reduce_slots")
                 if last:
-                    out = sc.tensor(plan.gfull_off, (B, o), torch.bfloat16).float()
+                    out = mod._finish(sc.tensor(plan.gfull_off, (B, o), torch.bfloat16))
                 a = nxt
             else:
                 part = plan.small[:B * o].view(B, o)
@@ -307,6 +307,14 @@ class FusedMPMLP(torch.nn.Module):
     @nvls_chunks.setter
     def nvls_chunks(self, v: int) -> None:
         self._nvls_chunks = int(v)
+
+    # dtype of the returned activations: fp32 (default, what a PyTorch loss expects) or the bf16 the last
+    # layer produced (half the bytes; pair it with ops.loss.mse_fused on very wide outputs)
+    out_bf16 = False
+
+    def _finish(self, t: torch.Tensor) -> torch.Tensor:
+        """Copy the last layer's result out of the (re-used) symmetric buffer."""
+        return t.clone() if self.out_bf16 else t.float()
 
     def _handle(self):
         return self._mpi if self._mpi is not None else _mpi.current()

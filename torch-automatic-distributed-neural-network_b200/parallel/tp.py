@@ -101,12 +101,22 @@ class _Fn(torch.autograd.Function):
         wbs = []
         out = None
         use_nvls = P > 1 and sc.has_multicast and mod.reduce_mode == "nvls"
+        trace = getattr(mod, "_trace", None)  # tools/mp_layer_timeline.py: a list that collects (label, event)
+
+        def mark(label):
+            if trace is not None:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record()
+                trace.append((label, e))
+
+        mark("start")
         for l in range(L):
             W, b = params[2 * l], params[2 * l + 1]
             o = mod.sizes[l + 1]
             last = l == L - 1
             wb = _cast_bf16(W)
             wbs.append(wb)
+            mark(f"l{l}.cast")
             if o % (64 * P) == 0 and use_nvls:
                 # NVLS form: plain (2-CTA) GEMM into the own heap, then every rank pulls the switch-reduced
                 # sum of its column block.  Row chunks pipeline the two: chunk c's reduction runs on the
@@ -143,6 +153,7 @@ class _Fn(torch.autograd.Function):
                 # P ranks push to P different destinations instead of all hammering rank 0's ingress
                 nblk = (o + 255) // 256
                 gemm_bf16(a, wb, bias=b, push=push, push_ldc=w, rs_width=w, n_rotate=((r + 1) % P) * nblk // P)
+                mark(f"l{l}.gemm+push")
                 nxt = torch.empty((B, w), device=x.device, dtype=torch.bfloat16)
                 _native.check(lib.tadnn_reduce_slots(
                     sc.handle, C.c_ulonglong(plan.slots_off), B, w, C.c_float(1.0), None, 0 if last else 1,
@@ -165,6 +176,7 @@ class _Fn(torch.autograd.Function):
                 else:
                     assert o % (8 * P) == 0, f"hidden width {o} must be a multiple of 8*P"
                     a = torch.tanh(y[:, r * (o // P):(r + 1) * (o // P)]).to(torch.bfloat16).contiguous()
+            mark(f"l{l}.reduce")
             if not last:
                 acts.append(a)
         ctx.mod, ctx.B = mod, B

@@ -163,3 +163,37 @@ def test_comm_speed_is_live():
         return tadnn.comm_speed(DATA, TGT, m, h, None, criterion=nn.MSECriterion(), iters=3)
 
     assert all(s > 0 for s in world.run(body))
+
+
+def test_sync_period_from_speed_table():
+    from tadnn.datamodule import sync_period_from_speed
+    assert sync_period_from_speed(1e-3, 1e-4, 1000) == 1          # sync is already 10 % of one sample
+    assert sync_period_from_speed(1e-3, 1e-3, 1000) == 10         # ten samples amortise it to 10 %
+    assert sync_period_from_speed(1e-4, 5e-3, 1000, overhead=0.05) == 1000  # clamped to the shard
+    assert sync_period_from_speed(0.0, 1e-3, 3000) == 50          # no measurement: the reference's table
+
+
+def test_parallelize_auto_period_is_measured_and_agreed():
+    """batchSize="auto": the period comes from comm_speed(split=True) (datamodule.lua:40-42 is the dead
+    call this revives); every rank must end up with the same period, and the model must be untouched."""
+    world = mpi.FakeWorld(3)
+
+    def body(h):
+        m = _mlp(seed=7)
+        before = torch.cat([p.detach().reshape(-1) for p in m.parameters()]).clone()
+        d, t, n = tadnn.parallelize(DATA, TGT, m, DATA.shape[0], h, None, "auto", verbose=False,
+                                    criterion=nn.MSECriterion())
+        after = torch.cat([p.detach().reshape(-1) for p in m.parameters()])
+        st = m._tadnn_sync
+        return st.batchSize, n, torch.equal(before, after), all(p.grad is None or float(p.grad.abs().sum()) == 0 for p in m.parameters())
+
+    res = world.run(body)
+    periods = {r[0] for r in res}
+    assert len(periods) == 1 and 1 <= res[0][0] <= res[0][1]
+    assert all(r[2] and r[3] for r in res)
+
+    def body2(h):
+        return tadnn.comm_speed(DATA, TGT, _mlp(seed=7), h, None, criterion=nn.MSECriterion(), iters=4, split=True, verbose=False)
+
+    out = mpi.FakeWorld(2).run(body2)
+    assert out[0] == out[1] and out[0][0] > 0 and out[0][1] > 0  # MAX over ranks: identical on every rank

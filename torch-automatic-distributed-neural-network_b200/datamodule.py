@@ -20,6 +20,7 @@ environment-driven: ``TADNN_DATA_SHUFFLE`` (``dataShuffle``), ``TADNN_SYNC_PROTO
 """
 from __future__ import annotations
 
+import math
 import os
 import time
 from typing import Optional
@@ -54,7 +55,8 @@ _USAGE = "-usage for parallelize(data, targets, model, size)"
 def parallelize(data=None, targets=None, model=None, size=None, mpi_obj=None, mpinn_obj=None,
                 batchSize=None, *, sync_init: Optional[bool] = None, remainder: str = "drop",
                 shuffle: Optional[bool] = None, flatten: Optional[bool] = None,
-                sync_mode: Optional[str] = None, overlap: Optional[bool] = None, verbose: bool = True):
+                sync_mode: Optional[str] = None, overlap: Optional[bool] = None, verbose: bool = True,
+                criterion=None):
     """Returns ``(newdata, newtargets, dataSize)`` — three values, as the code does
     (datamodule.lua:52), not the four its header comment promises — or ``-1`` after printing
     the usage line when a required argument is missing (datamodule.lua:18-21).
@@ -64,7 +66,9 @@ def parallelize(data=None, targets=None, model=None, size=None, mpi_obj=None, mp
     itself, datamodule.lua:31-34, SURVEY Q11; ``TADNN_COMPAT_SYNC_INIT=1`` restores that);
     ``remainder`` "drop" | "last" (Q6); ``shuffle`` strided shard (Q7); ``flatten`` move
     params/grads into the flat symmetric buffer (default: on CUDA); ``sync_mode`` "model" |
-    "grads"; ``overlap`` overlap the sync with backward.
+    "grads"; ``overlap`` overlap the sync with backward; ``batchSize="auto"`` measures the per-sample
+    compute time and the cost of one synchronisation (:func:`comm_speed` with ``criterion``) and picks
+    the period that keeps the synchronisation overhead near 10 % (:func:`sync_period_from_speed`).
     """
     if data is None or targets is None or model is None or size is None:
         print(_USAGE)
@@ -94,7 +98,13 @@ def parallelize(data=None, targets=None, model=None, size=None, mpi_obj=None, mp
     newdata, dataSize = data_parallel(data, size, mpi_obj, remainder=remainder, shuffle=shuffle, verbose=verbose)
     newtargets, _ = data_parallel(targets, size, mpi_obj, remainder=remainder, shuffle=shuffle, verbose=False)
 
-    if batchSize != -1:  # datamodule.lua:45-47
+    if batchSize == "auto":
+        # what the reference's commented-out call (datamodule.lua:40-42) was reaching for: measure the
+        # compute and the synchronisation cost on this machine and derive the period from them
+        speed = comm_speed(newdata, newtargets, model, mpi_obj, mpinn_obj, criterion=criterion,
+                           iters=min(10, int(dataSize)), split=True, verbose=verbose)
+        optimize_sync(speed, dataSize, model, mpinn_obj, mpi_obj, None, sync_mode=sync_mode, overlap=overlap)
+    elif batchSize != -1:  # datamodule.lua:45-47
         optimize_sync(None, dataSize, model, mpinn_obj, mpi_obj, batchSize, sync_mode=sync_mode, overlap=overlap)
 
     mpi_obj.barrier()  # datamodule.lua:50
@@ -115,14 +125,27 @@ def heuristic_batch_size(size: int) -> int:
     return 100
 
 
+def sync_period_from_speed(compute_s: float, sync_s: float, size: int, overhead: float = 0.10) -> int:
+    """Samples between synchronisations such that ``sync_s / (period * compute_s) <= overhead``, clamped
+    to ``[1, size]``.  The measured counterpart of the reference's size table (datamodule.lua:68-78)."""
+    if compute_s <= 0.0:
+        return heuristic_batch_size(size)
+    period = int(math.ceil(sync_s / (overhead * compute_s)))
+    return max(1, min(int(size), period))
+
+
 def optimize_sync(speed, size, model, mpinn, mpi, batchSize=None, *, sync_mode: Optional[str] = None,
                   overlap: Optional[bool] = None):
     """Pick the sync period (if not given) and install the synchronisation hooks on ``model``.
-    Returns ``batchSize`` (datamodule.lua:187).  ``speed`` is accepted and ignored, as in the
-    reference (its call site passes an undefined global, datamodule.lua:46)."""
+    Returns ``batchSize`` (datamodule.lua:187).  ``speed`` is ignored as in the reference (its call
+    site passes an undefined global, datamodule.lua:46) unless it is the ``(compute, sync)`` pair of
+    ``comm_speed(split=True)`` and no ``batchSize`` was given: then the period is derived from it."""
     from .parallel.dp import SyncState
     if batchSize is None:
-        batchSize = heuristic_batch_size(size)
+        if isinstance(speed, (tuple, list)) and len(speed) == 2:  # (compute s/sample, s per synchronisation)
+            batchSize = sync_period_from_speed(speed[0], speed[1], size)
+        else:
+            batchSize = heuristic_batch_size(size)
     old = getattr(model, "_tadnn_sync", None)
     if old is not None:
         old.remove()
@@ -220,9 +243,14 @@ def data_parallel(data, size, mpi, *, remainder: str = "drop", shuffle: Optional
 # ----------------------------------------------------------------------------
 # comm_speed (datamodule.lua:280-303; dead code there, live here)
 # ----------------------------------------------------------------------------
-def comm_speed(data, targets, model, mpi=None, mpinn=None, criterion=None, iters: int = 10):
+def comm_speed(data, targets, model, mpi=None, mpinn=None, criterion=None, iters: int = 10, split: bool = False,
+               verbose: bool = True):
     """Mean seconds of {forward, criterion backward, model backward, synchronizeGradients} over
-    ``iters`` samples.  Device-timed with CUDA events on GPU, wall clock on CPU."""
+    ``iters`` samples.  Device-timed with CUDA events on GPU, wall clock on CPU.  ``split=True`` times the
+    compute and the synchronisation separately and returns ``(compute_s, sync_s)``, each the MAX over
+    ranks (so every rank derives the same period); gradients are left as they were."""
+    if split:
+        return _comm_speed_split(data, targets, model, mpi or _mpi_mod.current(), mpinn or _mpinn_mod, criterion, iters, verbose)
     mpi = mpi or _mpi_mod.current()
     mpinn = mpinn or _mpinn_mod
     if criterion is None:
@@ -255,6 +283,61 @@ def comm_speed(data, targets, model, mpi=None, mpinn=None, criterion=None, iters
         speed = (time.perf_counter() - t0) / iters
     print(f"Rank: {mpi.rank()} comm speed: {speed}")
     return speed
+
+
+def _comm_speed_split(data, targets, model, mpi, mpinn, criterion, iters, verbose):
+    if criterion is None:
+        from .nn import CrossEntropyCriterion
+        criterion = CrossEntropyCriterion()
+    params = [p for p in model.parameters() if p.requires_grad]
+    cuda = any(p.is_cuda for p in params)
+
+    def timed(fn, n):
+        if cuda:
+            torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for i in range(n):
+            fn(i)
+        if cuda:
+            torch.cuda.synchronize()
+        return (time.perf_counter() - t0) / max(1, n)
+
+    def compute(i):
+        x, y = data[i % len(data)], targets[i % len(targets)]
+        if cuda:
+            x = x.to(params[0].device)
+            y = y.to(params[0].device) if torch.is_tensor(y) else y
+        with torch.enable_grad():
+            torch.autograd.grad(criterion(model(x), y), params, allow_unused=True)
+
+    mpi.barrier()
+    compute(0)  # warm-up (allocator, kernels)
+    compute_s = timed(compute, iters)
+    saved = [None if p.grad is None else p.grad.detach().clone() for p in params]
+    for p in params:  # synchronizeModel reduces parameters AND gradients: give it gradients to move
+        if p.grad is None:
+            p.grad = torch.zeros_like(p)
+    before = [p.detach().clone() for p in params]
+    synchronizeModel(model, mpi)  # warm-up
+    sync_s = timed(lambda i: synchronizeModel(model, mpi), 3)
+    with torch.no_grad():  # averaging identical replicas is a no-op, but restore anyway (replicas may differ)
+        for p, b, g in zip(params, before, saved):
+            p.copy_(b)
+            if g is None:
+                p.grad = None
+            else:
+                p.grad.copy_(g)
+    t = torch.tensor([compute_s, sync_s], dtype=torch.float64)
+    t = t.to(params[0].device) if cuda else t
+    for k in range(2):  # MAX over ranks from a sum-only all-reduce: gather one slot per rank
+        slots = torch.zeros(mpi.size(), dtype=t.dtype, device=t.device)
+        slots[mpi.rank()] = t[k]
+        mpi.allreduceTensor(slots)
+        t[k] = slots.max()
+    compute_s, sync_s = float(t[0]), float(t[1])
+    if verbose:
+        print(f"Rank: {mpi.rank()} compute {compute_s:.6f} s/sample, sync {sync_s:.6f} s")
+    return compute_s, sync_s
 
 
 # snake_case aliases

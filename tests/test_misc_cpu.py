@@ -4,6 +4,7 @@ import os
 import subprocess
 import sys
 
+import pytest
 import torch
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -102,3 +103,26 @@ def test_python_dash_m_tadnn_describes_the_installation():
     d = json.loads(p.stdout)
     assert d["native"]["built"] and d["native"]["missing_entry_points"] == [] and d["native"]["entry_points"] > 50
     assert d["env"] == {"TADNN_PRINT_DIMS": "1"} and "gpus" in d["devices"]
+
+
+def _free_port():
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+@pytest.mark.parametrize("script,nproc,args,expect", [
+    ("mlp_dp_cpu.py", 2, ["--size", "40", "--batchSize", "5"], "4 syncs"),
+    ("mlp_mp.py", 2, [], "|fused - dense|"),
+    ("mlp_hybrid_cpu.py", 4, ["--tp", "2", "--size", "40", "--batchSize", "5"], "tp 1/2"),
+])
+def test_multiprocess_examples_run_on_cpu(script, nproc, args, expect):
+    """The launcher path of the examples (examples/launch.sh = torchrun on 127.0.0.1), CPU / gloo."""
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={nproc}", "--master-addr", "127.0.0.1",
+           "--master-port", str(_free_port()), os.path.join(ROOT, "examples", script)] + args
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=ROOT, env=dict(os.environ, CUDA_VISIBLE_DEVICES=""))
+    assert p.returncode == 0, p.stdout[-1500:] + p.stderr[-1500:]
+    assert expect in p.stdout, p.stdout[-1500:]

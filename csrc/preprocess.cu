@@ -8,7 +8,9 @@
 //   preprocess_uv_stats_kernel : sum / sum-of-squares of U and V over the shard (fp64 atomics)
 //   preprocess_yuv_lcn_kernel  : one CTA per image; RGB is read once, Y and the centred Y live in
 //                                shared memory, the two 7x7 neighbourhood averages are computed from
-//                                there (separable border correction folded into one divide), U and V
+//                                there with Torch7's arithmetic (border coefficient = the estimator
+//                                applied to ones; divisor = sqrt(local mean of squares) / coefficient,
+//                                replaced by `thresval` where it does not exceed `threshold`), U and V
 //                                are standardised with the statistics passed in, and the three planes
 //                                are written once (fp32 or bf16).
 //
@@ -64,15 +66,13 @@ __global__ void __launch_bounds__(256) preprocess_uv_stats_kernel(const float* _
 template <bool OUT_BF16>
 __global__ void __launch_bounds__(256) preprocess_yuv_lcn_kernel(const float* __restrict__ rgb, void* __restrict__ out_, int H, int W,
                                                                  PreTaps taps, float mean_u, float inv_std_u, float mean_v,
-                                                                 float inv_std_v, float threshold) {
+                                                                 float inv_std_v, float threshold, float thresval) {
   extern __shared__ float sm[];
   const int hw = H * W;
-  float* ys = sm;            // Y, later the divisor field (std)
+  float* ys = sm;            // Y
   float* cs = sm + hw;       // centred Y
   float* c1h = sm + 2 * hw;  // 1-D border coefficients along H
   float* c1w = c1h + H;      // ... and along W
-  __shared__ float red[8];
-  __shared__ float thr_s;
   const int pad = taps.n / 2;
   const long long img = blockIdx.x;
   const float* src = rgb + img * 3 * hw;
@@ -122,8 +122,8 @@ __global__ void __launch_bounds__(256) preprocess_yuv_lcn_kernel(const float* __
   }
   __syncthreads();
 
-  // divisive step: std = sqrt((k2 * centred^2) / coef); divisor = max(std, max(mean(std), threshold))
-  float local = 0.f;
+  // divisive step (Torch7 nn.SpatialDivisiveNormalization): std = sqrt(k2 * centred^2) / coef -- the square root
+  // is divided by the border coefficient -- and nn.Threshold(threshold, thresval) element-wise on the divisor
   for (int p = threadIdx.x; p < hw; p += 256) {
     const int i = p / W, j = p - i * W;
     float acc = 0.f;
@@ -140,22 +140,8 @@ __global__ void __launch_bounds__(256) preprocess_yuv_lcn_kernel(const float* __
       }
       acc += taps.k[a] * row;
     }
-    const float sd = sqrtf(fmaxf(acc / (c1h[i] * c1w[j]), 0.f));
-    ys[p] = sd;  // Y itself is no longer needed
-    local += sd;
-  }
-  local = warp_sum(local);
-  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = local;
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    float s = 0.f;
-    for (int w = 0; w < 8; ++w) s += red[w];
-    thr_s = fmaxf(s / static_cast<float>(hw), threshold);
-  }
-  __syncthreads();
-  const float thr = thr_s;
-  for (int p = threadIdx.x; p < hw; p += 256) {
-    const float y = cs[p] / fmaxf(ys[p], thr);
+    const float sd = sqrtf(fmaxf(acc, 0.f)) / (c1h[i] * c1w[j]);
+    const float y = cs[p] / (sd > threshold ? sd : thresval);
     if (OUT_BF16) static_cast<__nv_bfloat16*>(out_)[img * 3 * hw + p] = __float2bfloat16(y);
     else static_cast<float*>(out_)[img * 3 * hw + p] = y;
   }
@@ -179,7 +165,7 @@ extern "C" int tadnn_preprocess_uv_stats(const float* rgb, double* stats4, long 
 
 extern "C" int tadnn_preprocess_yuv_lcn(const float* rgb, void* out, int out_bf16, long long n_img, int H, int W, const float* taps1d,
                                         int n_taps, float mean_u, float std_u, float mean_v, float std_v, float threshold,
-                                        tadnn_stream_t stream_) {
+                                        float thresval, tadnn_stream_t stream_) {
   TADNN_REQUIRE(rgb && out && taps1d && n_img > 0, "preprocess_yuv_lcn: bad arguments");
   TADNN_REQUIRE(n_taps >= 1 && n_taps <= kMaxTaps && (n_taps & 1), "preprocess_yuv_lcn: the neighbourhood needs an odd tap count <= %d (got %d)",
                 kMaxTaps, n_taps);
@@ -195,10 +181,10 @@ extern "C" int tadnn_preprocess_yuv_lcn(const float* rgb, void* out, int out_bf1
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   if (out_bf16) {
     preprocess_yuv_lcn_kernel<true><<<static_cast<unsigned>(n_img), 256, smem, stream>>>(rgb, out, H, W, taps, mean_u, 1.f / std_u, mean_v,
-                                                                                          1.f / std_v, threshold);
+                                                                                          1.f / std_v, threshold, thresval);
   } else {
     preprocess_yuv_lcn_kernel<false><<<static_cast<unsigned>(n_img), 256, smem, stream>>>(rgb, out, H, W, taps, mean_u, 1.f / std_u, mean_v,
-                                                                                           1.f / std_v, threshold);
+                                                                                           1.f / std_v, threshold, thresval);
   }
   TADNN_LAUNCH_CHECK("preprocess_yuv_lcn");
   return 0;

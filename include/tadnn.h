@@ -334,13 +334,14 @@ int tadnn_mse_loss_grad(const void* y, const void* target, int target_fp32, void
  * cifar_example/sgd-torchad_nn-cifar.lua:182-216: rgb2yuv, U/V standardised with the training
  * shard's mean/std, Y through SpatialContrastiveNormalization(1, gaussian1D(7)).  rgb is fp32
  * [n, 3, H, W]; stats4 receives (sum u, sum u^2, sum v, sum v^2) in fp64 on the device; out is fp32 or
- * bf16 [n, 3, H, W].  H*W <= 5120, odd tap count <= 15.  Pass a negative std for the reference's
+ * bf16 [n, 3, H, W].  H*W <= 5120, odd tap count <= 15.  threshold / thresval are those of
+ * nn.SpatialDivisiveNormalization (defaults 1e-4 / threshold).  Pass a negative std for the reference's
  * sign quirk (lines 195, 200, 213, 216). */
 int tadnn_preprocess_uv_stats(const float* rgb, double* stats4, long long n_img, int H, int W,
                               tadnn_stream_t stream);
 int tadnn_preprocess_yuv_lcn(const float* rgb, void* out, int out_bf16, long long n_img, int H, int W,
                              const float* taps1d, int n_taps, float mean_u, float std_u, float mean_v,
-                             float std_v, float threshold, tadnn_stream_t stream);
+                             float std_v, float threshold, float thresval, tadnn_stream_t stream);
 
 #ifdef __cplusplus
 }

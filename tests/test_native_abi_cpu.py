@@ -101,7 +101,7 @@ def test_preprocess_validation_messages():
     p = C.cast(buf, C.c_void_p)
     taps = (C.c_float * 7)(*([1.0] * 7))
     args = lambda n_taps, H, W, su: (p, p, 0, C.c_longlong(1), H, W, taps, n_taps, C.c_float(0), C.c_float(su),
-                                     C.c_float(0), C.c_float(1), C.c_float(1e-4), None)
+                                     C.c_float(0), C.c_float(1), C.c_float(1e-4), C.c_float(1e-4), None)
     rc = lib.tadnn_preprocess_yuv_lcn(*args(6, 32, 32, 1.0))
     assert rc != 0 and b"odd tap count" in lib.tadnn_last_error()
     rc = lib.tadnn_preprocess_yuv_lcn(*args(7, 128, 128, 1.0))

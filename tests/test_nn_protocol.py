@@ -70,3 +70,57 @@ def test_confusion_matrix():
     cm.add(torch.tensor([[0.1, 0.8, 0.1], [0.9, 0.05, 0.05]]), torch.tensor([1, 2]))
     cm.add(torch.tensor([0.0, 0.0, 1.0]), 2)
     assert abs(cm.totalValid - 2 / 3) < 1e-9 and "global correct" in str(cm)
+
+
+def _scn_by_hand(x, k1, threshold=1e-4, thresval=None):
+    """Torch7 nn.SpatialContrastiveNormalization written out with loops (float64): estimator
+    E(x)(i,j) = sum_c sum_ab k2[a,b]/(sum k2 * C) * x[c, i+a-p, j+b-p] with zero padding, coef = E(ones),
+    subtractive x - E(x)/coef, divisive x / T(sqrt(E(x^2))/coef)."""
+    thresval = threshold if thresval is None else thresval
+    x = x.double()
+    C, H, W = x.shape
+    k2 = torch.outer(k1, k1).double()
+    k2 = k2 / (k2.sum() * C)
+    p = k1.numel() // 2
+
+    def E(z):
+        out = torch.zeros(H, W, dtype=torch.float64)
+        for i in range(H):
+            for j in range(W):
+                s = 0.0
+                for a in range(k1.numel()):
+                    for b in range(k1.numel()):
+                        ii, jj = i + a - p, j + b - p
+                        if 0 <= ii < H and 0 <= jj < W:
+                            s += float(k2[a, b]) * float(z[:, ii, jj].sum())
+                out[i, j] = s
+        return out
+
+    coef = E(torch.ones_like(x))
+    c = x - E(x) / coef
+    sd = torch.sqrt(E(c * c)) / coef
+    sd = torch.where(sd > threshold, sd, torch.full_like(sd, thresval))
+    return c / sd
+
+
+def test_spatial_contrastive_normalization_is_torch7_arithmetic():
+    from tadnn.utils import preprocess
+    g = torch.Generator().manual_seed(3)
+    k = preprocess.gaussian1d(5)
+    x1 = torch.rand(1, 8, 9, generator=g)
+    m = nn.SpatialContrastiveNormalization(1, k)
+    assert torch.allclose(m(x1).double(), _scn_by_hand(x1, k), atol=1e-5)          # [C, H, W] input, borders included
+    assert torch.allclose(m(x1.unsqueeze(0))[0], m(x1))                             # batch mode
+    assert torch.allclose(preprocess.spatial_contrastive_normalization(x1.unsqueeze(0), k)[0], m(x1), atol=1e-6)
+    x3 = torch.rand(3, 7, 7, generator=g)                                           # several planes share one local mean / std
+    assert torch.allclose(nn.SpatialContrastiveNormalization(3, k)(x3).double(), _scn_by_hand(x3, k), atol=1e-5)
+    assert torch.allclose(m(4.0 * x1), m(x1), atol=1e-4)                            # contrast invariance above the threshold
+    flat = torch.full((1, 8, 8), 0.3)
+    assert m(flat).abs().max() < 1e-2                                               # std <= threshold -> divided by thresval
+    big = nn.SpatialDivisiveNormalization(1, k, threshold=10.0, thresval=2.0)       # element-wise Threshold(threshold, thresval)
+    assert torch.allclose(big(x1), x1 / 2.0)
+    sub = nn.SpatialSubtractiveNormalization(1, k)
+    assert torch.allclose(sub(flat), torch.zeros_like(flat), atol=1e-6)             # border-corrected mean of a constant is the constant
+    import pytest
+    with pytest.raises(ValueError):
+        nn.SpatialContrastiveNormalization(1, torch.ones(4))                        # even kernels are refused, as in Torch7

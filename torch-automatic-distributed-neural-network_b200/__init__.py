@@ -23,6 +23,7 @@ __version__ = "0.1.0"
 from . import mpi, mpinn  # noqa: F401
 from . import datamodule, nodemodule  # noqa: F401
 from . import nn  # noqa: F401
+from . import image, optim  # noqa: F401  (the two helper packages the example script touches)
 from .datamodule import (comm_speed, data_parallel, optimize_sync, parallelize, remove_hooks,  # noqa: F401
                          selectCollective, synchronizeModel, synchronize_model)
 from .trainer import BatchTrainer  # noqa: F401
@@ -38,7 +39,7 @@ def native_available() -> bool:
 
 __all__ = [
     "parallelize", "synchronizeModel", "synchronize_model", "data_parallel", "optimize_sync",
-    "selectCollective", "comm_speed", "remove_hooks", "mpi", "mpinn", "nn", "datamodule", "nodemodule",
+    "selectCollective", "comm_speed", "remove_hooks", "mpi", "mpinn", "nn", "image", "optim", "datamodule", "nodemodule",
     "MPInitialLinear", "MPBaseLinear", "MPTanh", "MPInitialReshape", "MPBaseReshape",
     "StochasticGradient", "BatchTrainer", "native_available",
 ]

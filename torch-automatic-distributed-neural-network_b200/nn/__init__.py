@@ -16,6 +16,8 @@ from __future__ import annotations
 from .protocol import T7Protocol  # noqa: F401
 from .layers import (Module, Sequential, Linear, Tanh, ReLU, LogSoftMax, Dropout, Reshape, View,  # noqa: F401
                      SpatialConvolutionMM, SpatialMaxPooling)
+from .normalization import (SpatialContrastiveNormalization, SpatialDivisiveNormalization,  # noqa: F401
+                            SpatialSubtractiveNormalization)
 from .criterion import Criterion, ClassNLLCriterion, CrossEntropyCriterion, MSECriterion  # noqa: F401
 from .mp import (MPBaseLinear, MPBaseReshape, MPInitialLinear, MPInitialReshape, MPTanh,  # noqa: F401
                  narrowInput, fuse_mp)
@@ -23,7 +25,8 @@ from .trainer import StochasticGradient  # noqa: F401
 
 __all__ = [
     "Module", "Sequential", "Linear", "Tanh", "ReLU", "LogSoftMax", "Dropout", "Reshape", "View",
-    "SpatialConvolutionMM", "SpatialMaxPooling", "Criterion", "ClassNLLCriterion",
+    "SpatialConvolutionMM", "SpatialMaxPooling", "SpatialSubtractiveNormalization", "SpatialDivisiveNormalization",
+    "SpatialContrastiveNormalization", "Criterion", "ClassNLLCriterion",
     "CrossEntropyCriterion", "MSECriterion", "StochasticGradient", "MPInitialLinear",
     "MPBaseLinear", "MPTanh", "MPInitialReshape", "MPBaseReshape", "narrowInput", "fuse_mp",
     "T7Protocol",

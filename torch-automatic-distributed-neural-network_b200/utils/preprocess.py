@@ -32,19 +32,18 @@ def gaussian1d(size: int = 7, sigma: float = 0.25, amplitude: float = 1.0) -> to
     return (amplitude * torch.exp(-(((i - center) / (sigma * size)) ** 2) / 2)).float()
 
 
-def spatial_contrastive_normalization(y: torch.Tensor, kernel1d: torch.Tensor, threshold: float = 1e-4) -> torch.Tensor:
-    """``nn.SpatialContrastiveNormalization(1, kernel)`` on ``[N, 1, H, W]``: subtractive then divisive
-    normalisation with a separable, border-corrected neighbourhood average."""
-    k2 = torch.outer(kernel1d, kernel1d).to(y)
-    k2 = (k2 / k2.sum()).view(1, 1, *k2.shape)
-    pad = kernel1d.numel() // 2
-    ones = torch.ones_like(y[:1])
-    coef = F.conv2d(ones, k2, padding=pad)  # border correction
-    mean = F.conv2d(y, k2, padding=pad) / coef
-    centered = y - mean
-    std = torch.sqrt(F.conv2d(centered * centered, k2, padding=pad) / coef)
-    thr = torch.clamp(std.mean(dim=(1, 2, 3), keepdim=True), min=threshold)
-    return centered / torch.maximum(std, thr)
+def spatial_contrastive_normalization(y: torch.Tensor, kernel1d: torch.Tensor, threshold: float = 1e-4,
+                                      thresval: float | None = None) -> torch.Tensor:
+    """``nn.SpatialContrastiveNormalization(1, kernel, threshold, thresval)`` on ``[N, 1, H, W]`` (Torch7 ``nn``
+    arithmetic, see :mod:`tadnn.nn.normalization`): subtract the border-corrected local mean, then divide by
+    the local standard deviation, element-wise replaced by ``thresval`` where it does not exceed ``threshold``."""
+    from ..nn.normalization import _kernel2d, local_estimate
+    k2 = _kernel2d(kernel1d).to(y.device)
+    thresval = threshold if thresval is None else thresval
+    coef = local_estimate(torch.ones_like(y[:1]), k2)  # border correction
+    centered = y - local_estimate(y, k2) / coef
+    std = torch.sqrt(local_estimate(centered * centered, k2)) / coef
+    return centered / torch.where(std > threshold, std, torch.full_like(std, thresval))
 
 
 def preprocess(train: torch.Tensor, test: torch.Tensor | None = None, reference_sign: bool = False):
@@ -86,7 +85,7 @@ def uv_stats_cuda(rgb: torch.Tensor):
 
 
 def yuv_lcn_cuda(rgb: torch.Tensor, stats, kernel1d: torch.Tensor | None = None, threshold: float = 1e-4,
-                 out_dtype: torch.dtype = torch.float32) -> torch.Tensor:
+                 out_dtype: torch.dtype = torch.float32, thresval: float | None = None) -> torch.Tensor:
     """rgb2yuv + U/V standardisation with ``stats`` + contrast normalisation of Y, one CTA per image."""
     import ctypes as C
     from .. import _native
@@ -99,7 +98,8 @@ def yuv_lcn_cuda(rgb: torch.Tensor, stats, kernel1d: torch.Tensor | None = None,
     out = torch.empty(rgb.shape, device=rgb.device, dtype=out_dtype)
     _native.check(_native.lib().tadnn_preprocess_yuv_lcn(
         C.c_void_p(rgb.data_ptr()), C.c_void_p(out.data_ptr()), int(out_dtype == torch.bfloat16), C.c_longlong(n), H, W, taps, k.numel(),
-        C.c_float(mu), C.c_float(sdu), C.c_float(mv), C.c_float(sdv), C.c_float(threshold), C.c_void_p(_native.stream_ptr())),
+        C.c_float(mu), C.c_float(sdu), C.c_float(mv), C.c_float(sdv), C.c_float(threshold),
+        C.c_float(threshold if thresval is None else thresval), C.c_void_p(_native.stream_ptr())),
         "tadnn_preprocess_yuv_lcn")
     return out
 

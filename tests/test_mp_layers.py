@@ -141,3 +141,28 @@ def test_print_dims_switch(monkeypatch, capsys):
     world.run(lambda h: _mp_model(h)(torch.randn(2, 8, 8)))
     out = capsys.readouterr().out
     assert "UPDATE OUTPUT" in out
+
+
+def test_model_parallelize_rewrites_a_dense_model():
+    """tadnn.model_parallelize: the README's by-hand rewrite (README.md:77-110) done automatically; the MP
+    model computes what the dense one does and gathers back to the same weights."""
+    import tadnn
+    from tadnn.utils.convert import dense_model_from_mp
+    g = torch.Generator().manual_seed(11)
+    dense = nn.Sequential().add(nn.Reshape(16)).add(nn.Linear(16, 12)).add(nn.Tanh()).add(nn.Linear(12, 4))
+    with torch.no_grad():
+        for p in dense.parameters():
+            p.copy_(torch.rand(p.shape, generator=g) - 0.5)
+    x = torch.randn(5, 1, 4, 4, generator=g)
+    want = dense(x).detach()
+
+    def body(h):
+        m = tadnn.model_parallelize(dense, h)
+        kinds = [type(c).__name__ for c in m.children()]
+        back = dense_model_from_mp(m, h)
+        same = all(torch.allclose(a, b) for a, b in zip(back.parameters(), dense.parameters()))
+        return kinds, (m(x) - want).abs().max().item(), same
+
+    for kinds, err, same in mpi.FakeWorld(4).run(body):
+        assert kinds == ["MPInitialReshape", "MPInitialLinear", "MPTanh", "MPBaseLinear"]
+        assert err < 1e-5 and same

@@ -27,6 +27,7 @@ from . import image, optim  # noqa: F401  (the two helper packages the example s
 from .datamodule import (comm_speed, data_parallel, optimize_sync, parallelize, remove_hooks,  # noqa: F401
                          selectCollective, synchronizeModel, synchronize_model)
 from .trainer import BatchTrainer  # noqa: F401
+from .nodemodule import model_parallelize  # noqa: F401
 from .nn import (MPBaseLinear, MPBaseReshape, MPInitialLinear, MPInitialReshape, MPTanh,  # noqa: F401
                  StochasticGradient)
 
@@ -41,5 +42,5 @@ __all__ = [
     "parallelize", "synchronizeModel", "synchronize_model", "data_parallel", "optimize_sync",
     "selectCollective", "comm_speed", "remove_hooks", "mpi", "mpinn", "nn", "image", "optim", "datamodule", "nodemodule",
     "MPInitialLinear", "MPBaseLinear", "MPTanh", "MPInitialReshape", "MPBaseReshape",
-    "StochasticGradient", "BatchTrainer", "native_available",
+    "StochasticGradient", "BatchTrainer", "native_available", "model_parallelize",
 ]

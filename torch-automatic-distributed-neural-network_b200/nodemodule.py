@@ -29,6 +29,20 @@ def syncReshape() -> bool:    # nodemodule.lua:5
     return not _flag("TADNN_COMPAT_BACKWARD")
 
 
+def model_parallelize(model, mpi=None, fuse: bool = False):
+    """The model-parallel counterpart of ``parallelize``: rewrite a dense ``Sequential`` of
+    ``Reshape / Linear / Tanh`` into the ``MP*`` layers, each rank keeping its own slice of every weight
+    (the README shows this rewrite done by hand, README.md:77-110).  ``fuse=True`` additionally returns
+    the fused B200 module (``FusedMPMLP``) sharing those parameters when the model is on a GPU with the
+    symmetric-memory context up.  The dense model must be identical on every rank (same seed)."""
+    from .utils.convert import mp_model_from_dense
+    out = mp_model_from_dense(model, mpi)
+    p = next(model.parameters(), None)
+    if p is not None:
+        out = out.to(p.device)
+    return fuse_mp(out, mpi=mpi) if fuse else out
+
+
 CLASSES = {
     "nn.MPInitialLinear": MPInitialLinear,
     "nn.MPBaseLinear": MPBaseLinear,

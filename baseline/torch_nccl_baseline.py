@@ -69,3 +69,49 @@ class BaselineTrainer:
         with torch.no_grad():
             torch._foreach_add_(self.params, [p.grad for p in self.params], alpha=-self.lr)
         return loss.detach()
+
+    def fit(self, data, targets, batch, steps, start=0, affine=(4.0 / 255.0, -2.0)):
+        """The same end-to-end loop the tadnn trainer is timed on, in plain PyTorch: every step
+        copies its (uint8 or bf16) inputs and labels from pinned host memory on a side stream
+        (double-buffered), widens them with torch ops, runs the step and reads the loss back."""
+        dev = self.params[0].device
+        nb = max(1, data.shape[0] // batch)
+        cs = torch.cuda.Stream()
+        main = torch.cuda.current_stream()
+        bufs = [(torch.empty((batch,) + tuple(data.shape[1:]), dtype=data.dtype, device=dev),
+                 torch.empty((batch,), dtype=targets.dtype, device=dev)) for _ in range(2)]
+        ready = [torch.cuda.Event(), torch.cuda.Event()]
+        done = [torch.cuda.Event(), torch.cuda.Event()]
+        host_loss = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
+        lev = [torch.cuda.Event(), torch.cuda.Event()]
+
+        def issue(s):
+            k = s & 1
+            i = ((start + s) % nb) * batch
+            with torch.cuda.stream(cs):
+                if s >= 2:
+                    cs.wait_event(done[k])
+                bufs[k][0].copy_(data[i:i + batch], non_blocking=True)
+                bufs[k][1].copy_(targets[i:i + batch], non_blocking=True)
+                ready[k].record(cs)
+
+        issue(0)
+        for s in range(steps):
+            k = s & 1
+            if s + 1 < steps:
+                issue(s + 1)
+            main.wait_event(ready[k])
+            x = bufs[k][0]
+            if x.dtype == torch.uint8:
+                x = x.to(torch.bfloat16).mul_(affine[0]).add_(affine[1])
+            loss = self.step(x, bufs[k][1])
+            done[k].record(main)
+            host_loss[k].copy_(loss, non_blocking=True)
+            lev[k].record(main)
+            if s >= 1:
+                lev[k ^ 1].synchronize()
+                yield float(host_loss[k ^ 1])
+        if steps >= 1:
+            k = (steps - 1) & 1
+            lev[k].synchronize()
+            yield float(host_loss[k])

@@ -35,6 +35,27 @@ __device__ __forceinline__ uint32_t cas_acquire_sys(uint32_t* p, uint32_t cmp, u
 // K5: block b of every rank meets block b of every other rank.  Flag protocol: signal =
 // CAS(peer slot 0->1) with release, wait = CAS(own slot 1->0) with acquire; self-resetting,
 // so launches can be replayed (CUDA graphs) without host-side epochs.
+// A peer that never shows up (dead or wedged process) does not hang or trap the survivors: after
+// c.timeout_ns the waiting thread records (rank, awaited peer, channel, phase) in the host-visible status
+// word, poisons the context and returns; see CommDev.
+__device__ __noinline__ void barrier_report(const CommDev& c, int rank, int peer, int channel, int phase) {
+  const uint32_t code = 1u + ((static_cast<uint32_t>(rank) << 20) | (static_cast<uint32_t>(peer) << 12) |
+                              (static_cast<uint32_t>(channel) << 4) | static_cast<uint32_t>(phase));
+  if (c.poison != nullptr && atomicCAS(c.poison, 0u, code) == 0u && c.status != nullptr) {
+    *reinterpret_cast<volatile uint32_t*>(c.status) = code;
+    __threadfence_system();
+  }
+}
+__device__ __forceinline__ bool barrier_spin_check(const CommDev& c, uint32_t& spins, unsigned long long t0, int rank, int peer,
+                                                   int channel, int phase) {
+  if ((++spins & 255u) != 0u) return false;
+  if (c.poison != nullptr && *reinterpret_cast<volatile uint32_t*>(c.poison) != 0u) return true;
+  if (globaltimer_ns() - t0 > c.timeout_ns) {
+    barrier_report(c, rank, peer, channel, phase);
+    return true;
+  }
+  return false;
+}
 __device__ __forceinline__ void block_barrier(const CommDev& c, int channel) {
   __syncthreads();
   if (threadIdx.x < c.world) {
@@ -45,11 +66,13 @@ __device__ __forceinline__ void block_barrier(const CommDev& c, int channel) {
     uint32_t* local = c.pad[rank] + slot + peer;
     __threadfence_system();
     const unsigned long long t0 = globaltimer_ns();
+    uint32_t spins = 0;
+    bool failed = false;
     while (cas_release_sys(remote, 0u, 1u) != 0u) {
-      if (globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();  // dead peer: fail, do not hang
+      if (barrier_spin_check(c, spins, t0, rank, peer, channel, 0)) { failed = true; break; }
     }
-    while (cas_acquire_sys(local, 1u, 0u) != 1u) {
-      if (globaltimer_ns() - t0 > kSpinTimeoutNs) __trap();
+    while (!failed && cas_acquire_sys(local, 1u, 0u) != 1u) {
+      if (barrier_spin_check(c, spins, t0, rank, peer, channel, 1)) break;
     }
   }
   __syncthreads();
@@ -497,6 +520,32 @@ int do_allreduce(const CommDev& dev, bool has_mc, unsigned long long off_bytes, 
 }
 
 }  // namespace
+
+int comm_init_status(tadnn_comm* c) {
+  c->dev.timeout_ns = kDefaultTimeoutNs;
+  if (const char* e = getenv("TADNN_COMM_TIMEOUT_S")) {
+    const double s = atof(e);
+    if (s > 0) c->dev.timeout_ns = static_cast<unsigned long long>(s * 1e9);
+  }
+  void* h = nullptr;
+  TADNN_CHECK_CUDA(cudaHostAlloc(&h, 64, cudaHostAllocMapped | cudaHostAllocPortable));
+  memset(h, 0, 64);
+  c->status_host = static_cast<uint32_t*>(h);
+  void* hd = nullptr;
+  TADNN_CHECK_CUDA(cudaHostGetDevicePointer(&hd, h, 0));
+  c->dev.status = static_cast<uint32_t*>(hd);
+  TADNN_CHECK_CUDA(cudaMalloc(&c->poison_dev, 16));
+  TADNN_CHECK_CUDA(cudaMemset(c->poison_dev, 0, 16));
+  c->dev.poison = static_cast<uint32_t*>(c->poison_dev);
+  return 0;
+}
+void comm_free_status(tadnn_comm* c) {
+  if (c->status_host) cudaFreeHost(c->status_host);
+  if (c->poison_dev) cudaFree(c->poison_dev);
+  c->status_host = nullptr;
+  c->poison_dev = nullptr;
+}
+
 }  // namespace tadnn
 
 using namespace tadnn;
@@ -527,6 +576,11 @@ extern "C" int tadnn_comm_create(int rank, int world, unsigned long long heap_by
   c->dev.rank = rank; c->dev.world = world;
   c->dev.heap[rank] = static_cast<uint8_t*>(c->base);
   c->dev.pad[rank] = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(c->base) + heap_bytes);
+  if (int rc = comm_init_status(c)) {
+    cudaFree(base);
+    delete c;
+    return rc;
+  }
   *out = c;
   return 0;
 }
@@ -610,8 +664,28 @@ extern "C" int tadnn_comm_destroy(tadnn_comm* c) {
     for (void* p : c->opened) cudaIpcCloseMemHandle(p);
     if (c->owns && c->base) cudaFree(c->base);
   }
+  comm_free_status(c);
   delete c;
   return 0;
+}
+
+extern "C" int tadnn_comm_set_timeout(tadnn_comm* c, double seconds) {
+  TADNN_REQUIRE(c != nullptr && seconds > 0, "comm_set_timeout: need a context and a positive number of seconds");
+  c->dev.timeout_ns = static_cast<unsigned long long>(seconds * 1e9);
+  return 0;
+}
+
+extern "C" int tadnn_comm_check(tadnn_comm* c) {
+  TADNN_REQUIRE(c != nullptr, "comm_check: null comm");
+  if (c->status_host == nullptr) return 0;
+  const uint32_t code = *reinterpret_cast<volatile uint32_t*>(c->status_host);
+  if (code == 0) return 0;
+  const uint32_t v = code - 1u;
+  set_error("collective timed out: rank %u waited more than %.1f s for rank %u (channel %u, %s) - that peer is dead, wedged or "
+            "never entered the collective; this communicator is unusable from here on",
+            (v >> 20) & 0xffu, static_cast<double>(c->dev.timeout_ns) * 1e-9, (v >> 12) & 0xffu, (v >> 4) & 0xffu,
+            (v & 15u) ? "waiting for its arrival flag" : "signalling it: its previous flag was never consumed");
+  return 4;
 }
 
 extern "C" int tadnn_barrier(tadnn_comm* c, int channel, tadnn_stream_t stream) {

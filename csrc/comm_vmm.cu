@@ -161,7 +161,7 @@ static int create_vmm_into(tadnn_comm* c, int rank, int world, unsigned long lon
   c->dev.pad[rank] = reinterpret_cast<uint32_t*>(static_cast<uint8_t*>(c->base) + heap_bytes);
   c->peer_handles.assign(world, 0);
   c->peer_vas.assign(world, nullptr);
-  return 0;
+  return comm_init_status(c);
 }
 
 extern "C" int tadnn_comm_create_vmm(int rank, int world, unsigned long long heap_bytes, tadnn_comm** out) {
@@ -173,6 +173,7 @@ extern "C" int tadnn_comm_create_vmm(int rank, int world, unsigned long long hea
   tadnn_comm* c = new tadnn_comm();
   if (int rc = create_vmm_into(c, rank, world, heap_bytes)) {
     tadnn_comm_vmm_release(c);  // unmaps / releases whatever was set up before the failure
+    comm_free_status(c);
     delete c;
     return rc;
   }

@@ -147,6 +147,41 @@ __global__ void __launch_bounds__(256) preprocess_yuv_lcn_kernel(const float* __
   }
 }
 
+// uint8 -> bf16 with a per-channel affine map (y = x * scale[c] + shift[c]); 16 pixels per thread.
+// This is what lets the training loop ship the dataset over PCIe as what CIFAR is on disk (one byte per
+// value, 3 KB per image) and widen it on the device, instead of copying bf16/fp32 tensors every step.
+struct U8Affine {
+  float scale[4], shift[4];
+};
+__global__ void __launch_bounds__(256) u8_to_bf16_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, long long nvec, int plane16,
+                                                         int C, U8Affine m) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < nvec;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>((i / plane16) % C);
+    const float sc = m.scale[c], sh = m.shift[c];
+    const uint4 v = __ldg(x + i);
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+    uint32_t o[8];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float f0 = static_cast<float>(w[k] & 0xffu) * sc + sh, f1 = static_cast<float>((w[k] >> 8) & 0xffu) * sc + sh;
+      const float f2 = static_cast<float>((w[k] >> 16) & 0xffu) * sc + sh, f3 = static_cast<float>(w[k] >> 24) * sc + sh;
+      o[2 * k] = pack_bf16x2(f0, f1);
+      o[2 * k + 1] = pack_bf16x2(f2, f3);
+    }
+    y[2 * i] = make_uint4(o[0], o[1], o[2], o[3]);
+    y[2 * i + 1] = make_uint4(o[4], o[5], o[6], o[7]);
+  }
+}
+__global__ void u8_to_bf16_scalar_kernel(const unsigned char* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n, int plane, int C,
+                                         U8Affine m) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const int c = static_cast<int>((i / plane) % C);
+    y[i] = __float2bfloat16_rn(static_cast<float>(x[i]) * m.scale[c] + m.shift[c]);
+  }
+}
+
 }  // namespace
 }  // namespace tadnn
 
@@ -187,5 +222,29 @@ extern "C" int tadnn_preprocess_yuv_lcn(const float* rgb, void* out, int out_bf1
                                                                                            1.f / std_v, threshold, thresval);
   }
   TADNN_LAUNCH_CHECK("preprocess_yuv_lcn");
+  return 0;
+}
+
+extern "C" int tadnn_u8_to_bf16(const void* x, void* y, long long n, int plane, int C, const float* host_scale, const float* host_shift,
+                                tadnn_stream_t stream_) {
+  TADNN_REQUIRE(x && y && n > 0 && plane > 0 && C >= 1 && C <= 4, "u8_to_bf16: bad arguments (n=%lld plane=%d C=%d; C <= 4)", n, plane, C);
+  U8Affine m;
+  for (int c = 0; c < 4; ++c) {
+    m.scale[c] = (host_scale && c < C) ? host_scale[c] : 1.f;
+    m.shift[c] = (host_shift && c < C) ? host_shift[c] : 0.f;
+  }
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const bool vec = (plane % 16 == 0) && (n % 16 == 0) && ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15) == 0;
+  if (vec) {
+    const long long nvec = n / 16;
+    long long blocks = (nvec + 255) / 256;
+    if (blocks > 8ll * sm_count()) blocks = 8ll * sm_count();
+    u8_to_bf16_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(static_cast<const uint4*>(x), static_cast<uint4*>(y), nvec, plane / 16, C, m);
+  } else {
+    long long blocks = (n + 255) / 256;
+    if (blocks > 8ll * sm_count()) blocks = 8ll * sm_count();
+    u8_to_bf16_scalar_kernel<<<static_cast<int>(blocks), 256, 0, stream>>>(static_cast<const unsigned char*>(x), static_cast<__nv_bfloat16*>(y), n, plane, C, m);
+  }
+  TADNN_LAUNCH_CHECK("u8_to_bf16");
   return 0;
 }

@@ -122,6 +122,15 @@ int tadnn_comm_attach(tadnn_comm* c, void* const* host_peer_heaps, void* const* 
 int tadnn_comm_heap(tadnn_comm* c, int peer, void** out_ptr);
 int tadnn_comm_info(tadnn_comm* c, int* rank, int* world, unsigned long long* heap_bytes, int* has_multicast);
 int tadnn_comm_destroy(tadnn_comm* c);
+/* Failure detection.  The reference hangs for ever when a rank dies (every MPI call it makes blocks:
+ * datamodule.lua:50,216,221; nodemodule.lua:52).  Here a device-side barrier that has waited `seconds`
+ * (default 120, or TADNN_COMM_TIMEOUT_S) gives up WITHOUT trapping: it records which rank was waiting for
+ * which peer, marks the context dead and lets the kernel run to completion (its output is garbage), and so
+ * does every later collective on the context.  tadnn_comm_check returns non-zero once that has happened,
+ * with a message naming the missing rank in tadnn_last_error(); it reads one word of mapped host memory and
+ * is safe to call at any time, including while kernels are running. */
+int tadnn_comm_set_timeout(tadnn_comm* c, double seconds);
+int tadnn_comm_check(tadnn_comm* c);
 
 /* VMM + multicast backend (csrc/comm_vmm.cu): the heap is a cuMemCreate allocation shared as a
  * POSIX file descriptor; where the driver exposes NVLS a multicast object over all heaps is mapped
@@ -299,7 +308,9 @@ int tadnn_head_backward(const tadnn_head_args* a, tadnn_stream_t stream);
  *  - The first call on each device looks up the array's device address and sets a kernel
  *    attribute; make that first call before any stream capture is begun on that device.
  *  - All calls on one device share the array: two calls whose kernels can overlap on the GPU
- *    (different streams) race on it.  Calls on one stream are safe back to back. */
+ *    (different streams) race on it.  Calls on one stream are safe back to back.
+ *  - The looked-up address is cached for the life of the process: after a cudaDeviceReset() the
+ *    cached value is stale, so a process that resets a device must not call this again on it. */
 int tadnn_head_forward_noalloc(const tadnn_head_args* a, tadnn_stream_t stream);
 
 /* p -= lr * (g + wd * p); optionally g = 0.  Replaces accUpdateGradParameters' in-place step
@@ -342,6 +353,14 @@ int tadnn_preprocess_uv_stats(const float* rgb, double* stats4, long long n_img,
 int tadnn_preprocess_yuv_lcn(const float* rgb, void* out, int out_bf16, long long n_img, int H, int W,
                              const float* taps1d, int n_taps, float mean_u, float std_u, float mean_v,
                              float std_v, float threshold, float thresval, tadnn_stream_t stream);
+
+/* uint8 -> bf16 widening with a per-channel affine map, y = x * scale[c] + shift[c], over an NCHW-style
+ * buffer (`plane` = H*W values per channel, C <= 4 channels; scale/shift are HOST arrays of C floats, NULL =
+ * identity).  The reference keeps its shard device-resident as preprocessed floats
+ * (cifar_example/sgd-torchad_nn-cifar.lua:239-245); a streaming input pipeline instead ships the raw bytes
+ * (3 KB per CIFAR image) over PCIe every step and widens them here. */
+int tadnn_u8_to_bf16(const void* x, void* y, long long n, int plane, int C, const float* host_scale,
+                     const float* host_shift, tadnn_stream_t stream);
 
 #ifdef __cplusplus
 }

@@ -93,3 +93,17 @@ def test_preprocess_cuda_flat_image_is_zero():
     flat = torch.full((2, 3, 32, 32), 0.5, device="cuda")
     out = P.yuv_lcn_cuda(flat, (0.0, 1.0, 0.0, 1.0))
     assert out[:, 0].abs().max().item() < 1e-2
+
+
+@pytest.mark.parametrize("shape", [(64, 3, 32, 32), (5, 3, 7, 9), (33, 1, 16, 16)])
+def test_u8_to_bf16_matches_torch(shape):
+    from tadnn.ops.cnn import u8_to_bf16
+    torch.manual_seed(0)
+    x = torch.randint(0, 256, shape, dtype=torch.uint8, device="cuda")
+    C_ = shape[1]
+    scale = [0.01 * (c + 1) for c in range(C_)]
+    shift = [-1.0 + 0.25 * c for c in range(C_)]
+    y = u8_to_bf16(x, shape[2] * shape[3], C_, scale, shift)
+    ref = x.float() * torch.tensor(scale, device="cuda").view(1, C_, 1, 1) + torch.tensor(shift, device="cuda").view(1, C_, 1, 1)
+    assert y.dtype == torch.bfloat16 and y.shape == x.shape
+    assert (y.float() - ref).abs().max().item() <= 2 ** -7 * max(1.0, ref.abs().max().item())  # one bf16 ulp (fma vs mul+add)

@@ -155,6 +155,10 @@ class _CnnLoss(torch.autograd.Function):
 
 
 class CifarCNN(torch.nn.Module, T7Protocol):
+    # uint8 pixels -> roughly unit-variance bf16: what BatchTrainer.fit applies on the device when the
+    # dataset is shipped as bytes (the reference's own preprocessing is utils/preprocess.py)
+    input_affine = ([4.0 / 255.0] * 3, [-2.0] * 3)
+
     def __init__(self, dropout: float = 0.5, seed: int = 1, fused_conv1: bool = True, conv2_mode: str = "dense"):
         super().__init__()
         assert conv2_mode in ("dense", "pooled", "legacy")

@@ -269,15 +269,25 @@ class TorchMPI(_Handle):
 
     # -- collectives -----------------------------------------------------------
     def barrier(self):
+        """Host-level barrier (datamodule.lua:50,283).  Always ``torch.distributed``'s: ranks may
+        arrive arbitrarily late here (rank 0 writing a checkpoint, uneven data loading, a profiler
+        replaying kernels), and a host barrier waits without occupying the GPU.  The device-side
+        flag barrier (csrc/comm.cu K5) is used *inside* the collective kernels only, where all
+        ranks are already within microseconds of each other; ``symm.barrier()`` exposes it."""
         import torch.distributed as dist
         if dist.is_initialized() and self.size() > 1:
             if self._use_gpu:
                 torch.cuda.synchronize()
-                if self.symm is not None:
-                    self.symm.barrier()
-                    torch.cuda.synchronize()
-                    return
             dist.barrier(group=self._group)
+
+    def nccl_only(self) -> "TorchMPI":
+        """A view of this communicator whose collectives never use the symmetric-memory kernels
+        (``torch.distributed``/NCCL only) — the comparator arm of the benchmarks, in-process."""
+        v = TorchMPI()
+        v.__dict__.update(self.__dict__)
+        v.symm = None
+        v._owns_pg = False
+        return v
 
     def allreduceTensor(self, t: torch.Tensor) -> torch.Tensor:
         """In-place sum over all ranks (nodemodule.lua:52, datamodule.lua:216)."""

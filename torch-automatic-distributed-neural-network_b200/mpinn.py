@@ -25,6 +25,10 @@ def synchronizeParameters(model, mpi=None, root: int = 0) -> None:
     flat = getattr(model, "_tadnn_flat", None)
     if flat is not None and flat.symmetric:
         flat.broadcast_params(root)
+        with torch.no_grad():  # buffers (e.g. running statistics) are not part of the flat region
+            for b in model.buffers():
+                if b.is_floating_point():
+                    mpi.broadcastTensor(root, b.data)
         return
     with torch.no_grad():
         for p in _params(model):

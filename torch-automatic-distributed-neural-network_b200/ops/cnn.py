@@ -20,6 +20,10 @@ class HeadArgs(C.Structure):
     ]
 
 
+_F4 = C.c_float * 4
+C_ll = C.c_longlong
+
+
 def _s(stream=None):
     return C.c_void_p(_native.stream_ptr(stream))
 
@@ -171,11 +175,22 @@ def sgd_step(p: torch.Tensor, g: torch.Tensor, lr: float, weight_decay: float = 
                                                C.c_float(weight_decay), int(zero_grad), _s()), "tadnn_sgd_step")
 
 
+def u8_to_bf16(x: torch.Tensor, plane: int, C: int, scale, shift, out=None) -> torch.Tensor:
+    """uint8 [n, C, ...] -> bf16 with y = x * scale[c] + shift[c] (csrc/preprocess.cu)."""
+    assert x.dtype == torch.uint8 and x.is_contiguous() and 1 <= C <= 4
+    if out is None:
+        out = torch.empty(x.shape, device=x.device, dtype=torch.bfloat16)
+    fs = (_F4)(*([float(v) for v in scale][:C] + [1.0] * (4 - C)))
+    fh = (_F4)(*([float(v) for v in shift][:C] + [0.0] * (4 - C)))
+    _native.check(_native.lib().tadnn_u8_to_bf16(_p(x), _p(out), C_ll(x.numel()), int(plane), int(C), fs, fh, _s()), "tadnn_u8_to_bf16")
+    return out
+
+
 def auto_split_k(M: int, N: int, K: int, tile_n: int = 256) -> int:
     tiles = ((M + 127) // 128) * ((N + tile_n - 1) // tile_n)
     kb = (K + 63) // 64
     return max(1, min(kb, 148 // max(1, tiles)))
 
 
-__all__ = ["im2col_winfirst", "conv_toeplitz_pack", "expand_corner", "conv1_weight_pack", "conv1_pool_forward", "conv1_pool_backward", "im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "colsum_relu_mask_corner", "conv_weight_pack",
+__all__ = ["u8_to_bf16", "im2col_winfirst", "conv_toeplitz_pack", "expand_corner", "conv1_weight_pack", "conv1_pool_forward", "conv1_pool_backward", "im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "colsum_relu_mask_corner", "conv_weight_pack",
            "conv_wgrad_unpack", "head_workspace", "sgd_step", "auto_split_k", "HeadArgs", "gemm_bf16"]

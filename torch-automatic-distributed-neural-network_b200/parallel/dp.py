@@ -10,10 +10,11 @@ hooking mechanism — the reference redefines ``nn.Sequential:backward`` and
 consult it: ``tadnn.nn.Sequential.backward`` (Torch7 style), ``StochasticGradient.train`` and
 plain autograd ``loss.backward()`` (post-accumulate-grad hooks + an end-of-backward callback).
 
-Overlap: on a step that will synchronise, parameter averaging is launched on a side stream
-when the backward starts (parameters do not change during backward) and each gradient bucket
-is launched as soon as its last gradient has been accumulated; the compute stream only waits
-for the side stream at the end of backward.
+Overlap: on a step that will synchronise, each gradient bucket is all-reduced on a side stream
+as soon as its last gradient has been accumulated; the parameters are averaged on that stream
+once backward has finished (they are still being read by the dgrad kernels until then, and
+in "model" mode with batchSize > 1 the replicas differ); the compute stream waits for the side
+stream at the end of backward.
 """
 from __future__ import annotations
 
@@ -135,9 +136,6 @@ class SyncState:
                     b["left"] = len(b["ids"])
                 ev = torch.cuda.current_stream().record_event()
                 self.comm_stream.wait_event(ev)
-                if self.sync_mode == "model":  # params are stable during backward: reduce now
-                    P = self.flat.ctx.world
-                    self.flat.allreduce("params", 1.0 / P, stream=self.comm_stream, channel=_symm.CH_DP)
         if self.overlap and self._will_sync:
             if self.flat is not None and p.grad is not None:
                 gv = self.flat.grad_view(p)
@@ -171,6 +169,15 @@ class SyncState:
                     self.flat.ctx.allreduce_offset(b["off"], b["count"], b["dtype"], 1.0 / P, 0, 0,
                                                    _symm.CH_DP, self.comm_stream)
                     b["left"] = 0
+            if self.sync_mode == "model":
+                # Parameters are averaged only now: the rest of backward was still reading W on the
+                # compute stream (dX = dY·W), and the replicas of a "model"-mode run with
+                # batchSize > 1 have diverged, so reducing them in place any earlier would feed a
+                # mix of local and averaged weights into the gradients.  The reference also
+                # averages after backward has finished (datamodule.lua:96-107).
+                ev = torch.cuda.current_stream().record_event()
+                self.comm_stream.wait_event(ev)
+                self.flat.allreduce("params", 1.0 / P, stream=self.comm_stream, channel=_symm.CH_DP)
             torch.cuda.current_stream().wait_stream(self.comm_stream)
             self.syncs += 1
             owner.sync_counter = c + 1

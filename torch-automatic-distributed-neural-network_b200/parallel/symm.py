@@ -14,8 +14,13 @@ reduce-scatter (csrc/comm_vmm.cu).  ``ipc``: ``cudaMalloc`` + CUDA-IPC handles e
 Allocation is a symmetric bump allocator: all ranks must call ``alloc`` in the same order
 with the same sizes (they do: the callers are SPMD).  ``tensor()`` returns a zero-copy
 ``torch.Tensor`` view of heap memory, so model parameters and gradients can *live* in the
-heap (tadnn.parallel.fusion) and be reduced in place.  The allocator never frees: long-lived
-buffers only (flat model buffers, per-batch-size layer plans); size it with ``TADNN_SYMM_HEAP_MB``.
+heap (tadnn.parallel.fusion) and be reduced in place.  ``alloc``/``free`` manage the heap with a
+deterministic first-fit free list; size it with ``TADNN_SYMM_HEAP_MB``.
+
+Failure detection: a barrier inside a collective kernel that waits longer than the timeout
+(``set_timeout`` / ``TADNN_COMM_TIMEOUT_S``, default 120 s) records which rank it was waiting for
+and lets the stream drain; ``check()`` — called before every collective launch — turns that into a
+``CommTimeout`` exception that names the missing rank (the reference just hangs).
 """
 from __future__ import annotations
 
@@ -34,6 +39,10 @@ CH_DEFAULT = 0   # mpi.allreduceTensor & friends on the compute stream
 CH_DP = 1        # data-parallel gradient/parameter sync on the comm stream
 CH_TP = 2        # model-parallel layer collectives
 CH_BARRIER = 3
+
+
+class CommTimeout(_native.NativeError):
+    """A device-side collective gave up waiting for a peer (dead or wedged rank)."""
 
 
 class _RawCuda:
@@ -55,7 +64,9 @@ class SymmContext:
         self.heap_bytes = 0
         self.heap_ptrs: list[int] = []
         self.has_multicast = False
-        self._bump = 0
+        self._bump = 0          # high-water mark (diagnostics)
+        self._free: list = []   # sorted [(offset, size)] free blocks
+        self._live: dict = {}   # offset -> size of live allocations
         self._heap_u8: Optional[torch.Tensor] = None
         self._staging_off = 0
         self._staging_bytes = 0
@@ -112,6 +123,8 @@ class SymmContext:
         raw = _RawCuda(self.heap_ptrs[self.rank], self.heap_bytes, self)
         self._heap_u8 = torch.as_tensor(raw, device=self.device)
         assert self._heap_u8.data_ptr() == self.heap_ptrs[self.rank], "zero-copy heap view failed"
+        self._free = [(0, self.heap_bytes)]
+        self._live = {}
         self._staging_bytes = staging_mb << 20
         self._staging_off = self.alloc(self._staging_bytes)
         if self.world > 1:
@@ -224,13 +237,68 @@ class SymmContext:
 
     # ------------------------------------------------------------------ memory
     def alloc(self, nbytes: int, align: int = 256) -> int:
-        off = (self._bump + align - 1) // align * align
-        if off + nbytes > self.heap_bytes:
-            raise MemoryError(
-                f"tadnn symmetric heap exhausted ({off + nbytes} > {self.heap_bytes} bytes); "
-                "raise TADNN_SYMM_HEAP_MB")
-        self._bump = off + nbytes
-        return off
+        """Symmetric allocation: first fit over a free list, 256-byte granules.  Deterministic, so
+        ranks that make the same calls in the same order get the same offsets (the callers are
+        SPMD).  Returns the heap offset; release it with :meth:`free`."""
+        gran = 256
+        align = max(gran, (align + gran - 1) // gran * gran)
+        size = max(gran, (int(nbytes) + gran - 1) // gran * gran)
+        for i, (foff, fsize) in enumerate(self._free):
+            off = (foff + align - 1) // align * align
+            if off + size <= foff + fsize:
+                pieces = []
+                if off > foff:
+                    pieces.append((foff, off - foff))
+                if off + size < foff + fsize:
+                    pieces.append((off + size, foff + fsize - off - size))
+                self._free[i:i + 1] = pieces
+                self._live[off] = size
+                self._bump = max(self._bump, off + size)
+                return off
+        raise MemoryError(
+            f"tadnn symmetric heap exhausted: {size} bytes requested, {self.free_bytes()} free "
+            f"(largest block {max((f[1] for f in self._free), default=0)}) of {self.heap_bytes}; "
+            "raise TADNN_SYMM_HEAP_MB or free() buffers that are no longer used")
+
+    def free(self, off: int) -> None:
+        """Return an allocation to the heap.  Like ``alloc`` this is a collective in spirit: every
+        rank must free the same offsets in the same order, and no kernel (local or remote) may still
+        be using the memory — synchronise first if in doubt."""
+        size = self._live.pop(int(off), None)
+        if size is None:
+            raise ValueError(f"free({off}): not a live symmetric allocation")
+        import bisect
+        i = bisect.bisect_left(self._free, (off, 0))
+        self._free.insert(i, (off, size))
+        # merge with the neighbours
+        if i + 1 < len(self._free) and self._free[i][0] + self._free[i][1] == self._free[i + 1][0]:
+            self._free[i:i + 2] = [(self._free[i][0], self._free[i][1] + self._free[i + 1][1])]
+        if i > 0 and self._free[i - 1][0] + self._free[i - 1][1] == self._free[i][0]:
+            self._free[i - 1:i + 1] = [(self._free[i - 1][0], self._free[i - 1][1] + self._free[i][1])]
+
+    def free_tensor(self, t: torch.Tensor) -> None:
+        off = self.offset_of(t)
+        if off is None:
+            raise ValueError("free_tensor: not a tensor of this heap")
+        self.free(off)
+
+    def free_bytes(self) -> int:
+        return sum(f[1] for f in self._free)
+
+    def live_bytes(self) -> int:
+        return sum(self._live.values())
+
+    # ------------------------------------------------------------------ failure detection
+    def set_timeout(self, seconds: float) -> None:
+        """How long a device-side barrier waits for a peer before it gives up (default 120 s or
+        ``TADNN_COMM_TIMEOUT_S``)."""
+        _native.check(_native.lib().tadnn_comm_set_timeout(self.handle, C.c_double(seconds)), "tadnn_comm_set_timeout")
+
+    def check(self) -> None:
+        """Raise :class:`CommTimeout` if a collective on this context has timed out waiting for a
+        peer (the message names the ranks).  One read of host memory; call it as often as you like."""
+        if self.handle and _native.lib().tadnn_comm_check(self.handle) != 0:
+            raise CommTimeout(_native.lib().tadnn_last_error().decode("utf-8", "replace"))
 
     def tensor(self, off: int, shape, dtype: torch.dtype) -> torch.Tensor:
         n = 1
@@ -265,11 +333,13 @@ class SymmContext:
 
     # ------------------------------------------------------------------ collectives
     def barrier(self, channel: int = CH_BARRIER, stream=None):
+        self.check()
         _native.check(_native.lib().tadnn_barrier(self.handle, C.c_int(channel),
                                                   C.c_void_p(_native.stream_ptr(stream))), "tadnn_barrier")
 
     def allreduce_offset(self, off: int, count: int, dtype: torch.dtype, scale: float = 1.0,
                          algo: int = 0, max_blocks: int = 0, channel: int = CH_DEFAULT, stream=None):
+        self.check()
         _native.check(_native.lib().tadnn_allreduce(
             self.handle, C.c_ulonglong(off), C.c_ulonglong(count), C.c_int(_DT[dtype]),
             C.c_float(scale), C.c_int(algo), C.c_int(max_blocks), C.c_int(channel),

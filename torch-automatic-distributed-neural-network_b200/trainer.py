@@ -84,53 +84,90 @@ class BatchTrainer:
 
     # ------------------------------------------------------------------ streaming from the host
     def fit(self, data: torch.Tensor, targets: torch.Tensor, batch: int, steps: int,
-            start: int = 0) -> Iterator[float]:
+            start: int = 0, depth: int = 4, input_affine=None) -> Iterator[float]:
         """Run ``steps`` steps over ``data``/``targets`` (host tensors, ideally pinned; wraps
         around), yielding each step's loss as a Python float (read one step late).  Per step:
-        one H2D copy of that step's inputs and one D2H read of its loss."""
+        one H2D copy of that step's inputs (and one of its labels) and one D2H read of its loss.
+
+        ``data`` may be ``uint8`` (what CIFAR is on disk: 3 KB per image instead of 6 KB as bf16):
+        the bytes are what crosses PCIe, and the device widens them to bf16 with the affine map
+        ``input_affine = (scale[C], shift[C])`` (default: the model's ``input_affine`` attribute, else
+        ``x/255``) in one small kernel (csrc/preprocess.cu: tadnn_u8_to_bf16) before the step.
+        ``depth`` staging buffers are kept in flight on the copy stream (the reference instead
+        keeps its whole shard on the GPU, cifar_example/sgd-torchad_nn-cifar.lua:239-245)."""
         n = data.shape[0]
         nb = max(1, n // batch)
         if not self._cuda:
             for s in range(steps):
                 i = ((start + s) % nb) * batch
-                yield float(self.step(data[i:i + batch], targets[i:i + batch]))
+                x = data[i:i + batch]
+                if x.dtype == torch.uint8:
+                    x = _widen_cpu(x, input_affine or getattr(self.model, "input_affine", None))
+                yield float(self.step(x, targets[i:i + batch]))
             return
         dev = self._params[0].device
         cs = self._copy_stream
         main = torch.cuda.current_stream()
+        depth = max(2, min(int(depth), max(2, steps)))
+        u8 = data.dtype == torch.uint8
+        if u8:
+            from .ops.cnn import u8_to_bf16
+            aff = input_affine or getattr(self.model, "input_affine", None)
+            C = int(data.shape[1]) if data.dim() >= 3 else 1
+            plane = int(data[0].numel() // C)
+            if aff is None:
+                aff = ([1.0 / 255.0] * C, [0.0] * C)
+            wide = [torch.empty((batch,) + tuple(data.shape[1:]), dtype=torch.bfloat16, device=dev) for _ in range(2)]
         bufs = [(torch.empty((batch,) + tuple(data.shape[1:]), dtype=data.dtype, device=dev),
-                 torch.empty((batch,) + tuple(targets.shape[1:]), dtype=targets.dtype, device=dev)) for _ in range(2)]
-        ready = [torch.cuda.Event(), torch.cuda.Event()]
-        consumed = [torch.cuda.Event(), torch.cuda.Event()]
+                 torch.empty((batch,) + tuple(targets.shape[1:]), dtype=targets.dtype, device=dev)) for _ in range(depth)]
+        ready = [torch.cuda.Event() for _ in range(depth)]
+        consumed = [torch.cuda.Event() for _ in range(depth)]
         host_loss = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
         loss_ev = [torch.cuda.Event(), torch.cuda.Event()]
 
         def issue(s):
-            k = s & 1
+            k = s % depth
             i = ((start + s) % nb) * batch
             with torch.cuda.stream(cs):
-                if s >= 2:
+                if s >= depth:
                     cs.wait_event(consumed[k])
                 bufs[k][0].copy_(data[i:i + batch], non_blocking=True)
                 bufs[k][1].copy_(targets[i:i + batch], non_blocking=True)
                 ready[k].record(cs)
 
-        issue(0)
+        for s in range(min(depth - 1, steps)):
+            issue(s)
         for s in range(steps):
-            k = s & 1
-            if s + 1 < steps:
-                issue(s + 1)
+            k = s % depth
+            if s + depth - 1 < steps:
+                issue(s + depth - 1)
             main.wait_event(ready[k])
-            loss = self.step(bufs[k][0], bufs[k][1])
-            consumed[k].record(main)
-            host_loss[k].copy_(loss, non_blocking=True)
-            loss_ev[k].record(main)
+            if u8:
+                x = u8_to_bf16(bufs[k][0], plane, C, aff[0], aff[1], out=wide[s & 1])
+                consumed[k].record(main)  # the staged bytes are free as soon as they are widened
+                loss = self.step(x, bufs[k][1])
+            else:
+                loss = self.step(bufs[k][0], bufs[k][1])
+                consumed[k].record(main)
+            j = s & 1
+            host_loss[j].copy_(loss, non_blocking=True)
+            loss_ev[j].record(main)
             if s >= 1:
-                loss_ev[k ^ 1].synchronize()
-                yield float(host_loss[k ^ 1])
+                loss_ev[j ^ 1].synchronize()
+                yield float(host_loss[j ^ 1])
         if steps >= 1:
-            k = (steps - 1) & 1
-            loss_ev[k].synchronize()
-            yield float(host_loss[k])
+            j = (steps - 1) & 1
+            loss_ev[j].synchronize()
+            yield float(host_loss[j])
         self.h2d_bytes_per_step = batch * (data[0].numel() * data.element_size() + targets[0].numel() * targets.element_size())
         self.d2h_bytes_per_step = 4
+
+
+def _widen_cpu(x: torch.Tensor, aff):
+    C = int(x.shape[1]) if x.dim() >= 3 else 1
+    if aff is None:
+        aff = ([1.0 / 255.0] * C, [0.0] * C)
+    shape = [1, C] + [1] * (x.dim() - 2) if x.dim() >= 3 else [1] * x.dim()
+    sc = torch.tensor(list(aff[0]), dtype=torch.float32).view(shape)
+    sh = torch.tensor(list(aff[1]), dtype=torch.float32).view(shape)
+    return x.float() * sc + sh

@@ -56,63 +56,103 @@ def max_over_ranks(value: float) -> float:
 
 
 class ClockSampler:
-    """Samples ``nvidia-smi`` SM clocks / throttle reasons in a background thread DURING a timed
-    region (the profiling recipe's clocks line).  ``summary()`` gives the bench JSON's ``clocks``."""
+    """Samples SM clocks / throttle reasons DURING a timed region (the profiling recipe's clocks
+    line).  ``summary()`` gives the bench JSON's ``clocks``.
+
+    Primary source: NVML in-process (``pynvml``), polled every ``period_ms`` (default 2 ms) from a
+    background thread — a 20-step timed region of the flagship bench lasts ~12 ms, far below the
+    granularity of ``nvidia-smi -lms``.  ``start()`` and ``stop()`` each take one synchronous
+    sample, so a summary never comes back empty.  Fallback when NVML cannot be loaded: the same
+    fields through one ``nvidia-smi`` call per sample."""
 
     QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+    _REASONS = (("hw_slowdown", 0x8), ("hw_thermal_slowdown", 0x40), ("sw_thermal_slowdown", 0x20),
+                ("sw_power_cap", 0x4))
 
-    def __init__(self, gpu_index: int = 0, period_ms: int = 50):
+    def __init__(self, gpu_index: int = 0, period_ms: float = 2.0):
         self.gpu = gpu_index
         self.period_ms = period_ms
-        self.rows: List[List[str]] = []
-        self._proc: Optional[subprocess.Popen] = None
+        self.rows: List[tuple] = []      # (sm_mhz, sm_max_mhz, reason bitmask)
         self._thr: Optional[threading.Thread] = None
+        self._stop = threading.Event()
+        self._nvml = None
+        self._h = None
+        self._max = None
+        self.source = None
+
+    def _open(self):
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            h = None
+            try:
+                uuid = str(torch.cuda.get_device_properties(self.gpu).uuid)
+                if not uuid.startswith("GPU-"):
+                    uuid = "GPU-" + uuid
+                h = pynvml.nvmlDeviceGetHandleByUUID(uuid)
+            except Exception:
+                h = pynvml.nvmlDeviceGetHandleByIndex(self.gpu)
+            self._nvml, self._h = pynvml, h
+            self._max = float(pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM))
+            self.source = "nvml"
+        except Exception:
+            self._nvml = None
+            self.source = "nvidia-smi"
+
+    def sample_once(self):
+        if self._nvml is not None:
+            try:
+                n, h = self._nvml, self._h
+                sm = float(n.nvmlDeviceGetClockInfo(h, n.NVML_CLOCK_SM))
+                try:
+                    bits = int(n.nvmlDeviceGetCurrentClocksEventReasons(h))
+                except Exception:
+                    bits = int(n.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                self.rows.append((sm, self._max, bits))
+                return
+            except Exception:
+                pass
+        try:
+            out = subprocess.run(["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits"],
+                                 capture_output=True, text=True, timeout=10).stdout
+            for line in out.splitlines():
+                parts = [q.strip() for q in line.split(",")]
+                if len(parts) >= 9:
+                    bits = 0
+                    for (name, bit), v in zip(self._REASONS, parts[5:9]):
+                        if v.lower().startswith("active"):
+                            bits |= bit
+                    self.rows.append((float(parts[1]), float(parts[2]), bits))
+        except Exception:
+            pass
 
     def start(self):
-        try:
-            self._proc = subprocess.Popen(
-                ["nvidia-smi", f"--id={self.gpu}", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
-                 "-lms", str(self.period_ms)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
-        except OSError:
-            self._proc = None
-            return self
-
-        def pump():
-            for line in self._proc.stdout:
-                parts = [p.strip() for p in line.split(",")]
-                if len(parts) >= 9:
-                    self.rows.append(parts)
-        self._thr = threading.Thread(target=pump, daemon=True)
-        self._thr.start()
+        self._open()
+        self.sample_once()
+        if self._nvml is not None:
+            def pump():
+                while not self._stop.wait(self.period_ms / 1e3):
+                    self.sample_once()
+            self._thr = threading.Thread(target=pump, daemon=True)
+            self._thr.start()
         return self
 
     def stop(self):
-        if self._proc is not None:
-            self._proc.terminate()
-            try:
-                self._proc.wait(timeout=2)
-            except subprocess.TimeoutExpired:
-                self._proc.kill()
+        self._stop.set()
         if self._thr is not None:
             self._thr.join(timeout=2)
+        self.sample_once()
         return self
 
     def summary(self) -> dict:
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        if not self.rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0, "source": self.source}
+        sm = sorted(r[0] for r in self.rows)
+        bits = 0
         for r in self.rows:
-            try:
-                sm.append(float(r[1]))
-                mx.append(float(r[2]))
-            except ValueError:
-                continue
-            for name, v in zip(names, r[5:9]):
-                if v.lower().startswith("active"):
-                    reasons.add(name)
-        if not sm:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        sm.sort()
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons),
-                "samples": len(sm)}
+            bits |= r[2]
+        reasons = [name for name, bit in self._REASONS if bits & bit]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(r[1] for r in self.rows), "reasons": reasons,
+                "samples": len(sm), "source": self.source}

@@ -453,7 +453,6 @@ __global__ void conv_wgrad_unpack_kernel(const float* __restrict__ dwp, float* _
 // p2 [B, D] bf16  -> dropout(p) -> fc1 (H x D) + ReLU -> fc2 (NC x H) -> log-softmax -> NLL(target)
 // D = 64, H = 100, NC = 10 for the reference model; limits: D <= 64, H <= 128, NC <= 32.
 constexpr int kHeadD = 64, kHeadH = 128, kHeadC = 32;
-constexpr int kHeadChunk = 32;  // samples staged per block iteration in backward
 
 struct HeadArgs {
   const __nv_bfloat16* p2;   // [B, D]
@@ -469,171 +468,319 @@ struct HeadArgs {
   float* loss;               // [1] mean loss
   // backward only
   float *gw1, *gb1, *gw2, *gb2;  // fp32 gradient accumulators (+=)
-  __nv_bfloat16* dp2;            // [B, D]
+  __nv_bfloat16* dp2;            // [B, D] (optional)
   float grad_scale;              // dLoss (normally 1): gradients are d(mean loss) * grad_scale
   const float* grad_scale_dev;   // optional device scalar folded into grad_scale
+  // backward, optional: route dp2 through the preceding ReLU + 3x3 max-pool in the same pass
+  const unsigned char* pool_idx; // [B, D] arg-max position (0..8) of the pooling window
+  __nv_bfloat16* dpre;           // [B*9, D]: row s*9+pos gets dp2[s] where pos is the arg-max and p2 > 0, else 0
+  float* gbias_pre;              // [D] += sum_s dp2[s] * (p2[s] > 0)   (bias gradient of the layer before the pool)
 };
 
+// Both head kernels work on chunks of 32 samples with register-tiled inner products (4 samples x 4
+// hidden units per thread in the forward; 4 x 2 and 4 x 8 tiles in the backward): two 16-byte
+// shared-memory loads feed 16 FMAs, where the first version (one warp per sample) fed one.
+constexpr int kHeadS = 32;
+__host__ __device__ constexpr int head_hp(int H) { return (H + 3) & ~3; }
+
 __global__ void __launch_bounds__(256) head_fwd_kernel(HeadArgs a) {
-  extern __shared__ float sm[];
-  float* w1t = sm;                         // [D][H]
-  float* w2t = w1t + a.D * a.H;            // [H][NC]
-  float* b1 = w2t + a.H * a.NC;            // [H]
-  float* b2 = b1 + a.H;                    // [NC]
-  float* dbuf = b2 + a.NC;                 // [8 warps][D]
-  float* hb = dbuf + 8 * kHeadD;           // [8 warps][H]
-  __shared__ float block_loss[8];
+  extern __shared__ __align__(16) float sm[];
+  const int HP = head_hp(a.H);
+  float* w1t = sm;                          // [64][HP]   w1t[i*HP + j] = w1[j][i]
+  float* w2s = w1t + kHeadD * HP;           // [NC][HP]
+  float* b1 = w2s + a.NC * HP;              // [HP]
+  float* b2 = b1 + HP;                      // [32]
+  float* sdt = b2 + kHeadC;                 // [64][32]   dropped input, sample-minor
+  float* sh = sdt + kHeadD * kHeadS;        // [32][HP]
+  float* slog = sh + kHeadS * HP;           // [32][32]
+  __shared__ float block_loss;
   __shared__ bool is_last;
-  for (int i = threadIdx.x; i < a.D * a.H; i += blockDim.x) { const int j = i / a.D, d = i % a.D; w1t[d * a.H + j] = a.w1[i]; }
-  for (int i = threadIdx.x; i < a.H * a.NC; i += blockDim.x) { const int c = i / a.H, j = i % a.H; w2t[j * a.NC + c] = a.w2[i]; }
-  for (int i = threadIdx.x; i < a.H; i += blockDim.x) b1[i] = a.b1[i];
-  for (int i = threadIdx.x; i < a.NC; i += blockDim.x) b2[i] = a.b2[i];
-  __syncthreads();
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  float* d = dbuf + warp * kHeadD;
-  float* h = hb + warp * a.H;
+  const int t = threadIdx.x;
+  for (int i = t; i < kHeadD * HP; i += 256) {
+    const int d = i / HP, j = i - d * HP;
+    w1t[i] = (d < a.D && j < a.H) ? a.w1[j * a.D + d] : 0.f;
+  }
+  for (int i = t; i < a.NC * HP; i += 256) {
+    const int c = i / HP, j = i - c * HP;
+    w2s[i] = j < a.H ? a.w2[c * a.H + j] : 0.f;
+  }
+  for (int i = t; i < HP; i += 256) b1[i] = i < a.H ? a.b1[i] : 0.f;
+  if (t < kHeadC) b2[t] = t < a.NC ? a.b2[t] : 0.f;
+  const int nJ = HP >> 2;
+  const int jq = t % nJ, sq = t / nJ;       // phase-1 tile: hidden units 4*jq.., samples 4*sq..
   float my_loss = 0.f;
-  for (int s = blockIdx.x * 8 + warp; s < a.B; s += gridDim.x * 8) {
-    for (int i = lane; i < a.D; i += 32)
-      d[i] = __bfloat162float(a.p2[static_cast<long long>(s) * a.D + i]) * dropout_scale(a.seed, static_cast<uint32_t>(s) * a.D + i, a.p);
-    __syncwarp();
-    for (int j = lane; j < a.H; j += 32) {
-      float acc = b1[j];
-      for (int i = 0; i < a.D; ++i) acc += w1t[i * a.H + j] * d[i];
-      acc = fmaxf(acc, 0.f);
-      h[j] = acc;
-      a.hbuf[static_cast<long long>(s) * a.H + j] = acc;
+  const int chunks = (a.B + kHeadS - 1) / kHeadS;
+  for (int ch = blockIdx.x; ch < chunks; ch += gridDim.x) {
+    const int base = ch * kHeadS;
+    __syncthreads();
+    for (int i = t; i < kHeadS * kHeadD; i += 256) {
+      const int s = i >> 6, d = i & 63;
+      float v = 0.f;
+      if (base + s < a.B && d < a.D)
+        v = __bfloat162float(a.p2[static_cast<long long>(base + s) * a.D + d]) *
+            dropout_scale(a.seed, static_cast<uint32_t>(base + s) * a.D + d, a.p);
+      sdt[d * kHeadS + s] = v;
     }
-    __syncwarp();
-    float logit = -INFINITY;
-    if (lane < a.NC) {
-      float acc = b2[lane];
-      for (int j = 0; j < a.H; ++j) acc += w2t[j * a.NC + lane] * h[j];
-      logit = acc;
+    __syncthreads();
+    if (sq < kHeadS / 4) {
+      float acc[4][4];
+#pragma unroll
+      for (int x = 0; x < 4; ++x)
+#pragma unroll
+        for (int y = 0; y < 4; ++y) acc[x][y] = 0.f;
+#pragma unroll 8
+      for (int i = 0; i < kHeadD; ++i) {
+        const float4 dv = *reinterpret_cast<const float4*>(sdt + i * kHeadS + 4 * sq);
+        const float4 wv = *reinterpret_cast<const float4*>(w1t + i * HP + 4 * jq);
+        const float ds[4] = {dv.x, dv.y, dv.z, dv.w}, ws[4] = {wv.x, wv.y, wv.z, wv.w};
+#pragma unroll
+        for (int x = 0; x < 4; ++x)
+#pragma unroll
+          for (int y = 0; y < 4; ++y) acc[x][y] = fmaf(ds[x], ws[y], acc[x][y]);
+      }
+#pragma unroll
+      for (int x = 0; x < 4; ++x) {
+        const int s = 4 * sq + x;
+        float4 o;
+        o.x = fmaxf(acc[x][0] + b1[4 * jq], 0.f); o.y = fmaxf(acc[x][1] + b1[4 * jq + 1], 0.f);
+        o.z = fmaxf(acc[x][2] + b1[4 * jq + 2], 0.f); o.w = fmaxf(acc[x][3] + b1[4 * jq + 3], 0.f);
+        *reinterpret_cast<float4*>(sh + s * HP + 4 * jq) = o;
+      }
     }
-    const float mx = warp_max(logit);
-    const float e = lane < a.NC ? __expf(logit - mx) : 0.f;
-    const float lse = mx + __logf(warp_sum(e));
-    const float lp = logit - lse;
-    if (lane < a.NC) a.logp[static_cast<long long>(s) * a.NC + lane] = lp;
-    const int t = static_cast<int>(a.target[s]);
-    const float lt = __shfl_sync(0xffffffffu, lp, t & 31);
-    if (lane == 0) my_loss -= lt;
-    __syncwarp();
+    __syncthreads();
+    for (int i = t; i < kHeadS * a.H; i += 256) {   // hidden -> global (coalesced)
+      const int s = i / a.H, j = i - s * a.H;
+      if (base + s < a.B) a.hbuf[static_cast<long long>(base + s) * a.H + j] = sh[s * HP + j];
+    }
+    for (int it = t; it < kHeadS * a.NC; it += 256) {
+      const int s = it / a.NC, c = it - s * a.NC;
+      float acc = b2[c];
+      const float* hr = sh + s * HP;
+      const float* wr = w2s + c * HP;
+      for (int j = 0; j < HP; ++j) acc = fmaf(hr[j], wr[j], acc);
+      slog[s * kHeadC + c] = acc;
+    }
+    __syncthreads();
+    if (t < kHeadS && base + t < a.B) {
+      const float* lg = slog + t * kHeadC;
+      float mx = -INFINITY;
+      for (int c = 0; c < a.NC; ++c) mx = fmaxf(mx, lg[c]);
+      float se = 0.f;
+      for (int c = 0; c < a.NC; ++c) se += __expf(lg[c] - mx);
+      const float lse = mx + __logf(se);
+      const int tg = static_cast<int>(a.target[base + t]);
+      float* lp = a.logp + static_cast<long long>(base + t) * a.NC;
+      for (int c = 0; c < a.NC; ++c) lp[c] = lg[c] - lse;
+      if (tg >= 0 && tg < a.NC) my_loss -= lg[tg] - lse;
+    }
   }
   // deterministic mean: per-block partials in scratch, summed in block order by the last block
-  if (lane == 0) block_loss[warp] = my_loss;
+  if (t < 32) {
+    const float tot = warp_sum(my_loss);   // fixed shuffle tree: bit-reproducible
+    if (t == 0) block_loss = tot;
+  }
   __syncthreads();
-  if (threadIdx.x == 0) {
-    float t = 0.f;
-    for (int w = 0; w < 8; ++w) t += block_loss[w];
-    a.loss_partial[blockIdx.x] = t;
+  if (t == 0) {
+    a.loss_partial[blockIdx.x] = block_loss;
     __threadfence();
     const unsigned done = atomicAdd(a.counter, 1u);
     is_last = (done == gridDim.x - 1);
   }
   __syncthreads();
-  if (is_last && threadIdx.x == 0) {
+  if (is_last && t == 0) {
     __threadfence();
-    float t = 0.f;
-    for (unsigned b = 0; b < gridDim.x; ++b) t += reinterpret_cast<volatile float*>(a.loss_partial)[b];
-    *a.loss = t / static_cast<float>(a.B);
+    float tot = 0.f;
+    for (unsigned b = 0; b < gridDim.x; ++b) tot += reinterpret_cast<volatile float*>(a.loss_partial)[b];
+    *a.loss = tot / static_cast<float>(a.B);
     *a.counter = 0u;  // ready for the next launch
   }
 }
 
 __global__ void __launch_bounds__(256) head_bwd_kernel(HeadArgs a) {
-  extern __shared__ float sm[];
-  float* w1 = sm;                                  // [H][D]  (row-major, as stored)
-  float* w2t = w1 + a.H * a.D;                     // [H][NC]
-  float* sd = w2t + a.H * a.NC;                    // [chunk][D]   dropped input
-  float* sdh = sd + kHeadChunk * kHeadD;           // [chunk][H]   dL/d(pre-ReLU hidden)
-  float* sh = sdh + kHeadChunk * a.H;              // [chunk][H]   hidden
-  float* sdl = sh + kHeadChunk * a.H;              // [chunk][NC]  dL/dlogits
-  for (int i = threadIdx.x; i < a.H * a.D; i += blockDim.x) w1[i] = a.w1[i];
-  for (int i = threadIdx.x; i < a.H * a.NC; i += blockDim.x) { const int c = i / a.H, j = i % a.H; w2t[j * a.NC + c] = a.w2[i]; }
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  extern __shared__ __align__(16) float sm[];
+  const int HP = head_hp(a.H);
+  float* w1s = sm;                          // [HP][64]  as stored (row j), zero padded
+  float* w2s = w1s + HP * kHeadD;           // [NC][HP]
+  float* sd = w2s + a.NC * HP;              // [32][64]  dropped input
+  float* sdh = sd + kHeadS * kHeadD;        // [32][HP]  dL/d(pre-ReLU hidden)
+  float* sdht = sdh + kHeadS * HP;          // [HP][32]  same, transposed
+  float* sh = sdht + HP * kHeadS;           // [32][HP]  hidden
+  float* sdl = sh + kHeadS * HP;            // [32][32]  dL/dlogits
+  float* sgb = sdl + kHeadS * kHeadC;       // [8][64]   bias-gradient partials of the layer before the pool
+  const int t = threadIdx.x;
+  for (int i = t; i < HP * kHeadD; i += 256) {
+    const int j = i >> 6, d = i & 63;
+    w1s[i] = (j < a.H && d < a.D) ? a.w1[j * a.D + d] : 0.f;
+  }
+  for (int i = t; i < a.NC * HP; i += 256) {
+    const int c = i / HP, j = i - c * HP;
+    w2s[i] = j < a.H ? a.w2[c * a.H + j] : 0.f;
+  }
   const float inv_b = a.grad_scale * (a.grad_scale_dev != nullptr ? *a.grad_scale_dev : 1.0f) / static_cast<float>(a.B);
-  // register accumulators: thread t owns gw1 entries t, t+256, ... and gw2 entries t, t+256, ...
-  constexpr int kW1PerThread = (kHeadH * kHeadD + 255) / 256;  // 32
-  constexpr int kW2PerThread = (kHeadC * kHeadH + 255) / 256;  // 16
-  float acc1[kW1PerThread], acc2[kW2PerThread];
+  const int nJ = HP >> 2;
+  // register accumulators
+  float acc1[4][8];                          // gw1 tile: hidden 4*jq.. x input 8*iq..   (threads < nJ*8)
 #pragma unroll
-  for (int k = 0; k < kW1PerThread; ++k) acc1[k] = 0.f;
+  for (int x = 0; x < 4; ++x)
+#pragma unroll
+    for (int y = 0; y < 8; ++y) acc1[x][y] = 0.f;
+  constexpr int kW2PerThread = (kHeadC * kHeadH + 255) / 256;  // 16
+  float acc2[kW2PerThread];
 #pragma unroll
   for (int k = 0; k < kW2PerThread; ++k) acc2[k] = 0.f;
-  float accb = 0.f;  // threads 0..H-1: gb1[t]; threads H..H+NC-1: gb2[t-H]
-  const int n1 = a.H * a.D, n2 = a.NC * a.H;
-  __syncthreads();
-  for (int base = blockIdx.x * kHeadChunk; base < a.B; base += gridDim.x * kHeadChunk) {
-    const int ns = min(kHeadChunk, a.B - base);
-    // phase A: one warp per sample
-    for (int ls = warp; ls < ns; ls += 8) {
-      const int s = base + ls;
-      float* d = sd + ls * kHeadD;
-      float* dh = sdh + ls * a.H;
-      float* hh = sh + ls * a.H;
-      float* dl = sdl + ls * a.NC;
-      for (int i = lane; i < a.D; i += 32)
-        d[i] = __bfloat162float(a.p2[static_cast<long long>(s) * a.D + i]) * dropout_scale(a.seed, static_cast<uint32_t>(s) * a.D + i, a.p);
-      const int t = static_cast<int>(a.target[s]);
-      if (lane < a.NC) dl[lane] = (__expf(a.logp[static_cast<long long>(s) * a.NC + lane]) - (lane == t ? 1.f : 0.f)) * inv_b;
-      __syncwarp();
-      for (int j = lane; j < a.H; j += 32) {
-        const float hv = a.hbuf[static_cast<long long>(s) * a.H + j];
-        float g = 0.f;
-        for (int c = 0; c < a.NC; ++c) g += dl[c] * w2t[j * a.NC + c];
-        hh[j] = hv;
-        dh[j] = hv > 0.f ? g : 0.f;
+  float accb = 0.f;                          // threads 0..H-1: gb1[t]; threads 128..128+NC-1: gb2[t-128]
+  float accp[2] = {0.f, 0.f};                // bias gradient before the pool, channels 2*ip, 2*ip+1
+  const int jq = t >> 3, iq = t & 7;         // gw1 tile
+  const int ip = t & 31, sg = t >> 5;        // dgrad tile: channels 2*ip.., samples 4*sg..
+  const int n2 = a.NC * HP;
+  const int chunks = (a.B + kHeadS - 1) / kHeadS;
+  for (int ch = blockIdx.x; ch < chunks; ch += gridDim.x) {
+    const int base = ch * kHeadS;
+    __syncthreads();
+    // ---- A: stage the chunk
+    for (int i = t; i < kHeadS * kHeadD; i += 256) {
+      const int s = i >> 6, d = i & 63;
+      float v = 0.f;
+      if (base + s < a.B && d < a.D)
+        v = __bfloat162float(a.p2[static_cast<long long>(base + s) * a.D + d]) *
+            dropout_scale(a.seed, static_cast<uint32_t>(base + s) * a.D + d, a.p);
+      sd[i] = v;
+    }
+    for (int i = t; i < kHeadS * HP; i += 256) {
+      const int s = i / HP, j = i - s * HP;
+      sh[i] = (base + s < a.B && j < a.H) ? a.hbuf[static_cast<long long>(base + s) * a.H + j] : 0.f;
+    }
+    for (int i = t; i < kHeadS * kHeadC; i += 256) {
+      const int s = i >> 5, c = i & 31;
+      float v = 0.f;
+      if (base + s < a.B && c < a.NC) {
+        const int tg = static_cast<int>(a.target[base + s]);
+        v = (__expf(a.logp[static_cast<long long>(base + s) * a.NC + c]) - (c == tg ? 1.f : 0.f)) * inv_b;
       }
-      __syncwarp();
-      for (int i = lane; i < a.D; i += 32) {
-        float g = 0.f;
-        for (int j = 0; j < a.H; ++j) g += dh[j] * w1[j * a.D + i];
-        a.dp2[static_cast<long long>(s) * a.D + i] = __float2bfloat16_rn(g * dropout_scale(a.seed, static_cast<uint32_t>(s) * a.D + i, a.p));
-      }
+      sdl[i] = v;
     }
     __syncthreads();
-    // phase B: every thread accumulates its own weight-gradient entries over the staged samples
+    // ---- B: dL/d(pre-ReLU hidden), both layouts
+    for (int i = t; i < kHeadS * HP; i += 256) {
+      const int s = i / HP, j = i - s * HP;
+      float g = 0.f;
+      for (int c = 0; c < a.NC; ++c) g = fmaf(sdl[s * kHeadC + c], w2s[c * HP + j], g);
+      g = sh[i] > 0.f ? g : 0.f;
+      sdh[i] = g;
+      sdht[j * kHeadS + s] = g;
+    }
+    __syncthreads();
+    // ---- C: gradient w.r.t. the input (4 samples x 2 channels per thread), dropout, optional ReLU+pool routing
+    {
+      float acc[4][2] = {{0.f, 0.f}, {0.f, 0.f}, {0.f, 0.f}, {0.f, 0.f}};
+      for (int j = 0; j < a.H; ++j) {
+        const float2 w = *reinterpret_cast<const float2*>(w1s + j * kHeadD + 2 * ip);
+        const float4 g = *reinterpret_cast<const float4*>(sdht + j * kHeadS + 4 * sg);
+        acc[0][0] = fmaf(g.x, w.x, acc[0][0]); acc[0][1] = fmaf(g.x, w.y, acc[0][1]);
+        acc[1][0] = fmaf(g.y, w.x, acc[1][0]); acc[1][1] = fmaf(g.y, w.y, acc[1][1]);
+        acc[2][0] = fmaf(g.z, w.x, acc[2][0]); acc[2][1] = fmaf(g.z, w.y, acc[2][1]);
+        acc[3][0] = fmaf(g.w, w.x, acc[3][0]); acc[3][1] = fmaf(g.w, w.y, acc[3][1]);
+      }
+      if (2 * ip < a.D) {
 #pragma unroll
-    for (int k = 0; k < kW1PerThread; ++k) {
-      const int e = threadIdx.x + k * 256;
-      if (e < n1) {
-        const int j = e / a.D, i = e % a.D;
-        float acc = acc1[k];
-        for (int ls = 0; ls < ns; ++ls) acc += sdh[ls * a.H + j] * sd[ls * kHeadD + i];
-        acc1[k] = acc;
+        for (int x = 0; x < 4; ++x) {
+          const long long s = base + 4 * sg + x;
+          if (s >= a.B) break;
+          const uint32_t e = static_cast<uint32_t>(s) * a.D + 2 * ip;
+          const float g0 = acc[x][0] * dropout_scale(a.seed, e, a.p);
+          const float g1 = (2 * ip + 1 < a.D) ? acc[x][1] * dropout_scale(a.seed, e + 1, a.p) : 0.f;
+          const uint32_t gp = pack_bf16x2(g0, g1);
+          if ((a.D & 1) == 0) {
+            if (a.dp2 != nullptr) *reinterpret_cast<uint32_t*>(a.dp2 + s * a.D + 2 * ip) = gp;
+            if (a.dpre != nullptr) {
+              const uint32_t pv = *reinterpret_cast<const uint32_t*>(a.p2 + s * a.D + 2 * ip);
+              const uint16_t iv = *reinterpret_cast<const uint16_t*>(a.pool_idx + s * a.D + 2 * ip);
+              const uint32_t live = ((pv & 0xffffu) ? 0xffffu : 0u) | ((pv & 0xffff0000u) ? 0xffff0000u : 0u);  // ReLU output > 0
+              const uint32_t gl = gp & live;
+              const float2 gf = unpack_bf16x2(gl);
+              accp[0] += gf.x;
+              accp[1] += gf.y;
+              const uint32_t p0 = iv & 0xffu, p1 = iv >> 8;
+#pragma unroll
+              for (uint32_t pos = 0; pos < 9; ++pos) {
+                const uint32_t m = (p0 == pos ? 0xffffu : 0u) | (p1 == pos ? 0xffff0000u : 0u);
+                *reinterpret_cast<uint32_t*>(a.dpre + (s * 9 + pos) * a.D + 2 * ip) = gl & m;
+              }
+            }
+          } else if (a.dp2 != nullptr) {
+            a.dp2[s * a.D + 2 * ip] = __float2bfloat16_rn(g0);
+            if (2 * ip + 1 < a.D) a.dp2[s * a.D + 2 * ip + 1] = __float2bfloat16_rn(g1);
+          }
+        }
       }
     }
+    // ---- D: fc1 weight gradient tile (4 hidden x 8 inputs per thread)
+    if (jq < nJ) {
+      for (int s = 0; s < kHeadS; ++s) {
+        const float4 g = *reinterpret_cast<const float4*>(sdh + s * HP + 4 * jq);
+        const float4 d0 = *reinterpret_cast<const float4*>(sd + s * kHeadD + 8 * iq);
+        const float4 d1 = *reinterpret_cast<const float4*>(sd + s * kHeadD + 8 * iq + 4);
+        const float gs[4] = {g.x, g.y, g.z, g.w};
+        const float ds[8] = {d0.x, d0.y, d0.z, d0.w, d1.x, d1.y, d1.z, d1.w};
+#pragma unroll
+        for (int x = 0; x < 4; ++x)
+#pragma unroll
+          for (int y = 0; y < 8; ++y) acc1[x][y] = fmaf(gs[x], ds[y], acc1[x][y]);
+      }
+    }
+    // ---- E: fc2 weight gradient, F: bias gradients
 #pragma unroll
     for (int k = 0; k < kW2PerThread; ++k) {
-      const int e = threadIdx.x + k * 256;
+      const int e = t + k * 256;
       if (e < n2) {
-        const int c = e / a.H, j = e % a.H;
+        const int c = e / HP, j = e - c * HP;
         float acc = acc2[k];
-        for (int ls = 0; ls < ns; ++ls) acc += sdl[ls * a.NC + c] * sh[ls * a.H + j];
+        for (int s = 0; s < kHeadS; ++s) acc = fmaf(sdl[s * kHeadC + c], sh[s * HP + j], acc);
         acc2[k] = acc;
       }
     }
-    if (static_cast<int>(threadIdx.x) < a.H) {
-      for (int ls = 0; ls < ns; ++ls) accb += sdh[ls * a.H + threadIdx.x];
-    } else if (static_cast<int>(threadIdx.x) < a.H + a.NC) {
-      for (int ls = 0; ls < ns; ++ls) accb += sdl[ls * a.NC + (threadIdx.x - a.H)];
+    if (t < a.H) {
+      for (int s = 0; s < kHeadS; ++s) accb += sdh[s * HP + t];
+    } else if (t >= 128 && t < 128 + a.NC) {
+      for (int s = 0; s < kHeadS; ++s) accb += sdl[s * kHeadC + (t - 128)];
     }
-    __syncthreads();
   }
+  // ---- flush
+  if (jq < nJ) {
 #pragma unroll
-  for (int k = 0; k < kW1PerThread; ++k) {
-    const int e = threadIdx.x + k * 256;
-    if (e < n1) atomicAdd(a.gw1 + e, acc1[k]);
+    for (int x = 0; x < 4; ++x) {
+      const int j = 4 * jq + x;
+      if (j < a.H) {
+#pragma unroll
+        for (int y = 0; y < 8; ++y) {
+          const int d = 8 * iq + y;
+          if (d < a.D) atomicAdd(a.gw1 + j * a.D + d, acc1[x][y]);
+        }
+      }
+    }
   }
 #pragma unroll
   for (int k = 0; k < kW2PerThread; ++k) {
-    const int e = threadIdx.x + k * 256;
-    if (e < n2) atomicAdd(a.gw2 + e, acc2[k]);
+    const int e = t + k * 256;
+    if (e < n2) {
+      const int c = e / HP, j = e - c * HP;
+      if (j < a.H) atomicAdd(a.gw2 + c * a.H + j, acc2[k]);
+    }
   }
-  if (static_cast<int>(threadIdx.x) < a.H) atomicAdd(a.gb1 + threadIdx.x, accb);
-  else if (static_cast<int>(threadIdx.x) < a.H + a.NC) atomicAdd(a.gb2 + (threadIdx.x - a.H), accb);
+  if (t < a.H) atomicAdd(a.gb1 + t, accb);
+  else if (t >= 128 && t < 128 + a.NC) atomicAdd(a.gb2 + (t - 128), accb);
+  if (a.gbias_pre != nullptr) {
+    __syncthreads();
+    sgb[sg * kHeadD + 2 * ip] = accp[0];
+    sgb[sg * kHeadD + 2 * ip + 1] = accp[1];
+    __syncthreads();
+    if (t < a.D) {
+      float v = 0.f;
+#pragma unroll
+      for (int g = 0; g < 8; ++g) v += sgb[g * kHeadD + t];
+      atomicAdd(a.gbias_pre + t, v);
+    }
+  }
 }
 
 // ---- optimiser / misc elementwise -------------------------------------------------------------
@@ -659,9 +806,15 @@ int grid_for(long long total, int threads) {
   return static_cast<int>(b);
 }
 
-size_t head_fwd_smem(int D, int H, int NC) { return sizeof(float) * (static_cast<size_t>(D) * H + H * NC + H + NC + 8 * kHeadD + 8 * H); }
+size_t head_fwd_smem(int D, int H, int NC) {
+  (void)D;
+  const size_t HP = head_hp(H);
+  return sizeof(float) * (kHeadD * HP + NC * HP + HP + kHeadC + kHeadD * kHeadS + kHeadS * HP + kHeadS * kHeadC);
+}
 size_t head_bwd_smem(int D, int H, int NC) {
-  return sizeof(float) * (static_cast<size_t>(H) * D + H * NC + kHeadChunk * kHeadD + 2 * kHeadChunk * H + kHeadChunk * NC);
+  (void)D;
+  const size_t HP = head_hp(H);
+  return sizeof(float) * (HP * kHeadD + NC * HP + kHeadS * kHeadD + 3 * kHeadS * HP + kHeadS * kHeadC + 8 * kHeadD);
 }
 
 }  // namespace
@@ -828,6 +981,9 @@ static HeadArgs to_dev(const tadnn_head_args* h) {
   a.dp2 = static_cast<__nv_bfloat16*>(h->dp2);
   a.grad_scale = h->grad_scale;
   a.grad_scale_dev = h->grad_scale_dev;
+  a.pool_idx = static_cast<const unsigned char*>(h->pool_idx);
+  a.dpre = static_cast<__nv_bfloat16*>(h->dpre);
+  a.gbias_pre = h->gbias_pre;
   return a;
 }
 
@@ -843,7 +999,7 @@ extern "C" int tadnn_head_forward(const tadnn_head_args* h, void* workspace, tad
   HeadArgs a = to_dev(h);
   a.loss_partial = static_cast<float*>(workspace);
   a.counter = reinterpret_cast<unsigned int*>(static_cast<uint8_t*>(workspace) + sizeof(float) * 1024);
-  int blocks = (h->B + 7) / 8;
+  int blocks = (h->B + kHeadS - 1) / kHeadS;
   const int cap = sm_count() * 2 < 1024 ? sm_count() * 2 : 1024;
   if (blocks > cap) blocks = cap;
   const size_t smem = head_fwd_smem(h->D, h->H, h->NC);
@@ -867,7 +1023,7 @@ static __device__ __align__(256) unsigned char tadnn_head_noalloc_scratch[2048];
 
 namespace {
 constexpr int kNoAllocMaxBlocks = 256;                      // partial-sum slots that fit in the array
-constexpr int kNoAllocMaxBatch = kNoAllocMaxBlocks * 8 * 32;  // 8 warps/block, <= 32 samples/warp: 65536
+constexpr int kNoAllocMaxBatch = 65536;                    // samples per call this entry point accepts
 constexpr size_t kNoAllocCounterOffset = 1024;              // 256 floats of partials, then the counter
 std::mutex g_noalloc_mu;
 void* g_noalloc_ptr[64] = {nullptr};                        // device address of the array, per device
@@ -902,7 +1058,7 @@ extern "C" int tadnn_head_forward_noalloc(const tadnn_head_args* h, tadnn_stream
   // The array is shared by every call and still holds whatever the previous call left behind.
   // Only the completion counter has to start at zero; the partial sums are overwritten before use.
   TADNN_CHECK_CUDA(cudaMemsetAsync(a.counter, 0, sizeof(unsigned int), stream));
-  int blocks = (h->B + 7) / 8;
+  int blocks = (h->B + kHeadS - 1) / kHeadS;
   if (blocks > kNoAllocMaxBlocks) blocks = kNoAllocMaxBlocks;
   head_fwd_kernel<<<blocks, 256, smem, stream>>>(a);
   TADNN_LAUNCH_CHECK("head_fwd_noalloc");
@@ -913,7 +1069,8 @@ extern "C" int tadnn_head_backward(const tadnn_head_args* h, tadnn_stream_t stre
   if (int rc = head_check(h, "head_backward")) return rc;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   HeadArgs a = to_dev(h);
-  int blocks = (h->B + kHeadChunk - 1) / kHeadChunk;
+  TADNN_REQUIRE(h->dpre == nullptr || (h->pool_idx != nullptr && h->D % 2 == 0), "head_backward: dpre needs pool_idx and an even D");
+  int blocks = (h->B + kHeadS - 1) / kHeadS;
   if (blocks > sm_count()) blocks = sm_count();
   const size_t smem = head_bwd_smem(h->D, h->H, h->NC);
   static std::atomic<unsigned long long> attr{0};

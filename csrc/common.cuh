@@ -52,6 +52,10 @@ inline int ceil_div(long long a, long long b) { return (int)((a + b - 1) / b); }
 
 int sm_count();  // cached multiProcessorCount of the current device
 
+// Tiled bf16 tensor map of rank 2..5, SWIZZLE_128B; dimensions innermost-first (core.cu).
+int encode_tmap_bf16(CUtensorMap* out, const void* ptr, int rank, const unsigned long long* gdim,
+                     const unsigned long long* gstride_bytes, const unsigned int* box);
+
 // Opt a kernel into more than 48 KB of dynamic shared memory, once per (call site, device): `done` is a
 // call-site static holding one bit per device ordinal, so a process that drives several GPUs sets the
 // attribute on each of them, and concurrent first calls are harmless (the attribute is idempotent).

@@ -42,6 +42,7 @@ struct Conv1Args {
   unsigned char* idx1;        // [B, 9, 9, 64]
   const __nv_bfloat16* dp1;   // backward: [B, 9, 9, 64]
   float* gw;                  // backward: [64, 75] Torch7 layout (c,kh,kw), accumulated with red.add
+  float* gb;                  // backward, optional: [64] bias gradient (+=) = sum over windows of dp1 * (p1 > 0)
   int B;
   int dph, dpw;               // backward: dp1 is stored compactly as [B, dph, dpw, 64] (zero outside), dph,dpw <= 9
 };
@@ -305,6 +306,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args 
   uint8_t* imgbuf = gbuf + 2 * kBlockBytes;
   __shared__ __align__(8) uint64_t ab_full[2], ab_empty[2], done_bar, img_full[2][2];
   __shared__ uint32_t tmem_base_smem;
+  __shared__ float s_gb[16][kO];   // bias-gradient partials of the 16 window slots
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long total_win = static_cast<long long>(a.B) * kWinPerImg;
@@ -406,6 +408,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args 
     uint4 dv = make_uint4(0, 0, 0, 0), pv = dv, ndv = dv, npv = dv;
     uint2 iv = make_uint2(0, 0), niv = iv;
     bool ok = false, nok = false;
+    float gbias[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     fetch(blockIdx.x, dv, pv, iv, ok);
     int i = 0;
     for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x, ++i) {
@@ -423,6 +426,9 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args 
         for (int e = 0; e < 4; ++e) {
           const uint32_t nz = ((pw[e] & 0xffffu) ? 0xffffu : 0u) | ((pw[e] & 0xffff0000u) ? 0xffff0000u : 0u);
           dw[e] = ok ? (dw[e] & nz) : 0u;
+          const float2 gf = unpack_bf16x2(dw[e]);   // conv bias gradient: the pooled gradient where ReLU was active
+          gbias[2 * e] += gf.x;
+          gbias[2 * e + 1] += gf.y;
         }
 #pragma unroll
         for (int pos = 0; pos < 9; ++pos) {
@@ -440,6 +446,17 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args 
       fence_proxy_async_smem();
       mbar_arrive(&ab_full[s]);
       dv = ndv; pv = npv; iv = niv; ok = nok;
+    }
+    if (a.gb != nullptr) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) s_gb[wl][j * 8 + e] = gbias[e];
+      asm volatile("bar.sync 6, 128;" ::: "memory");
+      if (gt < kO) {
+        float v = 0.f;
+#pragma unroll
+        for (int w = 0; w < kWinPerTile; ++w) v += s_gb[w][gt];
+        atomicAdd(a.gb + gt, v);
+      }
     }
     // final epilogue: accumulator rows = patch index k, columns = output channel
     if (has_work) {
@@ -512,6 +529,11 @@ extern "C" int tadnn_conv1_pool_forward(const void* x, const void* w_packed, con
 
 extern "C" int tadnn_conv1_pool_backward(const void* x, const void* dp1, int dp1_h, int dp1_w, const void* p1, const void* idx1,
                                          float* grad_weight, int B, tadnn_stream_t stream) {
+  return tadnn_conv1_pool_backward_bias(x, dp1, dp1_h, dp1_w, p1, idx1, grad_weight, nullptr, B, stream);
+}
+
+extern "C" int tadnn_conv1_pool_backward_bias(const void* x, const void* dp1, int dp1_h, int dp1_w, const void* p1, const void* idx1,
+                                              float* grad_weight, float* grad_bias, int B, tadnn_stream_t stream) {
   TADNN_REQUIRE(B > 0 && B <= 20000000, "conv1_pool_backward: batch %d out of range", B);
   TADNN_REQUIRE(dp1_h >= 1 && dp1_h <= kPH && dp1_w >= 1 && dp1_w <= kPW, "conv1_pool_backward: dp1 extent %dx%d out of range", dp1_h, dp1_w);
   TADNN_REQUIRE(((reinterpret_cast<uintptr_t>(dp1) | reinterpret_cast<uintptr_t>(p1) | reinterpret_cast<uintptr_t>(idx1)) & 15) == 0,
@@ -524,7 +546,7 @@ extern "C" int tadnn_conv1_pool_backward(const void* x, const void* dp1, int dp1
   a.x = static_cast<const __nv_bfloat16*>(x); a.dp1 = static_cast<const __nv_bfloat16*>(dp1);
   a.p1 = const_cast<__nv_bfloat16*>(static_cast<const __nv_bfloat16*>(p1));
   a.idx1 = const_cast<unsigned char*>(static_cast<const unsigned char*>(idx1));
-  a.gw = grad_weight; a.B = B; a.dph = dp1_h; a.dpw = dp1_w;
+  a.gw = grad_weight; a.gb = grad_bias; a.B = B; a.dph = dp1_h; a.dpw = dp1_w;
   const long long tiles = (static_cast<long long>(B) * kWinPerImg + kWinPerTile - 1) / kWinPerTile;
   const int grid = tiles < sm_count() ? static_cast<int>(tiles) : sm_count();
   if (dp1_h == kPH && dp1_w == kPW) conv1_bwd_kernel<false><<<grid, kThreads, kBwdSmem, static_cast<cudaStream_t>(stream)>>>(a);

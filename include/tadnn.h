@@ -268,12 +268,32 @@ int tadnn_conv_wgrad_unpack(const float* dwp, float* grad, int O, int C, int KH,
  * w_packed: bf16 [64,80] produced by tadnn_conv1_weight_pack from the Torch7 fp32 [64,75] weight;
  * grad_weight: fp32 [64,75] in the Torch7 order, accumulated (+=). */
 int tadnn_conv1_weight_pack(const float* w, void* w_packed, tadnn_stream_t stream);
+/* Second stage (csrc/conv2_fused.cu; cifar_example/sgd-torchad_nn-cifar.lua:96-98): conv5x5(64->64) + bias +
+ * ReLU + maxpool3/3 on p1 [B,9,9,64] as ONE implicit-GEMM kernel whose A tiles are 4-D TMA boxes of p1 (no
+ * im2col matrix); writes p2 [B,64] bf16 and the arg-max bytes idx2 [B,64] (and the un-pooled activation
+ * a2 [B,5,5,64] if non-NULL).  w2_packed: bf16 [64, 1600], k = tap*64 + c (tadnn_cnn_pack_shadows).
+ * tadnn_conv2_wgrad: dw_packed[o, tap*64 + c] += sum over images and the 3x3 window of
+ * da2w[n*9+pos, o] * p1[n, py+kh, px+kw, c], the operands again TMA boxes of p1 (MN-major);
+ * tadnn_conv2_wgrad_unpack adds dw_packed into the Torch7-layout gradient [64, 1600] and zeroes it.
+ * tadnn_cnn_pack_shadows rebuilds, in one launch, the bf16 operand copies of the fp32 master weights:
+ * w1_packed [64,80], w2_packed [64,1600] and the Toeplitz matrix [576, 4032] of the transposed conv. */
+int tadnn_conv2_pool_forward(const void* p1, const void* w2_packed, const float* bias, void* p2, void* idx2,
+                             void* a2, int B, tadnn_stream_t stream);
+int tadnn_conv2_wgrad(const void* p1, const void* da2w, float* dw_packed, int B, tadnn_stream_t stream);
+int tadnn_conv2_wgrad_unpack(float* dw_packed, float* grad_weight, tadnn_stream_t stream);
+int tadnn_cnn_pack_shadows(const float* w1, const float* w2, void* w1_packed, void* w2_packed,
+                           void* toeplitz_t, tadnn_stream_t stream);
 int tadnn_conv1_pool_forward(const void* x, const void* w_packed, const float* bias, void* p1,
                              void* idx1, int B, tadnn_stream_t stream);
 /* dp1 may be stored compactly as [B, dp1_h, dp1_w, 64] (its non-zero top-left corner); pass 9, 9
  * for the full tensor. */
 int tadnn_conv1_pool_backward(const void* x, const void* dp1, int dp1_h, int dp1_w, const void* p1,
                               const void* idx1, float* grad_weight, int B, tadnn_stream_t stream);
+/* Same, and grad_bias[64] += sum over pooling windows of dp1 * (p1 > 0) in the same pass (the kernel
+ * already loads both for every window); grad_bias may be NULL. */
+int tadnn_conv1_pool_backward_bias(const void* x, const void* dp1, int dp1_h, int dp1_w, const void* p1,
+                                   const void* idx1, float* grad_weight, float* grad_bias, int B,
+                                   tadnn_stream_t stream);
 
 /* Fused classifier head: dropout -> Linear(D,H)+ReLU -> Linear(H,NC) -> log-softmax -> NLL.
  * Limits: D <= 64, H <= 128, NC <= 32.  fc weights in Torch7 nn.Linear layout, fp32. */
@@ -292,6 +312,13 @@ typedef struct tadnn_head_args {
   void* dp2;                 /* backward: [B, D] bf16 gradient w.r.t. p2 */
   float grad_scale;          /* backward: upstream dLoss (1 for a plain mean loss) */
   const float* grad_scale_dev; /* backward: optional device scalar multiplied into grad_scale */
+  /* backward, optional (all three NULL to skip): the head's input is the output of ReLU + 3x3 max-pooling
+   * with saved arg-max bytes (0..8); route the input gradient through both in the same pass.  dpre is
+   * [B*9, D] bf16 (row s*9+pos = gradient at window pixel pos of sample s), gbias_pre [D] fp32 (+=) is the
+   * bias gradient of the layer feeding the pool.  dp2 may then be NULL. */
+  const void* pool_idx;
+  void* dpre;
+  float* gbias_pre;
 } tadnn_head_args;
 /* Scratch needed by tadnn_head_forward (per-block loss partials + a completion counter).  The
  * caller allocates it ONCE, zero-filled; the kernel leaves the counter at zero again. */

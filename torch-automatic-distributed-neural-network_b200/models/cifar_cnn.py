@@ -25,6 +25,38 @@ from ..nn.protocol import T7Protocol
 
 K1PAD = 80  # 75 -> multiple of 8 (TMA pitch)
 
+_SHADOWS: dict = {}
+_DP1: dict = {}
+
+
+def _shadows(dev, wkey: int):
+    """Operand buffers of the fused path, per (device, model — identified by the address of its conv2
+    weight): packed bf16 filters, the Toeplitz matrix of the transposed conv2, and the packed fp32 conv2
+    weight-gradient scratch (kept zeroed by its consumer)."""
+    key = (str(dev), int(wkey))
+    sh = _SHADOWS.get(key)
+    if sh is None:
+        if len(_SHADOWS) > 8:
+            _SHADOWS.clear()
+        sh = {"w1p": torch.empty((64, 80), device=dev, dtype=torch.bfloat16),
+              "w2p": torch.empty((64, 1600), device=dev, dtype=torch.bfloat16),
+              "Tt": torch.empty((576, 4032), device=dev, dtype=torch.bfloat16),
+              "dwp": torch.zeros((64, 1600), device=dev, dtype=torch.float32)}
+        _SHADOWS[key] = sh
+    return sh
+
+
+def _dp1_buffer(dev, B):
+    """[B,9,9,64] gradient buffer whose rows y >= 7 are zero and stay zero (the dgrad GEMM writes y < 7 only)."""
+    key = (str(dev), int(B))
+    t = _DP1.get(key)
+    if t is None:
+        if len(_DP1) > 4:
+            _DP1.clear()
+        t = torch.zeros((B, 9, 9, 64), device=dev, dtype=torch.bfloat16)
+        _DP1[key] = t
+    return t
+
 
 def _cnn_forward(x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fused_conv1, conv2_mode):
     """Launch the forward kernels; returns (loss, logp, saved-for-backward dict)."""
@@ -33,26 +65,37 @@ def _cnn_forward(x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fu
     dev = x.device
     xb = x if x.dtype == torch.bfloat16 else x.to(torch.bfloat16)
     xb = xb.contiguous()
-    w2p = K.conv_weight_pack(w2, 64, 5, 5, 1600)
-    col1 = a1 = None
-    if fused_conv1:
-        # implicit-GEMM conv + bias + ReLU + max-pool in one tcgen05 kernel: no col1 / a1 in HBM
-        p1, idx1 = K.conv1_pool_forward(xb, K.conv1_weight_pack(w1), b1)
+    col1 = a1 = col2 = a2 = sh = None
+    fused2 = conv2_mode == "dense" and fused_conv1
+    if fused2:
+        # one launch refreshes every bf16 operand copy of the fp32 master weights (they may have been changed
+        # by the optimiser, a synchronisation or a load since the last step)
+        sh = _shadows(dev, w2.data_ptr())
+        K.cnn_pack_shadows(w1, w2, sh["w1p"], sh["w2p"], sh["Tt"])
+        w2p = sh["w2p"]
+        p1, idx1 = K.conv1_pool_forward(xb, sh["w1p"], b1)
+        # conv2 + bias + ReLU + pool2 as ONE implicit-GEMM kernel: 4-D TMA boxes of p1 are the A tiles
+        p2, idx2 = K.conv2_pool_forward(p1, w2p, b2)
     else:
-        w1p = K.conv_weight_pack(w1, 3, 5, 5, K1PAD)
-        col1 = K.im2col(xb, 5, 5, K1PAD, nchw=True)                       # [B*784, 80]
-        a1 = K.gemm_bf16(col1, w1p, bias=b1, act="relu", tile_n=64)       # [B*784, 64] == NHWC [B,28,28,64]
-        p1, idx1 = K.maxpool_fwd(a1.view(B, 28, 28, 64), 3)               # [B,9,9,64]
-    if conv2_mode == "legacy":
-        col2 = K.im2col(p1, 5, 5, 1600, nchw=False)                       # [B*25, 1600]
-        a2 = K.gemm_bf16(col2, w2p, bias=b2, act="relu", tile_n=64)       # [B*25, 64] == [B,5,5,64]
-        p2, idx2 = K.maxpool_fwd(a2.view(B, 5, 5, 64), 3)                 # [B,1,1,64]
-    else:
-        # rows ordered with the 3x3 pixels that pool2 reads first; "dense" still evaluates the
-        # convolution at all 25 pixels (as the reference does), "pooled" only at those 9
-        col2 = K.im2col_winfirst(p1, 5, 5, 3, only_window=(conv2_mode == "pooled"))
-        a2 = K.gemm_bf16(col2, w2p, bias=b2, act="relu", tile_n=64)
-        p2, idx2 = K.maxpool_fwd(a2[:B * 9].view(B, 3, 3, 64), 3)         # [B,1,1,64]
+        w2p = K.conv_weight_pack(w2, 64, 5, 5, 1600)
+        if fused_conv1:
+            # implicit-GEMM conv + bias + ReLU + max-pool in one tcgen05 kernel: no col1 / a1 in HBM
+            p1, idx1 = K.conv1_pool_forward(xb, K.conv1_weight_pack(w1), b1)
+        else:
+            w1p = K.conv_weight_pack(w1, 3, 5, 5, K1PAD)
+            col1 = K.im2col(xb, 5, 5, K1PAD, nchw=True)                       # [B*784, 80]
+            a1 = K.gemm_bf16(col1, w1p, bias=b1, act="relu", tile_n=64)       # [B*784, 64] == NHWC [B,28,28,64]
+            p1, idx1 = K.maxpool_fwd(a1.view(B, 28, 28, 64), 3)               # [B,9,9,64]
+        if conv2_mode == "legacy":
+            col2 = K.im2col(p1, 5, 5, 1600, nchw=False)                       # [B*25, 1600]
+            a2 = K.gemm_bf16(col2, w2p, bias=b2, act="relu", tile_n=64)       # [B*25, 64] == [B,5,5,64]
+            p2, idx2 = K.maxpool_fwd(a2.view(B, 5, 5, 64), 3)                 # [B,1,1,64]
+        else:
+            # rows ordered with the 3x3 pixels that pool2 reads first; "dense" still evaluates the
+            # convolution at all 25 pixels (as the reference does), "pooled" only at those 9
+            col2 = K.im2col_winfirst(p1, 5, 5, 3, only_window=(conv2_mode == "pooled"))
+            a2 = K.gemm_bf16(col2, w2p, bias=b2, act="relu", tile_n=64)
+            p2, idx2 = K.maxpool_fwd(a2[:B * 9].view(B, 3, 3, 64), 3)         # [B,1,1,64]
     hidden = torch.empty((B, 100), device=dev, dtype=torch.float32)
     logp = torch.empty((B, 10), device=dev, dtype=torch.float32)
     loss = torch.empty((), device=dev, dtype=torch.float32)
@@ -69,7 +112,7 @@ def _cnn_forward(x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fu
                                                    C.c_void_p(_native.stream_ptr())), "tadnn_head_forward")
     saved = dict(xb=xb, col1=col1, a1=a1, p1=p1, idx1=idx1, col2=col2, a2=a2, p2=p2, idx2=idx2, hidden=hidden,
                  logp=logp, tgt=tgt, w2p=w2p, fw1=fw1, fb1=fb1, fw2=fw2, fb2=fb2, p_drop=float(p_drop), seed=seed,
-                 B=B, fused_conv1=bool(fused_conv1), conv2_mode=conv2_mode)
+                 B=B, fused_conv1=bool(fused_conv1), conv2_mode=conv2_mode, fused2=fused2, sh=sh)
     return loss, logp, saved
 
 
@@ -79,7 +122,7 @@ def _cnn_backward(sv, gw1, gb1, gw2, gb2, gfw1, gfb1, gfw2, gfb2, gloss=None):
     from ..ops import cnn as K
     B, dev = sv["B"], sv["p2"].device
     p1, idx1, p2, idx2, col2, a2, w2p = sv["p1"], sv["idx1"], sv["p2"], sv["idx2"], sv["col2"], sv["a2"], sv["w2p"]
-    dp2 = torch.empty((B, 1, 1, 64), device=dev, dtype=torch.bfloat16)
+    fused2 = sv.get("fused2", False)
     h = K.HeadArgs()
     h.p2, h.w1, h.b1, h.w2, h.b2 = p2.data_ptr(), sv["fw1"].data_ptr(), sv["fb1"].data_ptr(), sv["fw2"].data_ptr(), sv["fb2"].data_ptr()
     h.target = sv["tgt"].data_ptr()
@@ -87,11 +130,27 @@ def _cnn_backward(sv, gw1, gb1, gw2, gb2, gfw1, gfb1, gfw2, gfb2, gloss=None):
     h.dropout_p, h.seed = sv["p_drop"], sv["seed"]
     h.hidden, h.logp = sv["hidden"].data_ptr(), sv["logp"].data_ptr()
     h.gw1, h.gb1, h.gw2, h.gb2 = gfw1.data_ptr(), gfb1.data_ptr(), gfw2.data_ptr(), gfb2.data_ptr()
-    h.dp2 = dp2.data_ptr()
     h.grad_scale = 1.0
     if gloss is not None:
         gl = gloss.to(device=dev, dtype=torch.float32).contiguous()
         h.grad_scale_dev = gl.data_ptr()  # upstream dLoss stays on the device: no host sync
+    if fused2:
+        # head backward also routes the gradient through pool2 + ReLU (-> da2w, rows (n, window pixel)) and
+        # takes conv2's bias gradient; conv2's weight gradient reads p1 through TMA boxes (no im2col);
+        # the transposed convolution is one GEMM against the Toeplitz matrix, written straight into the
+        # full-size dp1 (its never-written rows stay zero); conv1's backward also takes conv1's bias gradient.
+        sh = sv["sh"]
+        da2w = torch.empty((B * 9, 64), device=dev, dtype=torch.bfloat16)
+        h.pool_idx, h.dpre, h.gbias_pre = idx2.data_ptr(), da2w.data_ptr(), gb2.data_ptr()
+        _native.check(_native.lib().tadnn_head_backward(C.byref(h), C.c_void_p(_native.stream_ptr())), "tadnn_head_backward")
+        K.conv2_wgrad(p1, da2w, sh["dwp"])
+        K.conv2_wgrad_unpack(sh["dwp"], gw2)
+        dp1 = _dp1_buffer(dev, B)
+        K.gemm_bf16(da2w.view(B, 576), sh["Tt"], b_mn_major=True, out=dp1.view(B, 81 * 64)[:, :7 * 9 * 64])
+        K.conv1_pool_backward_bias(sv["xb"], dp1, p1, idx1, gw1, gb1)
+        return
+    dp2 = torch.empty((B, 1, 1, 64), device=dev, dtype=torch.bfloat16)
+    h.dp2 = dp2.data_ptr()
     _native.check(_native.lib().tadnn_head_backward(C.byref(h), C.c_void_p(_native.stream_ptr())), "tadnn_head_backward")
     K.colsum_relu_mask(dp2, p2, gb2)
     if sv["conv2_mode"] == "legacy":

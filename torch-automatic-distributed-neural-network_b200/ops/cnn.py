@@ -17,6 +17,7 @@ class HeadArgs(C.Structure):
         ("dropout_p", C.c_float), ("seed", C.c_uint), ("hidden", C.c_void_p), ("logp", C.c_void_p),
         ("loss", C.c_void_p), ("gw1", C.c_void_p), ("gb1", C.c_void_p), ("gw2", C.c_void_p), ("gb2", C.c_void_p),
         ("dp2", C.c_void_p), ("grad_scale", C.c_float), ("grad_scale_dev", C.c_void_p),
+        ("pool_idx", C.c_void_p), ("dpre", C.c_void_p), ("gbias_pre", C.c_void_p),
     ]
 
 
@@ -146,6 +147,45 @@ def conv1_pool_backward(x, dp1, p1, idx1, grad_weight):
     return grad_weight
 
 
+def conv2_pool_forward(p1: torch.Tensor, w2p: torch.Tensor, bias: torch.Tensor, store_a2: bool = False):
+    """p1 [B,9,9,64] bf16 -> (p2 [B,64] bf16, idx2 [B,64] uint8[, a2 [B,5,5,64]]): conv5x5 + bias + ReLU + maxpool3/3
+    as one implicit-GEMM kernel fed by 4-D TMA boxes of p1 (csrc/conv2_fused.cu)."""
+    B = p1.shape[0]
+    assert p1.dtype == torch.bfloat16 and p1.is_contiguous() and tuple(p1.shape[1:]) == (9, 9, 64)
+    p2 = torch.empty((B, 64), device=p1.device, dtype=torch.bfloat16)
+    idx2 = torch.empty((B, 64), device=p1.device, dtype=torch.uint8)
+    a2 = torch.empty((B, 5, 5, 64), device=p1.device, dtype=torch.bfloat16) if store_a2 else None
+    _native.check(_native.lib().tadnn_conv2_pool_forward(_p(p1), _p(w2p), _p(bias), _p(p2), _p(idx2), _p(a2), B, _s()),
+                  "tadnn_conv2_pool_forward")
+    return (p2, idx2, a2) if store_a2 else (p2, idx2)
+
+
+def conv2_wgrad(p1: torch.Tensor, da2w: torch.Tensor, dw_packed: torch.Tensor):
+    """dw_packed [64,1600] fp32 (k = tap*64 + c) += sum_{n, 3x3 window} da2w[n*9+pos, o] * p1[n, py+kh, px+kw, c]."""
+    B = p1.shape[0]
+    assert da2w.dtype == torch.bfloat16 and da2w.is_contiguous() and da2w.numel() == B * 9 * 64
+    assert dw_packed.dtype == torch.float32 and dw_packed.is_contiguous() and dw_packed.numel() == 64 * 1600
+    _native.check(_native.lib().tadnn_conv2_wgrad(_p(p1), _p(da2w), _p(dw_packed), B, _s()), "tadnn_conv2_wgrad")
+    return dw_packed
+
+
+def conv2_wgrad_unpack(dw_packed: torch.Tensor, grad: torch.Tensor):
+    """grad[64,1600] (Torch7 order) += dw_packed; dw_packed = 0."""
+    _native.check(_native.lib().tadnn_conv2_wgrad_unpack(_p(dw_packed), _p(grad), _s()), "tadnn_conv2_wgrad_unpack")
+    return grad
+
+
+def cnn_pack_shadows(w1, w2, w1p, w2p, Tt):
+    _native.check(_native.lib().tadnn_cnn_pack_shadows(_p(w1), _p(w2), _p(w1p), _p(w2p), _p(Tt), _s()), "tadnn_cnn_pack_shadows")
+
+
+def conv1_pool_backward_bias(x, dp1, p1, idx1, grad_weight, grad_bias):
+    _native.check(_native.lib().tadnn_conv1_pool_backward_bias(_p(x), _p(dp1), int(dp1.shape[1]), int(dp1.shape[2]), _p(p1), _p(idx1),
+                                                               _p(grad_weight), _p(grad_bias), x.shape[0], _s()),
+                  "tadnn_conv1_pool_backward_bias")
+    return grad_weight
+
+
 def colsum_relu_mask_corner(dy: torch.Tensor, y: torch.Tensor, out: torch.Tensor):
     """out[c] += sum dy * (y > 0) where dy is [B, FH, FW, C], the top-left corner of y [B, H, W, C]."""
     B, FH, FW, Cc = dy.shape
@@ -192,5 +232,5 @@ def auto_split_k(M: int, N: int, K: int, tile_n: int = 256) -> int:
     return max(1, min(kb, 148 // max(1, tiles)))
 
 
-__all__ = ["u8_to_bf16", "im2col_winfirst", "conv_toeplitz_pack", "expand_corner", "conv1_weight_pack", "conv1_pool_forward", "conv1_pool_backward", "im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "colsum_relu_mask_corner", "conv_weight_pack",
+__all__ = ["u8_to_bf16", "conv2_pool_forward", "conv2_wgrad", "conv2_wgrad_unpack", "cnn_pack_shadows", "conv1_pool_backward_bias", "im2col_winfirst", "conv_toeplitz_pack", "expand_corner", "conv1_weight_pack", "conv1_pool_forward", "conv1_pool_backward", "im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "colsum_relu_mask_corner", "conv_weight_pack",
            "conv_wgrad_unpack", "head_workspace", "sgd_step", "auto_split_k", "HeadArgs", "gemm_bf16"]

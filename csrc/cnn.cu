@@ -587,12 +587,23 @@ __global__ void __launch_bounds__(256) head_fwd_kernel(HeadArgs a) {
     is_last = (done == gridDim.x - 1);
   }
   __syncthreads();
-  if (is_last && t == 0) {
+  if (is_last) {
+    // fixed assignment of partials to threads + fixed reduction tree: deterministic, and 128 L2 round trips
+    // are taken in parallel instead of one after the other (that serial loop was most of this kernel's time)
     __threadfence();
-    float tot = 0.f;
-    for (unsigned b = 0; b < gridDim.x; ++b) tot += reinterpret_cast<volatile float*>(a.loss_partial)[b];
-    *a.loss = tot / static_cast<float>(a.B);
-    *a.counter = 0u;  // ready for the next launch
+    float v = 0.f;
+    for (unsigned b = t; b < gridDim.x; b += 256) v += reinterpret_cast<volatile float*>(a.loss_partial)[b];
+    v = warp_sum(v);
+    __shared__ float red[8];
+    if ((t & 31) == 0) red[t >> 5] = v;
+    __syncthreads();
+    if (t == 0) {
+      float tot = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) tot += red[w];
+      *a.loss = tot / static_cast<float>(a.B);
+      *a.counter = 0u;  // ready for the next launch
+    }
   }
 }
 
@@ -745,19 +756,21 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(HeadArgs a) {
       for (int s = 0; s < kHeadS; ++s) accb += sdl[s * kHeadC + (t - 128)];
     }
   }
-  // ---- flush
+  // ---- flush: the fc1 tile goes through shared memory so that a warp's 32 atomics hit 32 consecutive
+  // floats (4 sectors) instead of 32 different sectors
+  __syncthreads();
+  float* stage = w1s;   // [HP][64]; the weights are no longer needed
   if (jq < nJ) {
 #pragma unroll
     for (int x = 0; x < 4; ++x) {
-      const int j = 4 * jq + x;
-      if (j < a.H) {
-#pragma unroll
-        for (int y = 0; y < 8; ++y) {
-          const int d = 8 * iq + y;
-          if (d < a.D) atomicAdd(a.gw1 + j * a.D + d, acc1[x][y]);
-        }
-      }
+      *reinterpret_cast<float4*>(stage + (4 * jq + x) * kHeadD + 8 * iq) = make_float4(acc1[x][0], acc1[x][1], acc1[x][2], acc1[x][3]);
+      *reinterpret_cast<float4*>(stage + (4 * jq + x) * kHeadD + 8 * iq + 4) = make_float4(acc1[x][4], acc1[x][5], acc1[x][6], acc1[x][7]);
     }
+  }
+  __syncthreads();
+  for (int e = t; e < a.H * kHeadD; e += 256) {
+    const int j = e >> 6, d = e & 63;
+    if (d < a.D) atomicAdd(a.gw1 + j * a.D + d, stage[e]);
   }
 #pragma unroll
   for (int k = 0; k < kW2PerThread; ++k) {

@@ -199,30 +199,149 @@ __global__ void __launch_bounds__(512) allreduce_twoshot_kernel(CommDev c, size_
 // ---- K3: NVLS (multimem) ---------------------------------------------------
 // The switch reduces: one multimem.ld_reduce of the multicast address returns the sum over
 // all ranks, one multimem.st broadcasts the result.  Rank r handles chunk r.
+__device__ __forceinline__ uint4 mm_ld_reduce_f32(const uint8_t* p) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint4 mm_ld_reduce_bf16(const uint8_t* p) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mm_st(uint8_t* p, const uint4& v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+template <int DT>
+__device__ __forceinline__ uint4 scale_vec(const uint4& v, float s) {
+  if (DT == 0)
+    return make_uint4(__float_as_uint(__uint_as_float(v.x) * s), __float_as_uint(__uint_as_float(v.y) * s),
+                      __float_as_uint(__uint_as_float(v.z) * s), __float_as_uint(__uint_as_float(v.w) * s));
+  float2 a = unpack_bf16x2(v.x), b = unpack_bf16x2(v.y), c = unpack_bf16x2(v.z), d = unpack_bf16x2(v.w);
+  return make_uint4(pack_bf16x2(a.x * s, a.y * s), pack_bf16x2(b.x * s, b.y * s), pack_bf16x2(c.x * s, c.y * s), pack_bf16x2(d.x * s, d.y * s));
+}
+// Four 16-byte switch reductions in flight per thread before the first result is used (the loop was
+// latency-bound with one: each multimem.ld_reduce is a round trip to the switch).
 template <int DT>
 __global__ void __launch_bounds__(512) allreduce_nvls_kernel(CommDev c, size_t off, size_t nvec, float scale, int channel) {
+  constexpr int U = 4;
+  const int rank = my_rank(c);
+  const size_t chunk = (nvec + c.world - 1) / c.world;
+  const size_t lo = min(nvec, chunk * rank), hi = min(nvec, lo + chunk);
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const size_t tid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  block_barrier(c, channel);
+  for (size_t base = lo; base < hi; base += stride * U) {
+    uint4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = base + tid + u * stride;
+      if (i < hi) v[u] = DT == 0 ? mm_ld_reduce_f32(c.mc_heap + off + i * 16) : mm_ld_reduce_bf16(c.mc_heap + off + i * 16);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = base + tid + u * stride;
+      if (i < hi) mm_st(c.mc_heap + off + i * 16, scale_vec<DT>(v[u], scale));
+    }
+  }
+  block_barrier(c, channel);
+}
+
+// ---- all-reduce-average of the gradients FUSED with the SGD step (fp32) -------------------------------
+// The rank that holds a reduced gradient vector in registers applies  p -= lr * (g + wd * p)  right there
+// and clears the gradient, so the synchronised training step needs no second pass over the flat buffer
+// and no parameter half in the message (the reference sends both, datamodule.lua:214-223, and then runs
+// the optimiser separately).  Valid when the replicas hold identical parameters, which the caller
+// guarantees (sync every step from a broadcast start); every rank then computes the same update in the
+// same rank order, so the parameters stay bit-identical without ever being communicated.
+//   one-shot: every rank reads all P gradient copies and updates its own parameters; second barrier
+//             before the gradients are cleared (peers may still be reading them).
+//   nvls    : rank r owns chunk r: switch-reduced load, update of its own parameter chunk, and the new
+//             parameters and the cleared gradients are multicast-stored to every rank.
+__global__ void __launch_bounds__(512) allreduce_sgd_oneshot_kernel(CommDev c, size_t g_off, size_t p_off, size_t nvec, float scale,
+                                                                    float lr, float wd, int channel) {
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const size_t tid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const int rank = my_rank(c);
+  block_barrier(c, channel);
+  for (size_t i = tid; i < nvec; i += stride) {
+    uint4 v[kMaxRanks];
+#pragma unroll
+    for (int r = 0; r < kMaxRanks; ++r)
+      if (r < c.world) v[r] = ld_peer16(c.heap[r] + g_off + i * 16);
+    float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int r = 0; r < kMaxRanks; ++r)
+      if (r < c.world) Vec<0>::add(a, v[r]);
+    float4* pp = reinterpret_cast<float4*>(c.heap[rank] + p_off + i * 16);
+    float4 w = *pp;
+    w.x -= lr * (a[0] * scale + wd * w.x); w.y -= lr * (a[1] * scale + wd * w.y);
+    w.z -= lr * (a[2] * scale + wd * w.z); w.w -= lr * (a[3] * scale + wd * w.w);
+    *pp = w;
+  }
+  block_barrier(c, channel);
+  for (size_t i = tid; i < nvec; i += stride) *reinterpret_cast<uint4*>(c.heap[rank] + g_off + i * 16) = make_uint4(0, 0, 0, 0);
+}
+
+__global__ void __launch_bounds__(512) allreduce_sgd_nvls_kernel(CommDev c, size_t g_off, size_t p_off, size_t nvec, float scale, float lr,
+                                                                 float wd, int channel) {
+  constexpr int U = 4;
+  const int rank = my_rank(c);
+  const size_t chunk = (nvec + c.world - 1) / c.world;
+  const size_t lo = min(nvec, chunk * rank), hi = min(nvec, lo + chunk);
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  const size_t tid = static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x;
+  block_barrier(c, channel);
+  for (size_t base = lo; base < hi; base += stride * U) {
+    uint4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = base + tid + u * stride;
+      if (i < hi) v[u] = mm_ld_reduce_f32(c.mc_heap + g_off + i * 16);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const size_t i = base + tid + u * stride;
+      if (i < hi) {
+        float4 w = *reinterpret_cast<const float4*>(c.heap[rank] + p_off + i * 16);
+        w.x -= lr * (__uint_as_float(v[u].x) * scale + wd * w.x); w.y -= lr * (__uint_as_float(v[u].y) * scale + wd * w.y);
+        w.z -= lr * (__uint_as_float(v[u].z) * scale + wd * w.z); w.w -= lr * (__uint_as_float(v[u].w) * scale + wd * w.w);
+        mm_st(c.mc_heap + p_off + i * 16, make_uint4(__float_as_uint(w.x), __float_as_uint(w.y), __float_as_uint(w.z), __float_as_uint(w.w)));
+        mm_st(c.mc_heap + g_off + i * 16, make_uint4(0, 0, 0, 0));
+      }
+    }
+  }
+  block_barrier(c, channel);
+}
+
+// two-shot form of the same for contexts without a multicast mapping
+__global__ void __launch_bounds__(512) allreduce_sgd_twoshot_kernel(CommDev c, size_t g_off, size_t p_off, size_t nvec, float scale, float lr,
+                                                                    float wd, int channel) {
   const int rank = my_rank(c);
   const size_t chunk = (nvec + c.world - 1) / c.world;
   const size_t lo = min(nvec, chunk * rank), hi = min(nvec, lo + chunk);
   const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
   block_barrier(c, channel);
   for (size_t i = lo + static_cast<size_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < hi; i += stride) {
-    uint8_t* p = c.mc_heap + off + i * 16;
-    if (DT == 0) {
-      float a, b, d, e;
-      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(a), "=f"(b), "=f"(d), "=f"(e) : "l"(p) : "memory");
-      a *= scale; b *= scale; d *= scale; e *= scale;
-      asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "f"(a), "f"(b), "f"(d), "f"(e) : "memory");
-    } else {
-      uint32_t x, y, z, w;
-      asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];" : "=r"(x), "=r"(y), "=r"(z), "=r"(w) : "l"(p) : "memory");
-      float2 f;
-      f = unpack_bf16x2(x); x = pack_bf16x2(f.x * scale, f.y * scale);
-      f = unpack_bf16x2(y); y = pack_bf16x2(f.x * scale, f.y * scale);
-      f = unpack_bf16x2(z); z = pack_bf16x2(f.x * scale, f.y * scale);
-      f = unpack_bf16x2(w); w = pack_bf16x2(f.x * scale, f.y * scale);
-      asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(x), "r"(y), "r"(z), "r"(w) : "memory");
-    }
+    uint4 v[kMaxRanks];
+#pragma unroll
+    for (int r = 0; r < kMaxRanks; ++r)
+      if (r < c.world) v[r] = ld_peer16(c.heap[r] + g_off + i * 16);
+    float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int r = 0; r < kMaxRanks; ++r)
+      if (r < c.world) Vec<0>::add(a, v[r]);
+    float4 w = *reinterpret_cast<const float4*>(c.heap[rank] + p_off + i * 16);
+    w.x -= lr * (a[0] * scale + wd * w.x); w.y -= lr * (a[1] * scale + wd * w.y);
+    w.z -= lr * (a[2] * scale + wd * w.z); w.w -= lr * (a[3] * scale + wd * w.w);
+    const uint4 o = make_uint4(__float_as_uint(w.x), __float_as_uint(w.y), __float_as_uint(w.z), __float_as_uint(w.w));
+    const uint4 z = make_uint4(0, 0, 0, 0);
+#pragma unroll
+    for (int r = 0; r < kMaxRanks; ++r)
+      if (r < c.world) {
+        st_peer16(c.heap[r] + p_off + i * 16, o);
+        st_peer16(c.heap[r] + g_off + i * 16, z);
+      }
   }
   block_barrier(c, channel);
 }
@@ -701,6 +820,48 @@ extern "C" int tadnn_allreduce(tadnn_comm* c, unsigned long long off_bytes, unsi
   const unsigned long long es = dtype == 0 ? 4 : 2;
   TADNN_REQUIRE(off_bytes + count * es <= c->heap_bytes, "allreduce: [%llu, +%llu) exceeds the %llu-byte heap", off_bytes, count * es, c->heap_bytes);
   return do_allreduce(c->dev, c->dev.mc_heap != nullptr, off_bytes, count, dtype, scale, algo, max_blocks, channel, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" int tadnn_allreduce_sgd(tadnn_comm* c, unsigned long long grad_off, unsigned long long param_off, unsigned long long count,
+                                   float scale, float lr, float weight_decay, int algo, int max_blocks, int channel, tadnn_stream_t stream_) {
+  if (int rc = validate(c, channel, "allreduce_sgd")) return rc;
+  TADNN_REQUIRE(grad_off % 16 == 0 && param_off % 16 == 0 && count % 4 == 0, "allreduce_sgd: offsets must be 16-byte aligned and count a multiple of 4 floats");
+  TADNN_REQUIRE(grad_off + count * 4 <= c->heap_bytes && param_off + count * 4 <= c->heap_bytes, "allreduce_sgd: range exceeds the heap");
+  TADNN_REQUIRE(grad_off + count * 4 <= param_off || param_off + count * 4 <= grad_off, "allreduce_sgd: gradient and parameter ranges overlap");
+  if (count == 0) return 0;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const size_t nvec = count / 4;
+  const bool has_mc = c->dev.mc_heap != nullptr;
+  if (algo == 0) algo = (count * 4 <= (512u << 10)) ? 1 : (has_mc ? 3 : 2);
+  TADNN_REQUIRE(algo >= 1 && algo <= 3 && (algo != 3 || has_mc), "allreduce_sgd: algo %d unavailable on this context", algo);
+  if (algo == 1) {
+    const int blocks = pick_blocks(nvec, max_blocks, 64);
+    allreduce_sgd_oneshot_kernel<<<blocks, 512, 0, stream>>>(c->dev, grad_off, param_off, nvec, scale, lr, weight_decay, channel);
+    TADNN_LAUNCH_CHECK("allreduce_sgd_oneshot");
+  } else if (algo == 3) {
+    const int blocks = pick_blocks(nvec / c->world / 4 + 1, max_blocks, 64);
+    allreduce_sgd_nvls_kernel<<<blocks, 512, 0, stream>>>(c->dev, grad_off, param_off, nvec, scale, lr, weight_decay, channel);
+    TADNN_LAUNCH_CHECK("allreduce_sgd_nvls");
+  } else {
+    const int blocks = pick_blocks(nvec / c->world + 1, max_blocks, 128);
+    allreduce_sgd_twoshot_kernel<<<blocks, 512, 0, stream>>>(c->dev, grad_off, param_off, nvec, scale, lr, weight_decay, channel);
+    TADNN_LAUNCH_CHECK("allreduce_sgd_twoshot");
+  }
+  return 0;
+}
+
+extern "C" int tadnn_allreduce_sgd_emulated(tadnn_comm* const* comms, int world, unsigned long long grad_off, unsigned long long param_off,
+                                            unsigned long long count, float scale, float lr, float weight_decay, int algo, tadnn_stream_t stream_) {
+  TADNN_REQUIRE(comms && world >= 1 && world <= kMaxRanks, "allreduce_sgd_emulated: bad arguments");
+  TADNN_REQUIRE(algo == 1 || algo == 2, "allreduce_sgd_emulated: algo must be 1 (one-shot) or 2 (two-shot)");
+  TADNN_REQUIRE(grad_off % 16 == 0 && param_off % 16 == 0 && count % 4 == 0, "allreduce_sgd_emulated: alignment");
+  CommDev dev = comms[0]->dev;
+  dev.rank = -1;
+  dev.world = world;
+  const size_t nvec = count / 4;
+  const size_t g = grad_off, p = param_off;
+  if (algo == 1) return launch_maybe_coop(dev, allreduce_sgd_oneshot_kernel, pick_blocks(nvec, 8, 8), 512, static_cast<cudaStream_t>(stream_), "allreduce_sgd_oneshot", dev, g, p, nvec, scale, lr, weight_decay, 0);
+  return launch_maybe_coop(dev, allreduce_sgd_twoshot_kernel, pick_blocks(nvec / world + 1, 8, 8), 512, static_cast<cudaStream_t>(stream_), "allreduce_sgd_twoshot", dev, g, p, nvec, scale, lr, weight_decay, 0);
 }
 
 extern "C" int tadnn_allreduce_emulated(tadnn_comm* const* comms, int world, unsigned long long off_bytes, unsigned long long count, int dtype, float scale, int algo, tadnn_stream_t stream) {

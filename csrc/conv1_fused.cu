@@ -67,6 +67,9 @@ __device__ __forceinline__ void stage_images_async(const __nv_bfloat16* __restri
 // k 64..79 in its chunks 0..1.  Each (kh, c) run of 5 contiguous input pixels is fetched as three
 // aligned 32-bit words and funnel-shifted by the pixel's column parity; the 2-byte shuffles into
 // patch order are compile-time byte permutes.
+// ONES: the first padding slot (k = 75) of a valid row holds 1.0, so that a weight row whose slot 75 is
+// the bias makes the MMA add it (forward only).
+template <bool ONES>
 __device__ __forceinline__ void build_patch_row(const uint32_t* __restrict__ img_words, int total_win, int tile, int b0,
                                                 int r, uint8_t* blk0, uint8_t* blk1) {
   const int win = tile * kWinPerTile + r / 9;
@@ -103,7 +106,7 @@ __device__ __forceinline__ void build_patch_row(const uint32_t* __restrict__ img
           const uint32_t wsrc = e < 2 ? A[g] : (e < 4 ? Bv[g] : Cv[g]);
           half[h] = (e == 1 || e == 3) ? (wsrc >> 16) : (wsrc & 0xffffu);
         } else {
-          half[h] = 0u;
+          half[h] = (ONES && k == kK) ? 0x3f80u : 0u;
         }
       }
       out[m] = half[0] | (half[1] << 16);
@@ -123,7 +126,9 @@ __device__ __forceinline__ void build_patch_row(const uint32_t* __restrict__ img
 // ======================================= forward =======================================
 // smem: W block0 | W block1 (64 rows each, 8 KB) | A[2] x (block0 16 KB + block1 16 KB) | E 16 KB
 constexpr int kImgStageBytes = 2 * 2 * kC * kH * kW * 2;  // per producer group: double-buffered pair of staged images
-constexpr int kFwdSmem = 2 * 8192 + 2 * 2 * kBlockBytes + 2 * kRows * 128 + 2 * kImgStageBytes + 1024;
+constexpr int kEPitch = 144;                  // staging row pitch: 128 B + 16 B pad = conflict-free row writes, constant read offsets
+constexpr int kEBytes = kRows * kEPitch;      // per epilogue group
+constexpr int kFwdSmem = 2 * 8192 + 2 * 2 * kBlockBytes + 2 * kEBytes + 2 * kImgStageBytes + 1024;
 
 __global__ void __launch_bounds__(kFwdThreads, 1) conv1_fwd_kernel(const Conv1Args a) {
   extern __shared__ uint8_t smem_raw[];
@@ -131,11 +136,10 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1_fwd_kernel(const Conv1Ar
   uint8_t* w0 = smem;
   uint8_t* w1 = smem + 8192;
   uint8_t* abuf = smem + 16384;                       // stage s: abuf + s*32768 (+0: block0, +16384: block1)
-  uint8_t* ebuf = abuf + 2 * 2 * kBlockBytes;         // [128 rows][64 ch] bf16, plain row-major
-  uint8_t* imgbuf = ebuf + 2 * kRows * 128;            // staged input images
+  uint8_t* ebuf = abuf + 2 * 2 * kBlockBytes;         // 2 x [128 rows][64 ch] bf16, row pitch kEPitch
+  uint8_t* imgbuf = ebuf + 2 * kEBytes;                // staged input images (2 * kEBytes = 36 KB keeps them 1 KB aligned)
   __shared__ __align__(8) uint64_t a_full[2], a_empty[2], t_full[2], t_empty[2], img_full[2][2];
   __shared__ uint32_t tmem_base_smem;
-  __shared__ float s_bias[kO];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long total_win = static_cast<long long>(a.B) * kWinPerImg;
@@ -160,7 +164,10 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1_fwd_kernel(const Conv1Ar
     if (j < 8) *reinterpret_cast<uint4*>(w0 + sw128(row, j)) = v;
     else *reinterpret_cast<uint4*>(w1 + sw128(row, j - 8)) = v;
   }
-  if (threadIdx.x < kO) s_bias[threadIdx.x] = a.bias[threadIdx.x];
+  __syncthreads();
+  // the bias rides in the GEMM: weight slot k = 75 (the first padding column; the producers put 1.0 there)
+  if (threadIdx.x < kO)
+    *reinterpret_cast<__nv_bfloat16*>(w1 + sw128(threadIdx.x, 1) + 2 * (kK - 72)) = __float2bfloat16_rn(a.bias[threadIdx.x]);
   fence_proxy_async_smem();
   tc_fence_before_sync();
   __syncthreads();
@@ -208,8 +215,8 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1_fwd_kernel(const Conv1Ar
                            &img_full[grp][buf ^ 1]);
       mbar_wait(&img_full[grp][buf], (n >> 1) & 1);
       mbar_wait(&a_empty[grp], (n & 1) ^ 1);
-      build_patch_row(reinterpret_cast<const uint32_t*>(img + buf * 2 * kImgBytes), static_cast<int>(total_win), static_cast<int>(t), b0, r, b0p,
-                      b0p + kBlockBytes);
+      build_patch_row<true>(reinterpret_cast<const uint32_t*>(img + buf * 2 * kImgBytes), static_cast<int>(total_win), static_cast<int>(t), b0, r, b0p,
+                            b0p + kBlockBytes);
       fence_proxy_async_smem();
       mbar_arrive(&a_full[grp]);
       asm volatile("bar.sync %0, 128;" ::"r"(2 + grp) : "memory");  // everyone is done with img[buf] before it is refilled
@@ -222,7 +229,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1_fwd_kernel(const Conv1Ar
     const int q = warp & 3;                 // TMEM lane quarter of this warp
     const int row = q * 32 + lane;          // accumulator row = tile pixel
     const int et = (threadIdx.x - 288) & 127;
-    uint8_t* eb = ebuf + grp * kRows * 128;
+    uint8_t* eb = ebuf + grp * kEBytes;
     int n = 0;
     for (long long t = blockIdx.x + static_cast<long long>(grp) * gridDim.x; t < num_tiles; t += 2ll * gridDim.x, ++n) {
       mbar_wait(&t_full[grp], n & 1);
@@ -234,30 +241,31 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1_fwd_kernel(const Conv1Ar
       tmem_ld_wait();
       tc_fence_before_sync();
       mbar_arrive(&t_empty[grp]);
-      uint4* erow = reinterpret_cast<uint4*>(eb + row * 128);
+      // the accumulator already contains the bias; ReLU commutes with rounding and with max, so it is applied to the
+      // pooled value: per pixel only the bf16 pack remains
+      uint4* erow = reinterpret_cast<uint4*>(eb + row * kEPitch);
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float v[8];
+      for (int j = 0; j < 4; ++j)
+        erow[j] = make_uint4(pack_bf16x2(__uint_as_float(r0[8 * j]), __uint_as_float(r0[8 * j + 1])),
+                             pack_bf16x2(__uint_as_float(r0[8 * j + 2]), __uint_as_float(r0[8 * j + 3])),
+                             pack_bf16x2(__uint_as_float(r0[8 * j + 4]), __uint_as_float(r0[8 * j + 5])),
+                             pack_bf16x2(__uint_as_float(r0[8 * j + 6]), __uint_as_float(r0[8 * j + 7])));
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const int c = j * 8 + e;
-          v[e] = fmaxf(__uint_as_float(c < 32 ? r0[c] : r1[c - 32]) + s_bias[c], 0.f);
-        }
-        // rotate the chunk position by the row so that the 32 rows of a warp spread over all banks
-        erow[(j + row) & 7] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
-      }
+      for (int j = 0; j < 4; ++j)
+        erow[4 + j] = make_uint4(pack_bf16x2(__uint_as_float(r1[8 * j]), __uint_as_float(r1[8 * j + 1])),
+                                 pack_bf16x2(__uint_as_float(r1[8 * j + 2]), __uint_as_float(r1[8 * j + 3])),
+                                 pack_bf16x2(__uint_as_float(r1[8 * j + 4]), __uint_as_float(r1[8 * j + 5])),
+                                 pack_bf16x2(__uint_as_float(r1[8 * j + 6]), __uint_as_float(r1[8 * j + 7])));
       asm volatile("bar.sync %0, 128;" ::"r"(4 + grp) : "memory");
       // 14 windows x 16 channel quads, packed bf16x2 max + first-arg-max
       for (int o = et; o < kWinPerTile * 16; o += 128) {
         const int wl = o >> 4, q4 = o & 15;
         const long long win = t * kWinPerTile + wl;
         if (win < total_win) {
+          const uint8_t* base = eb + wl * 9 * kEPitch + q4 * 8;
           uint2 val[9];
 #pragma unroll
-          for (int pos = 0; pos < 9; ++pos) {
-            const int rr = wl * 9 + pos;
-            val[pos] = *reinterpret_cast<const uint2*>(eb + rr * 128 + ((((q4 >> 1) + rr) & 7) << 4) + ((q4 & 1) << 3));
-          }
+          for (int pos = 0; pos < 9; ++pos) val[pos] = *reinterpret_cast<const uint2*>(base + pos * kEPitch);
           uint32_t mx[2], ix[2];
 #pragma unroll
           for (int h = 0; h < 2; ++h) {
@@ -271,6 +279,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1_fwd_kernel(const Conv1Ar
               const uint32_t eq = __heq2_mask(*reinterpret_cast<const __nv_bfloat162*>(h ? &val[pos].y : &val[pos].x), m);
               idx = (idx & ~eq) | ((static_cast<uint32_t>(pos) * 0x00010001u) & eq);
             }
+            m = __hmax2(m, __float2bfloat162_rn(0.f));   // ReLU
             mx[h] = *reinterpret_cast<const uint32_t*>(&m);
             ix[h] = idx;  // two 16-bit positions
           }
@@ -295,7 +304,13 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1_fwd_kernel(const Conv1Ar
 //   A = col tile, MN-major: rows = pixels, two 64-wide chunks of k (block0, block1)
 //   B = g tile,   MN-major: rows = pixels, 64 channels
 // smem: A[2] x (block0 + block1) | G[2] x 16 KB
-constexpr int kBwdSmem = 2 * 2 * kBlockBytes + 2 * kBlockBytes + 2 * kImgStageBytes + 1024;
+// Gradient-side inputs of a tile (14 consecutive windows of dp1, p1 and idx1: three contiguous runs) are
+// fetched kGDist tiles ahead with bulk async copies into a ring of kGStages slots: with the one-tile register
+// prefetch this replaced, a tile (1.2 us) was shorter than the HBM latency of its own inputs and the group sat
+// on the scoreboard for half of the kernel (ncu: 48 % of its samples).
+constexpr int kGStages = 8, kGDist = 6;
+constexpr int kGSlot = 4608;   // 14*128 (dp1) + 14*128 (p1) + 14*64 (idx1) = 4480, rounded up
+constexpr int kBwdSmem = 2 * 2 * kBlockBytes + 2 * kBlockBytes + 2 * kImgStageBytes + kGStages * kGSlot + 1024;
 
 template <bool COMPACT>
 __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args a) {
@@ -304,7 +319,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args 
   uint8_t* abuf = smem;
   uint8_t* gbuf = smem + 2 * 2 * kBlockBytes;
   uint8_t* imgbuf = gbuf + 2 * kBlockBytes;
-  __shared__ __align__(8) uint64_t ab_full[2], ab_empty[2], done_bar, img_full[2][2];
+  uint8_t* gstage = imgbuf + 2 * kImgStageBytes;
+  __shared__ __align__(8) uint64_t ab_full[2], ab_empty[2], done_bar, img_full[2][2], g_full[kGStages];
   __shared__ uint32_t tmem_base_smem;
   __shared__ float s_gb[16][kO];   // bias-gradient partials of the 16 window slots
 
@@ -320,6 +336,7 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args 
       mbar_init(&img_full[s][1], 1);
     }
     mbar_init(&done_bar, 1);
+    for (int g = 0; g < kGStages; ++g) mbar_init(&g_full[g], 1);
     fence_mbar_init();
   }
   if (warp == 0) tmem_alloc<64>(&tmem_base_smem);
@@ -374,8 +391,8 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args 
                            &img_full[grp][buf ^ 1]);
       mbar_wait(&img_full[grp][buf], (n >> 1) & 1);
       mbar_wait(&ab_empty[grp], (n & 1) ^ 1);
-      build_patch_row(reinterpret_cast<const uint32_t*>(img + buf * 2 * kImgBytes), static_cast<int>(total_win), static_cast<int>(t), b0, r, b0p,
-                      b0p + kBlockBytes);
+      build_patch_row<false>(reinterpret_cast<const uint32_t*>(img + buf * 2 * kImgBytes), static_cast<int>(total_win), static_cast<int>(t), b0, r, b0p,
+                             b0p + kBlockBytes);
       fence_proxy_async_smem();
       mbar_arrive(&ab_full[grp]);
       asm volatile("bar.sync %0, 128;" ::"r"(2 + grp) : "memory");  // everyone is done with img[buf] before it is refilled
@@ -386,36 +403,56 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args 
     // rows of the window; the next tile's vectors are fetched before the current ones are used.
     const int gt = threadIdx.x - 288;
     const int wl = gt >> 3, j = gt & 7;          // wl 0..15 (14 real windows), j = 16-byte chunk
-    auto fetch = [&](long long t, uint4& dv, uint4& pv, uint2& iv, bool& ok) {
-      const long long win = t * kWinPerTile + wl;
-      ok = (wl < kWinPerTile) && (t < num_tiles) && (win < total_win);
-      if (ok) {
-        if (!COMPACT) {
-          dv = __ldg(reinterpret_cast<const uint4*>(a.dp1 + win * kO + j * 8));
-        } else {
-          // compact corner [B, dph, dpw, 64]: zero outside
-          const int w32 = static_cast<int>(win);  // B*81 < 2^31 is checked on the host; 32-bit division is cheap
-          const int b = w32 / kWinPerImg, wi = w32 - b * kWinPerImg;
-          const int py = wi / kPW, px = wi - py * kPW;
-          dv = make_uint4(0, 0, 0, 0);
-          if (py < a.dph && px < a.dpw)
-            dv = __ldg(reinterpret_cast<const uint4*>(a.dp1 + ((static_cast<long long>(b) * a.dph + py) * a.dpw + px) * kO + j * 8));
-        }
-        pv = __ldg(reinterpret_cast<const uint4*>(a.p1 + win * kO + j * 8));
-        iv = __ldg(reinterpret_cast<const uint2*>(a.idx1 + win * kO + j * 8));
-      }
+    // one thread streams the tiles' inputs into the ring; `issue(i)` fetches the i-th tile of this CTA
+    auto issue = [&](int i) {
+      const long long t = blockIdx.x + static_cast<long long>(i) * gridDim.x;
+      if (t >= num_tiles) return;
+      const long long w0 = t * kWinPerTile;
+      const int nw = static_cast<int>(min(static_cast<long long>(kWinPerTile), total_win - w0));
+      uint8_t* slot = gstage + (i % kGStages) * kGSlot;
+      uint64_t* bar = &g_full[i % kGStages];
+      mbar_arrive_expect_tx(bar, static_cast<uint32_t>(nw * (COMPACT ? 192 : 320)));
+      if (!COMPACT)
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(slot)),
+                     "l"(a.dp1 + w0 * kO), "r"(nw * 128), "r"(smem_u32(bar)) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(slot + 1792)),
+                   "l"(a.p1 + w0 * kO), "r"(nw * 128), "r"(smem_u32(bar)) : "memory");
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(slot + 3584)),
+                   "l"(a.idx1 + w0 * kO), "r"(nw * 64), "r"(smem_u32(bar)) : "memory");
     };
-    uint4 dv = make_uint4(0, 0, 0, 0), pv = dv, ndv = dv, npv = dv;
-    uint2 iv = make_uint2(0, 0), niv = iv;
-    bool ok = false, nok = false;
+    if (gt == 0)
+      for (int i = 0; i < kGDist; ++i) issue(i);
+    uint4 dv = make_uint4(0, 0, 0, 0), pv = dv;
+    uint2 iv = make_uint2(0, 0);
+    bool ok = false;
     float gbias[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    fetch(blockIdx.x, dv, pv, iv, ok);
     int i = 0;
     for (long long t = blockIdx.x; t < num_tiles; t += gridDim.x, ++i) {
       const int s = i & 1;
       const uint32_t ph = (i >> 1) & 1;
-      fetch(t + gridDim.x, ndv, npv, niv, nok);
-      mbar_wait(&ab_empty[s], ph ^ 1);
+      mbar_wait(&ab_empty[s], ph ^ 1);   // the MMA of tile i-2 has retired => every thread is done with ring slot (i-2) % kGStages
+      if (gt == 0) issue(i + kGDist);      // (i + kGDist) % kGStages == (i - 2) % kGStages
+      mbar_wait(&g_full[i % kGStages], (i / kGStages) & 1);
+      {
+        const uint8_t* slot = gstage + (i % kGStages) * kGSlot;
+        const long long win = t * kWinPerTile + wl;
+        ok = (wl < kWinPerTile) && (win < total_win);
+        if (ok) {
+          if (!COMPACT) {
+            dv = *reinterpret_cast<const uint4*>(slot + wl * 128 + j * 16);
+          } else {
+            // compact corner [B, dph, dpw, 64]: zero outside
+            const int w32 = static_cast<int>(win);  // B*81 < 2^31 is checked on the host; 32-bit division is cheap
+            const int b = w32 / kWinPerImg, wi = w32 - b * kWinPerImg;
+            const int py = wi / kPW, px = wi - py * kPW;
+            dv = make_uint4(0, 0, 0, 0);
+            if (py < a.dph && px < a.dpw)
+              dv = __ldg(reinterpret_cast<const uint4*>(a.dp1 + ((static_cast<long long>(b) * a.dph + py) * a.dpw + px) * kO + j * 8));
+          }
+          pv = *reinterpret_cast<const uint4*>(slot + 1792 + wl * 128 + j * 16);
+          iv = *reinterpret_cast<const uint2*>(slot + 3584 + wl * 64 + j * 8);
+        }
+      }
       uint8_t* g = gbuf + s * kBlockBytes;
       if (wl < kWinPerTile) {
         // integer domain: keep dp1 where the byte arg-max equals this pixel position and p1 != 0
@@ -445,7 +482,6 @@ __global__ void __launch_bounds__(kThreads, 1) conv1_bwd_kernel(const Conv1Args 
       }
       fence_proxy_async_smem();
       mbar_arrive(&ab_full[s]);
-      dv = ndv; pv = npv; iv = niv; ok = nok;
     }
     if (a.gb != nullptr) {
 #pragma unroll

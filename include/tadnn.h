@@ -162,6 +162,20 @@ int tadnn_barrier(tadnn_comm* c, int channel, tadnn_stream_t stream);
 int tadnn_allreduce(tadnn_comm* c, unsigned long long off_bytes, unsigned long long count, int dtype,
                     float scale, int algo, int max_blocks, int channel, tadnn_stream_t stream);
 
+/* Gradient all-reduce-average FUSED with the SGD step (fp32): for count floats,
+ *   g = scale * sum_ranks heap_r[grad_off ..];  heap[param_off ..] -= lr * (g + weight_decay * p);  heap[grad_off ..] = 0
+ * on every rank, in one kernel (one-shot / two-shot / NVLS as for tadnn_allreduce).  Replaces synchronizeModel
+ * (datamodule.lua:211-224) plus the optimiser pass when the replicas hold identical parameters (synchronised
+ * every step from a broadcast start): each rank then computes the same update in the same rank order, so the
+ * parameters stay bit-identical without being communicated.  *_emulated: all ranks in one cooperative launch
+ * on a tadnn_comm_create_local set (single-GPU tests). */
+int tadnn_allreduce_sgd(tadnn_comm* c, unsigned long long grad_off_bytes, unsigned long long param_off_bytes,
+                        unsigned long long count, float scale, float lr, float weight_decay, int algo,
+                        int max_blocks, int channel, tadnn_stream_t stream);
+int tadnn_allreduce_sgd_emulated(tadnn_comm* const* comms, int world, unsigned long long grad_off_bytes,
+                                 unsigned long long param_off_bytes, unsigned long long count, float scale,
+                                 float lr, float weight_decay, int algo, tadnn_stream_t stream);
+
 /* K4 broadcast of heap[off .. off+bytes) from `root` to every rank (push).  Replaces
  * mpinn.synchronizeParameters (datamodule.lua:33). */
 int tadnn_broadcast(tadnn_comm* c, unsigned long long off_bytes, unsigned long long bytes, int root,

@@ -162,6 +162,82 @@ def main():
             if not relb < 4e-2:
                 fails.append(f"{tag} layer {l} db rel err {relb:.3e}")
 
+    # ---- gradient all-reduce fused with the SGD step: every algo, vs the two-pass statement
+    for n in (64, 4800, 114944, (1 << 20) + 64):
+        for algo in ((1, 2, 3) if ctx.has_multicast else (1, 2)):
+            if algo == 1 and n > (1 << 18):
+                continue
+            reg3 = big[:2 * n]
+            p0 = torch.randn(n, generator=torch.Generator().manual_seed(5)).to(dev)  # identical on every rank
+            g0 = torch.randn(n, device=dev)
+            reg3[:n].copy_(p0)
+            reg3[n:].copy_(g0)
+            gavg = torch.stack(gather_all(g0)).sum(0) / P
+            ref = p0 - 0.1 * (gavg + 0.01 * p0)
+            torch.cuda.synchronize()
+            dist.barrier()
+            off = ctx.offset_of(reg3)
+            ctx.allreduce_sgd_offset(off + 4 * n, off, n, 1.0 / P, 0.1, 0.01, algo=algo, channel=S.CH_DEFAULT)
+            torch.cuda.synchronize()
+            expect(f"allreduce_sgd n={n} algo={algo} params", reg3[:n], ref, 1e-5)
+            expect(f"allreduce_sgd n={n} algo={algo} grads cleared", reg3[n:], torch.zeros(n, device=dev), 0.0)
+            got_all = gather_all(reg3[:n].clone())
+            if any(not torch.equal(got_all[0], g) for g in got_all):
+                fails.append(f"allreduce_sgd n={n} algo={algo}: parameters differ bitwise across ranks")
+            dist.barrier()
+
+    # ---- data-parallel CNN: fused sync+SGD step (tail overlapped with conv1's backward) == unfused two-pass step
+    import tadnn
+    from tadnn.models.cifar_cnn import CifarCNN
+    results = {}
+    for fused in ("1", "0"):
+        os.environ["TADNN_DP_FUSED_SGD"] = fused
+        torch.manual_seed(3)
+        m = CifarCNN(dropout=0.0).to(dev)
+        xs = torch.randn(P * 64, 3, 32, 32, generator=torch.Generator().manual_seed(11)).bfloat16()
+        ys = torch.randint(0, 10, (P * 64,), generator=torch.Generator().manual_seed(12))
+        d, t, n_sh = tadnn.parallelize(xs, ys, m, P * 64, h, None, 1, verbose=False)
+        tr = tadnn.BatchTrainer(m, learningRate=0.05, weightDecay=0.01)
+        for _ in range(3):
+            tr.step(d.to(dev), t.to(dev))
+        torch.cuda.synchronize()
+        results[fused] = torch.cat([p.detach().reshape(-1) for p in m.parameters()]).clone()
+        checks += 1
+        if m._tadnn_sync.fused_step_ok() != (fused == "1" and (P & (P - 1)) == 0):
+            fails.append(f"fused_step_ok() wrong for TADNN_DP_FUSED_SGD={fused}")
+        got_all = gather_all(results[fused])
+        if any(not torch.equal(got_all[0], g) for g in got_all):
+            fails.append(f"DP CNN fused={fused}: replicas differ bitwise after 3 steps")
+        m._tadnn_sync.remove()
+    os.environ.pop("TADNN_DP_FUSED_SGD", None)
+    expect("DP CNN fused vs unfused sync+SGD", results["1"], results["0"], 1e-5)
+
+    # ---- overlap=True vs overlap=False with DIVERGED replicas ('model' mode, sync every 2nd backward)
+    def run_overlap(ov):
+        torch.manual_seed(9)
+        net = torch.nn.Sequential(torch.nn.Linear(256, 512), torch.nn.Tanh(), torch.nn.Linear(512, 256), torch.nn.Tanh(),
+                                  torch.nn.Linear(256, 10)).to(dev)
+        xs = torch.randn(P * 32, 256, generator=torch.Generator().manual_seed(21))
+        ys = torch.randint(0, 10, (P * 32,), generator=torch.Generator().manual_seed(22))
+        d, t, _n = tadnn.parallelize(xs, ys, net, P * 32, h, None, 2, verbose=False, overlap=ov)
+        d, t = d.to(dev), t.to(dev)
+        for i in range(4):
+            loss = torch.nn.functional.cross_entropy(net(d[i * 8:(i + 1) * 8]), t[i * 8:(i + 1) * 8])
+            loss.backward()
+            with torch.no_grad():
+                for p_ in net.parameters():
+                    p_.add_(p_.grad, alpha=-0.05)   # per-rank SGD on different data: replicas diverge between syncs
+                    p_.grad.zero_()
+        torch.cuda.synchronize()
+        out = torch.cat([p_.detach().reshape(-1) for p_ in net.parameters()]).clone()
+        net._tadnn_sync.remove()
+        return out
+    try:
+        a_, b_ = run_overlap(True), run_overlap(False)
+        expect("DP overlap=True vs overlap=False (diverged replicas)", a_, b_, 1e-6)
+    except TypeError as e:  # parallelize() without an overlap keyword
+        fails.append(f"overlap check could not run: {e}")
+
     # ---- device barrier stress
     for _ in range(500):
         ctx.barrier()

@@ -60,6 +60,38 @@ def test_allreduce_emulated_single_launch(world, dtype, algo):
             lib.tadnn_comm_destroy(C.c_void_p(comms[r]))
 
 
+@pytest.mark.parametrize("world", [2, 8])
+@pytest.mark.parametrize("algo", [1, 2])
+def test_allreduce_sgd_emulated_single_launch(world, algo):
+    """Fused gradient all-reduce-average + SGD update + gradient clear, all ranks in one cooperative launch."""
+    from tadnn import _native
+    lib = _native.lib()
+    heap = 4 << 20
+    comms = (C.c_void_p * world)()
+    _native.check(lib.tadnn_comm_create_local(world, C.c_ulonglong(heap), comms), "create_local")
+    try:
+        for n in (64, 4864, 114944):
+            p0 = torch.randn(n, device="cuda")
+            gs = [torch.randn(n, device="cuda") for _ in range(world)]
+            views = [_heap_view(lib, C.c_void_p(comms[r]), heap, comms).view(torch.float32) for r in range(world)]
+            for v, g in zip(views, gs):
+                v[:n].copy_(p0)
+                v[n:2 * n].copy_(g)
+            torch.cuda.synchronize()
+            _native.check(lib.tadnn_allreduce_sgd_emulated(comms, world, C.c_ulonglong(4 * n), C.c_ulonglong(0), C.c_ulonglong(n),
+                                                           C.c_float(1.0 / world), C.c_float(0.1), C.c_float(0.01), algo,
+                                                           C.c_void_p(_native.stream_ptr())), "allreduce_sgd_emulated")
+            torch.cuda.synchronize()
+            ref = p0 - 0.1 * (torch.stack(gs).sum(0) / world + 0.01 * p0)
+            for v in views:
+                assert (v[:n] - ref).abs().max().item() < 1e-5
+                assert float(v[n:2 * n].abs().sum()) == 0.0
+                assert torch.equal(v[:n], views[0][:n])
+    finally:
+        for r in range(world):
+            lib.tadnn_comm_destroy(C.c_void_p(comms[r]))
+
+
 def test_world1_context_and_flat_buffer_sync():
     """parallelize() on a single GPU: flat symmetric buffer, hooks fire, sync is a no-op average."""
     import tadnn

@@ -116,7 +116,7 @@ def _cnn_forward(x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fu
     return loss, logp, saved
 
 
-def _cnn_backward(sv, gw1, gb1, gw2, gb2, gfw1, gfb1, gfw2, gfb2, gloss=None):
+def _cnn_backward(sv, gw1, gb1, gw2, gb2, gfw1, gfb1, gfw2, gfb2, gloss=None, tail_ready=None):
     """Launch the backward kernels; every gradient is ACCUMULATED (+=) into the given fp32 buffers
     (Torch7 layouts).  ``gloss``: optional device scalar dLoss."""
     from ..ops import cnn as K
@@ -147,6 +147,8 @@ def _cnn_backward(sv, gw1, gb1, gw2, gb2, gfw1, gfb1, gfw2, gfb2, gloss=None):
         K.conv2_wgrad_unpack(sh["dwp"], gw2)
         dp1 = _dp1_buffer(dev, B)
         K.gemm_bf16(da2w.view(B, 576), sh["Tt"], b_mn_major=True, out=dp1.view(B, 81 * 64)[:, :7 * 9 * 64])
+        if tail_ready is not None:
+            tail_ready()  # every gradient except conv1's is complete (and nothing below reads those parameters)
         K.conv1_pool_backward_bias(sv["xb"], dp1, p1, idx1, gw1, gb1)
         return
     dp2 = torch.empty((B, 1, 1, 64), device=dev, dtype=torch.bfloat16)
@@ -290,12 +292,14 @@ class CifarCNN(torch.nn.Module, T7Protocol):
         return [self.conv1_weight, self.conv1_bias, self.conv2_weight, self.conv2_bias,
                 self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias]
 
-    def forward_backward(self, x: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+    def forward_backward(self, x: torch.Tensor, target: torch.Tensor, tail_ready=None) -> torch.Tensor:
         """Torch7-style explicit step (``model:forward`` + ``model:backward``): runs the fused
         forward and backward kernels without autograd and ACCUMULATES the gradients into
         ``param.grad`` (= gradWeight/gradBias).  Returns the loss tensor (device).  The caller runs
         the synchronisation hook (``model._tadnn_sync.after_backward(model)``), as the hooked
-        ``Sequential:backward`` does (datamodule.lua:96-110)."""
+        ``Sequential:backward`` does (datamodule.lua:96-110).  ``tail_ready(first_param)``, if given, is called
+        from inside the backward pass once the gradients of ``first_param`` and of every parameter after it
+        are final (here: everything but conv1), so that their synchronisation can overlap conv1's backward."""
         if not self._native_ok(x):
             loss = self.loss(x, target)
             loss.backward()
@@ -309,7 +313,8 @@ class CifarCNN(torch.nn.Module, T7Protocol):
         seed = (self._seed * 2654435761 + self._step * 40503) & 0xFFFFFFFF
         with torch.no_grad():
             loss, _logp, sv = _cnn_forward(x, target, *[p.data for p in ps], pd, seed, self.fused_conv1, self.conv2_mode)
-            _cnn_backward(sv, *[p.grad for p in ps])
+            cb = (lambda: tail_ready(self.conv2_weight)) if (tail_ready is not None and sv.get("fused2")) else None
+            _cnn_backward(sv, *[p.grad for p in ps], tail_ready=cb)
         return loss
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:

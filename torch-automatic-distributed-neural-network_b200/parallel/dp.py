@@ -60,6 +60,7 @@ class SyncState:
                 overlap = nbytes >= (4 << 20)
         self.overlap = bool(overlap) and use_overlap
         self.comm_stream = torch.cuda.Stream() if self.overlap else None
+        self._fused_lo = None
         self.bucket_bytes = int(bucket_mb * (1 << 20))
         self._buckets = self._make_buckets() if self.overlap else []
 
@@ -85,6 +86,53 @@ class SyncState:
             datamodule.synchronizeModel(self.model, self.mpi)
         else:
             self.mpinn.synchronizeGradients(self.model, self.mpi, average=True)
+        self.syncs += 1
+
+    # ------------------------------------------------------------------ fused sync + SGD
+    def fused_step_ok(self) -> bool:
+        """True when a synchronised SGD step can be ONE kernel per gradient range (all-reduce-average +
+        update + gradient clear, csrc/comm.cu ``allreduce_sgd_*``): flat fp32 buffer in the symmetric
+        heap, more than one rank, a sync on every step (``batchSize == 1``: the replicas then always
+        hold identical parameters, so the parameter half of the reference's message,
+        datamodule.lua:214-218, is the identity), and a power-of-two world (sum/P of identical floats
+        is then exact, i.e. skipping it changes no bit)."""
+        f = self.flat
+        if f is None or not f.symmetric or os.environ.get("TADNN_DP_FUSED_SGD", "1") in ("0", "false"):
+            return False
+        P = f.ctx.world
+        return (P > 1 and (P & (P - 1)) == 0 and self.batchSize == 1 and len(f.groups) == 1
+                and next(iter(f.groups)) == torch.float32)
+
+    def fused_tail(self, first_param, lr: float, wd: float) -> None:
+        """Called from inside the backward pass as soon as the gradients of ``first_param`` and of every
+        parameter after it (flat order) are complete: their synchronised update runs on the side
+        stream while the rest of backward is still computing."""
+        g = next(iter(self.flat.groups.values()))
+        _g, lo = self.flat._where[id(first_param)]
+        lo = lo // 64 * 64  # 256-byte granule (parameters are 256-byte aligned in the flat buffer)
+        if self.comm_stream is None:
+            self.comm_stream = torch.cuda.Stream()
+        ev = torch.cuda.current_stream().record_event()
+        self.comm_stream.wait_event(ev)
+        P = self.flat.ctx.world
+        self.flat.ctx.allreduce_sgd_offset(g.heap_off + (g.half + lo) * 4, g.heap_off + lo * 4, g.half - lo, 1.0 / P, lr, wd,
+                                           0, _symm.CH_DP, self.comm_stream)
+        self._fused_lo = lo
+
+    def fused_finish(self, owner, lr: float, wd: float) -> None:
+        """End of backward: the remaining range on the compute stream, then join the side stream.
+        Same counter bookkeeping as ``after_backward``."""
+        g = next(iter(self.flat.groups.values()))
+        hi = getattr(self, "_fused_lo", None)
+        hi = g.half if hi is None else hi
+        P = self.flat.ctx.world
+        if hi > 0:
+            self.flat.ctx.allreduce_sgd_offset(g.heap_off + g.half * 4, g.heap_off, hi, 1.0 / P, lr, wd, 0, _symm.CH_DEFAULT, None)
+        if self._fused_lo is not None:
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        self._fused_lo = None
+        c = getattr(owner, "sync_counter", None) or 1
+        owner.sync_counter = c + 1
         self.syncs += 1
 
     # ------------------------------------------------------------------ autograd path

@@ -345,6 +345,15 @@ class SymmContext:
             C.c_float(scale), C.c_int(algo), C.c_int(max_blocks), C.c_int(channel),
             C.c_void_p(_native.stream_ptr(stream))), "tadnn_allreduce")
 
+    def allreduce_sgd_offset(self, grad_off: int, param_off: int, count: int, scale: float, lr: float,
+                             weight_decay: float = 0.0, algo: int = 0, channel: int = CH_DP, stream=None):
+        """Gradient all-reduce-average fused with the SGD update and the gradient clear (fp32; csrc/comm.cu)."""
+        self.check()
+        _native.check(_native.lib().tadnn_allreduce_sgd(
+            self.handle, C.c_ulonglong(grad_off), C.c_ulonglong(param_off), C.c_ulonglong(count), C.c_float(scale),
+            C.c_float(lr), C.c_float(weight_decay), C.c_int(algo), C.c_int(0), C.c_int(channel),
+            C.c_void_p(_native.stream_ptr(stream))), "tadnn_allreduce_sgd")
+
     def allreduce_(self, t: torch.Tensor, scale: float = 1.0, algo: int = 0,
                    channel: int = CH_DEFAULT, stream=None) -> torch.Tensor:
         """In-place ``t = scale * sum_ranks(t)``.  Zero-copy when ``t`` lives in the heap,

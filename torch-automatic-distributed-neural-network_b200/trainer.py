@@ -71,8 +71,16 @@ class BatchTrainer:
     def _step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
         if self.criterion is None and self._cuda and hasattr(self.model, "forward_backward"):
             # explicit forward+backward (no autograd), then the hooked-backward bookkeeping
-            loss = self.model.forward_backward(x, y)
             st = getattr(self.model, "_tadnn_sync", None)
+            if st is not None and st.fused_step_ok():
+                # synchronised SGD step as fused all-reduce+update kernels: the range whose gradients are
+                # complete early goes on the side stream from inside backward, the rest at the end
+                lr, wd = self.learningRate, self.weightDecay
+                loss = self.model.forward_backward(x, y, tail_ready=lambda p: st.fused_tail(p, lr, wd))
+                st.fused_finish(self.model, lr, wd)
+                self.steps += 1
+                return loss.detach()
+            loss = self.model.forward_backward(x, y)
             if st is not None:
                 st.after_backward(self.model)
         else:

@@ -483,6 +483,27 @@ struct HeadArgs {
 constexpr int kHeadS = 32;
 __host__ __device__ constexpr int head_hp(int H) { return (H + 3) & ~3; }
 
+// Stage `n` elements into shared memory with the global loads of 8 elements per thread in flight at once
+// (written as load-all-then-store-all: in the plain one-element loop every iteration waited for its own L2
+// round trip, and those serial round trips were most of the head kernels' time).
+template <typename Load>
+__device__ __forceinline__ void stage8(float* dst, int n, int t, Load load) {
+#pragma unroll 1
+  for (int i0 = t; i0 < n; i0 += 256 * 8) {
+    float v[8];
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int i = i0 + u * 256;
+      v[u] = i < n ? load(i) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int i = i0 + u * 256;
+      if (i < n) dst[i] = v[u];
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256) head_fwd_kernel(HeadArgs a) {
   extern __shared__ __align__(16) float sm[];
   const int HP = head_hp(a.H);
@@ -496,16 +517,16 @@ __global__ void __launch_bounds__(256) head_fwd_kernel(HeadArgs a) {
   __shared__ float block_loss;
   __shared__ bool is_last;
   const int t = threadIdx.x;
-  for (int i = t; i < kHeadD * HP; i += 256) {
+  stage8(w1t, kHeadD * HP, t, [&](int i) {
     const int d = i / HP, j = i - d * HP;
-    w1t[i] = (d < a.D && j < a.H) ? a.w1[j * a.D + d] : 0.f;
-  }
-  for (int i = t; i < a.NC * HP; i += 256) {
+    return (d < a.D && j < a.H) ? __ldg(a.w1 + j * a.D + d) : 0.f;
+  });
+  stage8(w2s, a.NC * HP, t, [&](int i) {
     const int c = i / HP, j = i - c * HP;
-    w2s[i] = j < a.H ? a.w2[c * a.H + j] : 0.f;
-  }
-  for (int i = t; i < HP; i += 256) b1[i] = i < a.H ? a.b1[i] : 0.f;
-  if (t < kHeadC) b2[t] = t < a.NC ? a.b2[t] : 0.f;
+    return j < a.H ? __ldg(a.w2 + c * a.H + j) : 0.f;
+  });
+  for (int i = t; i < HP; i += 256) b1[i] = i < a.H ? __ldg(a.b1 + i) : 0.f;
+  if (t < kHeadC) b2[t] = t < a.NC ? __ldg(a.b2 + t) : 0.f;
   const int nJ = HP >> 2;
   const int jq = t % nJ, sq = t / nJ;       // phase-1 tile: hidden units 4*jq.., samples 4*sq..
   float my_loss = 0.f;
@@ -513,13 +534,18 @@ __global__ void __launch_bounds__(256) head_fwd_kernel(HeadArgs a) {
   for (int ch = blockIdx.x; ch < chunks; ch += gridDim.x) {
     const int base = ch * kHeadS;
     __syncthreads();
-    for (int i = t; i < kHeadS * kHeadD; i += 256) {
-      const int s = i >> 6, d = i & 63;
-      float v = 0.f;
-      if (base + s < a.B && d < a.D)
-        v = __bfloat162float(a.p2[static_cast<long long>(base + s) * a.D + d]) *
-            dropout_scale(a.seed, static_cast<uint32_t>(base + s) * a.D + d, a.p);
-      sdt[d * kHeadS + s] = v;
+    {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = t + u * 256, s = i >> 6, d = i & 63;
+        v[u] = (base + s < a.B && d < a.D) ? __bfloat162float(a.p2[static_cast<long long>(base + s) * a.D + d]) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int i = t + u * 256, s = i >> 6, d = i & 63;
+        sdt[d * kHeadS + s] = v[u] * dropout_scale(a.seed, static_cast<uint32_t>(base + s) * a.D + d, a.p);
+      }
     }
     __syncthreads();
     if (sq < kHeadS / 4) {
@@ -619,14 +645,14 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(HeadArgs a) {
   float* sdl = sh + kHeadS * HP;            // [32][32]  dL/dlogits
   float* sgb = sdl + kHeadS * kHeadC;       // [8][64]   bias-gradient partials of the layer before the pool
   const int t = threadIdx.x;
-  for (int i = t; i < HP * kHeadD; i += 256) {
+  stage8(w1s, HP * kHeadD, t, [&](int i) {
     const int j = i >> 6, d = i & 63;
-    w1s[i] = (j < a.H && d < a.D) ? a.w1[j * a.D + d] : 0.f;
-  }
-  for (int i = t; i < a.NC * HP; i += 256) {
+    return (j < a.H && d < a.D) ? __ldg(a.w1 + j * a.D + d) : 0.f;
+  });
+  stage8(w2s, a.NC * HP, t, [&](int i) {
     const int c = i / HP, j = i - c * HP;
-    w2s[i] = j < a.H ? a.w2[c * a.H + j] : 0.f;
-  }
+    return j < a.H ? __ldg(a.w2 + c * a.H + j) : 0.f;
+  });
   const float inv_b = a.grad_scale * (a.grad_scale_dev != nullptr ? *a.grad_scale_dev : 1.0f) / static_cast<float>(a.B);
   const int nJ = HP >> 2;
   // register accumulators
@@ -649,24 +675,32 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(HeadArgs a) {
     const int base = ch * kHeadS;
     __syncthreads();
     // ---- A: stage the chunk
-    for (int i = t; i < kHeadS * kHeadD; i += 256) {
+    stage8(sd, kHeadS * kHeadD, t, [&](int i) {
       const int s = i >> 6, d = i & 63;
-      float v = 0.f;
-      if (base + s < a.B && d < a.D)
-        v = __bfloat162float(a.p2[static_cast<long long>(base + s) * a.D + d]) *
-            dropout_scale(a.seed, static_cast<uint32_t>(base + s) * a.D + d, a.p);
-      sd[i] = v;
-    }
-    for (int i = t; i < kHeadS * HP; i += 256) {
+      return (base + s < a.B && d < a.D) ? __bfloat162float(a.p2[static_cast<long long>(base + s) * a.D + d]) : 0.f;
+    });
+    stage8(sh, kHeadS * HP, t, [&](int i) {
       const int s = i / HP, j = i - s * HP;
-      sh[i] = (base + s < a.B && j < a.H) ? a.hbuf[static_cast<long long>(base + s) * a.H + j] : 0.f;
-    }
-    for (int i = t; i < kHeadS * kHeadC; i += 256) {
+      return (base + s < a.B && j < a.H) ? __ldg(a.hbuf + static_cast<long long>(base + s) * a.H + j) : 0.f;
+    });
+    stage8(sdl, kHeadS * kHeadC, t, [&](int i) {
       const int s = i >> 5, c = i & 31;
+      return (base + s < a.B && c < a.NC) ? __ldg(a.logp + static_cast<long long>(base + s) * a.NC + c) : 1.f;
+    });
+    __syncthreads();
+    // dropout on the staged input; dL/dlogits from the staged log-probabilities (own elements only: no sync needed in between)
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const int i = t + u * 256, s = i >> 6, d = i & 63;
+      sd[i] *= dropout_scale(a.seed, static_cast<uint32_t>(base + s) * a.D + d, a.p);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = t + u * 256, s = i >> 5, c = i & 31;
       float v = 0.f;
       if (base + s < a.B && c < a.NC) {
-        const int tg = static_cast<int>(a.target[base + s]);
-        v = (__expf(a.logp[static_cast<long long>(base + s) * a.NC + c]) - (c == tg ? 1.f : 0.f)) * inv_b;
+        const int tg = static_cast<int>(__ldg(a.target + base + s));
+        v = (__expf(sdl[i]) - (c == tg ? 1.f : 0.f)) * inv_b;
       }
       sdl[i] = v;
     }
@@ -693,34 +727,47 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(HeadArgs a) {
         acc[3][0] = fmaf(g.w, w.x, acc[3][0]); acc[3][1] = fmaf(g.w, w.y, acc[3][1]);
       }
       if (2 * ip < a.D) {
+        const bool route = a.dpre != nullptr && (a.D & 1) == 0;
+        uint32_t pvs[4] = {0, 0, 0, 0};
+        uint32_t ivs[4] = {0, 0, 0, 0};
+        if (route) {   // all four samples' pooled values and arg-max bytes in flight together
+#pragma unroll
+          for (int x = 0; x < 4; ++x) {
+            const long long s = base + 4 * sg + x;
+            if (s < a.B) {
+              pvs[x] = *reinterpret_cast<const uint32_t*>(a.p2 + s * a.D + 2 * ip);
+              ivs[x] = *reinterpret_cast<const uint16_t*>(a.pool_idx + s * a.D + 2 * ip);
+            }
+          }
+        }
 #pragma unroll
         for (int x = 0; x < 4; ++x) {
           const long long s = base + 4 * sg + x;
-          if (s >= a.B) break;
-          const uint32_t e = static_cast<uint32_t>(s) * a.D + 2 * ip;
-          const float g0 = acc[x][0] * dropout_scale(a.seed, e, a.p);
-          const float g1 = (2 * ip + 1 < a.D) ? acc[x][1] * dropout_scale(a.seed, e + 1, a.p) : 0.f;
-          const uint32_t gp = pack_bf16x2(g0, g1);
-          if ((a.D & 1) == 0) {
-            if (a.dp2 != nullptr) *reinterpret_cast<uint32_t*>(a.dp2 + s * a.D + 2 * ip) = gp;
-            if (a.dpre != nullptr) {
-              const uint32_t pv = *reinterpret_cast<const uint32_t*>(a.p2 + s * a.D + 2 * ip);
-              const uint16_t iv = *reinterpret_cast<const uint16_t*>(a.pool_idx + s * a.D + 2 * ip);
-              const uint32_t live = ((pv & 0xffffu) ? 0xffffu : 0u) | ((pv & 0xffff0000u) ? 0xffff0000u : 0u);  // ReLU output > 0
-              const uint32_t gl = gp & live;
-              const float2 gf = unpack_bf16x2(gl);
-              accp[0] += gf.x;
-              accp[1] += gf.y;
-              const uint32_t p0 = iv & 0xffu, p1 = iv >> 8;
+          if (s < a.B) {
+            const uint32_t e = static_cast<uint32_t>(s) * a.D + 2 * ip;
+            const float g0 = acc[x][0] * dropout_scale(a.seed, e, a.p);
+            const float g1 = (2 * ip + 1 < a.D) ? acc[x][1] * dropout_scale(a.seed, e + 1, a.p) : 0.f;
+            const uint32_t gp = pack_bf16x2(g0, g1);
+            if ((a.D & 1) == 0) {
+              if (a.dp2 != nullptr) *reinterpret_cast<uint32_t*>(a.dp2 + s * a.D + 2 * ip) = gp;
+              if (route) {
+                const uint32_t pv = pvs[x], iv = ivs[x];
+                const uint32_t live = ((pv & 0xffffu) ? 0xffffu : 0u) | ((pv & 0xffff0000u) ? 0xffff0000u : 0u);  // ReLU output > 0
+                const uint32_t gl = gp & live;
+                const float2 gf = unpack_bf16x2(gl);
+                accp[0] += gf.x;
+                accp[1] += gf.y;
+                const uint32_t p0 = iv & 0xffu, p1 = iv >> 8;
 #pragma unroll
-              for (uint32_t pos = 0; pos < 9; ++pos) {
-                const uint32_t m = (p0 == pos ? 0xffffu : 0u) | (p1 == pos ? 0xffff0000u : 0u);
-                *reinterpret_cast<uint32_t*>(a.dpre + (s * 9 + pos) * a.D + 2 * ip) = gl & m;
+                for (uint32_t pos = 0; pos < 9; ++pos) {
+                  const uint32_t m = (p0 == pos ? 0xffffu : 0u) | (p1 == pos ? 0xffff0000u : 0u);
+                  *reinterpret_cast<uint32_t*>(a.dpre + (s * 9 + pos) * a.D + 2 * ip) = gl & m;
+                }
               }
+            } else if (a.dp2 != nullptr) {
+              a.dp2[s * a.D + 2 * ip] = __float2bfloat16_rn(g0);
+              if (2 * ip + 1 < a.D) a.dp2[s * a.D + 2 * ip + 1] = __float2bfloat16_rn(g1);
             }
-          } else if (a.dp2 != nullptr) {
-            a.dp2[s * a.D + 2 * ip] = __float2bfloat16_rn(g0);
-            if (2 * ip + 1 < a.D) a.dp2[s * a.D + 2 * ip + 1] = __float2bfloat16_rn(g1);
           }
         }
       }

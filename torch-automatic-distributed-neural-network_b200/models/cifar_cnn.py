@@ -256,7 +256,8 @@ class CifarCNN(torch.nn.Module, T7Protocol):
         def r(t):
             return t.to(torch.bfloat16).float() if emulate_bf16 else t
         x = x.float()
-        y = F.conv2d(x, r(self.conv1_weight).view(64, 3, 5, 5), self.conv1_bias)
+        # the fused conv1 carries its bias through the GEMM as a bf16 operand column
+        y = F.conv2d(x, r(self.conv1_weight).view(64, 3, 5, 5), r(self.conv1_bias) if self.fused_conv1 else self.conv1_bias)
         y = F.max_pool2d(r(F.relu(y)), 3, 3)
         y = F.conv2d(y, r(self.conv2_weight).view(64, 64, 5, 5), self.conv2_bias)
         y = F.max_pool2d(r(F.relu(y)), 3, 3).reshape(-1, 64)

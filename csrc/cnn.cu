@@ -280,7 +280,7 @@ __global__ void maxpool_fwd_nhwc_kernel(const uint4* __restrict__ x, uint4* __re
 // (ReLU backward folded in: the pooled value is the max of ReLU outputs), else 0.
 __global__ void maxpool_relu_bwd_nhwc_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ y,
                                              const uint2* __restrict__ idx, uint4* __restrict__ dx, int B, int H, int W,
-                                             int C8, int PK, int PH, int PW) {
+                                             int C8, int PK, int PH, int PW, int relu) {
   const long long total = static_cast<long long>(B) * H * W * C8;
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
@@ -306,7 +306,7 @@ __global__ void maxpool_relu_bwd_nhwc_kernel(const uint4* __restrict__ dy, const
         const unsigned i1 = ((j < 2 ? id.x : id.y) >> (16 * (j & 1) + 8)) & 0xffu;
         const float2 gv = unpack_bf16x2(gw[j]);
         const float2 yv = unpack_bf16x2(pw[j]);
-        ow[j] = pack_bf16x2((i0 == me && yv.x > 0.f) ? gv.x : 0.f, (i1 == me && yv.y > 0.f) ? gv.y : 0.f);
+        ow[j] = pack_bf16x2((i0 == me && (!relu || yv.x > 0.f)) ? gv.x : 0.f, (i1 == me && (!relu || yv.y > 0.f)) ? gv.y : 0.f);
       }
       o = make_uint4(ow[0], ow[1], ow[2], ow[3]);
     }
@@ -858,6 +858,19 @@ __global__ void cast_f32_to_bf16_kernel(const float* __restrict__ x, __nv_bfloat
     y[i] = __float2bfloat16_rn(x[i]);
 }
 
+// fp32 [rows, cols] (row pitch ldx) -> bf16 (row pitch ldy >= cols, typically cols rounded up to 8 so that the
+// result is a legal TMA operand whatever the layer width)
+__global__ void cast_f32_to_bf16_2d_kernel(const float* __restrict__ x, long long ldx, __nv_bfloat16* __restrict__ y, long long ldy,
+                                           long long rows, int cols) {
+  const long long total = rows * cols;
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const long long r = i / cols;
+    const int c = static_cast<int>(i - r * cols);
+    y[r * ldy + c] = __float2bfloat16_rn(x[r * ldx + c]);
+  }
+}
+
 int grid_for(long long total, int threads) {
   long long b = (total + threads - 1) / threads;
   const long long cap = static_cast<long long>(sm_count()) * 16;
@@ -958,12 +971,19 @@ extern "C" int tadnn_maxpool_fwd(const void* x, void* y, void* idx, int B, int H
   return 0;
 }
 
+static int maxpool_bwd_impl(const void* dy, const void* y, const void* idx, void* dx, int B, int H, int W, int C, int k, int relu, tadnn_stream_t stream_);
 extern "C" int tadnn_maxpool_relu_bwd(const void* dy, const void* y, const void* idx, void* dx, int B, int H, int W, int C, int k, tadnn_stream_t stream_) {
+  return maxpool_bwd_impl(dy, y, idx, dx, B, H, W, C, k, 1, stream_);
+}
+extern "C" int tadnn_maxpool_bwd(const void* dy, const void* y, const void* idx, void* dx, int B, int H, int W, int C, int k, tadnn_stream_t stream_) {
+  return maxpool_bwd_impl(dy, y, idx, dx, B, H, W, C, k, 0, stream_);
+}
+static int maxpool_bwd_impl(const void* dy, const void* y, const void* idx, void* dx, int B, int H, int W, int C, int k, int relu, tadnn_stream_t stream_) {
   TADNN_REQUIRE(B > 0 && C % 8 == 0 && k >= 1 && k <= 15 && H >= k && W >= k, "maxpool_relu_bwd: bad shape");
   const int PH = H / k, PW = W / k;
   const long long total = static_cast<long long>(B) * H * W * (C / 8);
-  maxpool_relu_bwd_nhwc_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(static_cast<const uint4*>(dy), static_cast<const uint4*>(y), static_cast<const uint2*>(idx), static_cast<uint4*>(dx), B, H, W, C / 8, k, PH, PW);
-  TADNN_LAUNCH_CHECK("maxpool_relu_bwd_nhwc");
+  maxpool_relu_bwd_nhwc_kernel<<<grid_for(total, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(static_cast<const uint4*>(dy), static_cast<const uint4*>(y), static_cast<const uint2*>(idx), static_cast<uint4*>(dx), B, H, W, C / 8, k, PH, PW, relu);
+  TADNN_LAUNCH_CHECK(relu ? "maxpool_relu_bwd_nhwc" : "maxpool_bwd_nhwc");
   return 0;
 }
 
@@ -1151,6 +1171,14 @@ extern "C" int tadnn_sgd_step(float* p, float* g, long long n, float lr, float w
 extern "C" int tadnn_cast_f32_bf16(const float* x, void* y, long long n, tadnn_stream_t stream_) {
   if (n <= 0) return 0;
   cast_f32_to_bf16_kernel<<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(x, static_cast<__nv_bfloat16*>(y), n);
+  TADNN_LAUNCH_CHECK("cast_f32_bf16");
+  return 0;
+}
+
+extern "C" int tadnn_cast_f32_bf16_2d(const float* x, long long ldx, void* y, long long ldy, long long rows, int cols, tadnn_stream_t stream_) {
+  if (rows <= 0 || cols <= 0) return 0;
+  TADNN_REQUIRE(ldx >= cols && ldy >= cols, "cast_f32_bf16_2d: pitches must be >= cols");
+  cast_f32_to_bf16_2d_kernel<<<grid_for(rows * cols, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(x, ldx, static_cast<__nv_bfloat16*>(y), ldy, rows, cols);
   TADNN_LAUNCH_CHECK("cast_f32_bf16");
   return 0;
 }

@@ -256,6 +256,10 @@ int tadnn_col2im(const void* dcol, void* dx, int B, int C, int H, int W, int KH,
 int tadnn_maxpool_fwd(const void* x, void* y, void* idx, int B, int H, int W, int C, int k,
                       tadnn_stream_t stream);
 /* Backward of ReLU followed by that pooling: dx = dy routed to the argmax where y > 0. */
+/* tadnn_maxpool_bwd: plain max-pool backward (gradient to the arg-max); tadnn_maxpool_relu_bwd additionally
+ * masks windows whose pooled value is <= 0 (a ReLU directly before the pool, folded in). */
+int tadnn_maxpool_bwd(const void* dy, const void* y, const void* idx, void* dx, int B, int H, int W, int C, int k,
+                      tadnn_stream_t stream);
 int tadnn_maxpool_relu_bwd(const void* dy, const void* y, const void* idx, void* dx, int B, int H,
                            int W, int C, int k, tadnn_stream_t stream);
 /* out[c] += sum_r x[r,c]  (bias gradient; x bf16 [R, ld], out fp32). */
@@ -359,6 +363,9 @@ int tadnn_head_forward_noalloc(const tadnn_head_args* a, tadnn_stream_t stream);
 int tadnn_sgd_step(float* p, float* g, long long n, float lr, float weight_decay, int zero_grad,
                    tadnn_stream_t stream);
 int tadnn_cast_f32_bf16(const float* x, void* y, long long n, tadnn_stream_t stream);
+/* 2-D form with row pitches (elements): lets a layer of any width become a TMA operand (pitch rounded up to 8). */
+int tadnn_cast_f32_bf16_2d(const float* x, long long ldx, void* y, long long ldy, long long rows, int cols,
+                           tadnn_stream_t stream);
 
 /* ---- linear layers with a tiny output width (csrc/smalln.cu) -----------------------------------
  * The classifier layer of the README MLP is MPBaseLinear(i, 10) (nodemodule.lua:86-119): one 128-wide

@@ -27,7 +27,43 @@ class Sequential(torch.nn.Sequential, T7Protocol):
         return self[i]
 
     def _run(self, x):
+        fused = self._mp_fused(x)
+        if fused is not None:
+            from .. import _native
+            try:
+                return fused(x)
+            except (AssertionError, _native.NativeError):  # a shape the fused kernels do not cover: per-layer path
+                self.__dict__["_tadnn_mp_fused"] = None
         return torch.nn.Sequential.forward(self, x)
+
+    def _mp_fused(self, x):
+        """A stack of ``MP*`` layers on a GPU runs as the fused model-parallel module (``parallel/tp.py``:
+        GEMM epilogues that push their tiles to the owner ranks, tanh in the reduction) — what
+        ``fuse_mp(model)`` builds by hand, done once on the first CUDA forward.  Same parameters (shared,
+        not copied).  Opt out per model with ``model._tadnn_no_autofuse = True`` or globally with
+        ``TADNN_MP_AUTOFUSE=0``."""
+        import os
+        if not (torch.is_tensor(x) and x.is_cuda) or getattr(self, "_tadnn_no_autofuse", False):
+            return None
+        cached = self.__dict__.get("_tadnn_mp_fused", False)
+        if cached is not False:
+            return cached
+        fused = None
+        if os.environ.get("TADNN_MP_AUTOFUSE", "1") not in ("0", "false"):
+            from .mp import MPBaseLinear, MPInitialLinear, MPInitialReshape, MPTanh
+            mods = list(self)
+            if mods and any(isinstance(m, MPInitialLinear) for m in mods) and \
+                    all(isinstance(m, (MPInitialReshape, MPInitialLinear, MPBaseLinear, MPTanh)) for m in mods):
+                try:
+                    from .mp import _handle, fuse_mp
+                    lin = next(m for m in mods if isinstance(m, MPInitialLinear))
+                    h = _handle(lin._mpi)
+                    if getattr(h, "symm", None) is not None:
+                        fused = fuse_mp(self, mpi=h)
+                except Exception:  # noqa: BLE001 - an unsupported stack simply stays on the per-layer path
+                    fused = None
+        self.__dict__["_tadnn_mp_fused"] = fused
+        return fused
 
     def forward(self, input):  # noqa: D102
         return self._t7_forward(input)
@@ -50,6 +86,11 @@ class Linear(torch.nn.Linear, T7Protocol):
             if self.bias is not None:
                 self.bias.uniform_(-stdv, stdv)
         return self
+
+    def forward(self, x):
+        """CUDA: tcgen05 GEMM forward / dgrad / wgrad (ops/native_nn.py); elsewhere ``F.linear``."""
+        from ..ops import native_nn
+        return native_nn.linear(x, self.weight, self.bias)
 
 
 class Tanh(torch.nn.Tanh, T7Protocol):
@@ -137,6 +178,11 @@ class SpatialConvolutionMM(torch.nn.Module, T7Protocol):
         squeeze = x.dim() == 3
         if squeeze:
             x = x.unsqueeze(0)
+        from ..ops import native_nn
+        if native_nn.conv_ok(x, self.weight, self.kH, self.kW, self.dH, self.dW, self.padH, self.padW):
+            # CUDA: im2col + tcgen05 GEMM; the result is NHWC in memory, NCHW in shape (channels_last strides)
+            y = native_nn.Conv2dFn.apply(x, self.weight, self.bias, self.kH, self.kW)
+            return y.squeeze(0) if squeeze else y
         w = self.weight.view(self.nOutputPlane, self.nInputPlane, self.kH, self.kW)
         y = F.conv2d(x, w.to(x.dtype), self.bias.to(x.dtype), stride=(self.dH, self.dW),
                      padding=(self.padH, self.padW))
@@ -154,7 +200,11 @@ class SpatialMaxPooling(torch.nn.Module, T7Protocol):
         squeeze = x.dim() == 3
         if squeeze:
             x = x.unsqueeze(0)
-        y = F.max_pool2d(x, (self.kH, self.kW), (self.dH, self.dW), (self.padH, self.padW))
+        from ..ops import native_nn
+        if native_nn.pool_ok(x, self.kH, self.kW, self.dH, self.dW, self.padH, self.padW):
+            y = native_nn.MaxPoolFn.apply(x, self.kH)   # NHWC bf16 kernel with saved arg-max bytes
+        else:
+            y = F.max_pool2d(x, (self.kH, self.kW), (self.dH, self.dW), (self.padH, self.padW))
         return y.squeeze(0) if squeeze else y
 
 

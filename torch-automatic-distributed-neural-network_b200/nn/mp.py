@@ -167,7 +167,8 @@ class _MPLinear(torch.nn.Module, T7Protocol):
         h = _handle(self._mpi)
         x = _Narrow.apply(input, h, self.compat) if (input.requires_grad and h.size() > 1) \
             else narrowInput(input, h)
-        y = F.linear(x, self.weight.to(x.dtype), self.bias.to(x.dtype))
+        from ..ops import native_nn
+        y = native_nn.linear(x, self.weight, self.bias)   # CUDA: tcgen05 GEMM (strided slice = TMA pitch), else F.linear
         if _print_dims():
             print(f"#{type(self).__name__} UPDATE OUTPUT# input {tuple(x.shape)} output {tuple(y.shape)}")
         if h.size() > 1:

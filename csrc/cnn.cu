@@ -852,6 +852,19 @@ __global__ void sgd_kernel(float* __restrict__ p, float* __restrict__ g, long lo
     if (zero_grad) g[i] = 0.f;
   }
 }
+// SGD step that also refreshes the bf16 operand copy of the weights (what the GEMMs read): one pass instead of an
+// optimiser pass plus a cast pass per forward.
+__global__ void sgd_shadow_kernel(float4* __restrict__ p, const float4* __restrict__ g, uint2* __restrict__ shadow, long long n4, float lr,
+                                  float wd) {
+  for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n4;
+       i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    float4 w = p[i];
+    const float4 d = g[i];
+    w.x -= lr * (d.x + wd * w.x); w.y -= lr * (d.y + wd * w.y); w.z -= lr * (d.z + wd * w.z); w.w -= lr * (d.w + wd * w.w);
+    p[i] = w;
+    shadow[i] = make_uint2(pack_bf16x2(w.x, w.y), pack_bf16x2(w.z, w.w));
+  }
+}
 __global__ void cast_f32_to_bf16_kernel(const float* __restrict__ x, __nv_bfloat16* __restrict__ y, long long n) {
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<long long>(gridDim.x) * blockDim.x)
@@ -1180,5 +1193,15 @@ extern "C" int tadnn_cast_f32_bf16_2d(const float* x, long long ldx, void* y, lo
   TADNN_REQUIRE(ldx >= cols && ldy >= cols, "cast_f32_bf16_2d: pitches must be >= cols");
   cast_f32_to_bf16_2d_kernel<<<grid_for(rows * cols, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(x, ldx, static_cast<__nv_bfloat16*>(y), ldy, rows, cols);
   TADNN_LAUNCH_CHECK("cast_f32_bf16");
+  return 0;
+}
+
+extern "C" int tadnn_sgd_step_shadow(float* p, const float* g, void* shadow_bf16, long long n, float lr, float weight_decay, tadnn_stream_t stream_) {
+  if (n <= 0) return 0;
+  TADNN_REQUIRE(n % 4 == 0 && ((reinterpret_cast<uintptr_t>(p) | reinterpret_cast<uintptr_t>(g)) & 15) == 0 && (reinterpret_cast<uintptr_t>(shadow_bf16) & 7) == 0,
+                "sgd_step_shadow: n must be a multiple of 4 and the buffers 16-byte (shadow: 8-byte) aligned");
+  sgd_shadow_kernel<<<grid_for(n / 4, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(reinterpret_cast<float4*>(p), reinterpret_cast<const float4*>(g),
+                                                                                         static_cast<uint2*>(shadow_bf16), n / 4, lr, weight_decay);
+  TADNN_LAUNCH_CHECK("sgd_step_shadow");
   return 0;
 }

@@ -346,6 +346,56 @@ __global__ void __launch_bounds__(512) allreduce_sgd_twoshot_kernel(CommDev c, s
   block_barrier(c, channel);
 }
 
+// ---- low-latency all-reduce (fp32, <= kLLMaxFloats): data and flag travel together ------------------
+// Every rank stores its vector into ITS slot of every rank's staging area as 8-byte {value, epoch} pairs
+// (one NVLink one-way trip), then sums the P slots of its OWN staging area, spinning on each pair until its
+// epoch matches: no barrier, no second round trip.  The staging area is double-buffered on the parity of the
+// epoch: a peer can be at most one call ahead (it cannot finish call e+1 without our data for e+1, which we
+// send only after we have read everything of call e), so call e+1 never overwrites pairs of call e that are
+// still unread.  MODE 0: result written in place; MODE 1: fused SGD step on `p`, gradient cleared.
+constexpr int kLLMaxFloats = TADNN_LL_MAX_FLOATS;
+template <int MODE>
+__global__ void __launch_bounds__(512) allreduce_ll_kernel(CommDev c, size_t ll_off, size_t data_off, size_t p_off, int n, float scale,
+                                                           float lr, float wd, uint32_t epoch) {
+  const int rank = my_rank(c);
+  const int stride = gridDim.x * blockDim.x;
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t half = static_cast<size_t>(c.world) * kLLMaxFloats * 8;
+  const size_t base = ll_off + (epoch & 1u) * half;
+  float* data = reinterpret_cast<float*>(c.heap[rank] + data_off);
+  for (int i = tid; i < n; i += stride) {
+    const uint32_t v = __float_as_uint(data[i]);
+    const size_t o = base + (static_cast<size_t>(rank) * kLLMaxFloats + i) * 8;
+#pragma unroll
+    for (int q = 0; q < kMaxRanks; ++q)
+      if (q < c.world) asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(c.heap[q] + o), "r"(v), "r"(epoch) : "memory");
+  }
+  const unsigned long long t0 = globaltimer_ns();
+  for (int i = tid; i < n; i += stride) {
+    float acc = 0.f;
+    bool failed = false;
+    for (int r = 0; r < c.world && !failed; ++r) {
+      const uint8_t* src = c.heap[rank] + base + (static_cast<size_t>(r) * kLLMaxFloats + i) * 8;
+      uint32_t v, e, spins = 0;
+      for (;;) {
+        asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v), "=r"(e) : "l"(src) : "memory");
+        if (e == epoch) break;
+        if (barrier_spin_check(c, spins, t0, rank, r, 7, 2)) { failed = true; break; }
+      }
+      acc += __uint_as_float(v);
+    }
+    const float g = acc * scale;
+    if (MODE == 0) {
+      data[i] = g;
+    } else {
+      float* pp = reinterpret_cast<float*>(c.heap[rank] + p_off) + i;
+      const float w = *pp;
+      *pp = w - lr * (g + wd * w);
+      data[i] = 0.f;
+    }
+  }
+}
+
 // ---- tail (< 16 B) handled by a scalar one-shot on a single block -----------
 template <int DT>
 __global__ void allreduce_tail_kernel(CommDev c, size_t off_bytes, int n, float scale, int channel) {
@@ -607,7 +657,8 @@ int do_allreduce(const CommDev& dev, bool has_mc, unsigned long long off_bytes, 
   if (algo == 0) {
     // one-shot moves (P-1)*S per rank but has the shortest critical path; two-shot / NVLS
     // move ~2(P-1)/P*S.  Crossover measured on NVSwitch sits at a few hundred KB.
-    if (bytes <= (512u << 10)) algo = 1;
+    // (measured at P = 8: 64 KB one-shot 23 us vs two-shot 18 / NVLS 19; 1 MB 35 vs 26 / 24)
+    if (bytes * static_cast<size_t>(dev.world - 1) <= (512u << 10)) algo = 1;
     else algo = has_mc ? 3 : 2;
   }
   TADNN_REQUIRE(algo >= 1 && algo <= 3, "allreduce: unknown algo %d", algo);
@@ -832,7 +883,7 @@ extern "C" int tadnn_allreduce_sgd(tadnn_comm* c, unsigned long long grad_off, u
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   const size_t nvec = count / 4;
   const bool has_mc = c->dev.mc_heap != nullptr;
-  if (algo == 0) algo = (count * 4 <= (512u << 10)) ? 1 : (has_mc ? 3 : 2);
+  if (algo == 0) algo = (count * 4 * static_cast<unsigned long long>(c->world - 1) <= (512u << 10)) ? 1 : (has_mc ? 3 : 2);
   TADNN_REQUIRE(algo >= 1 && algo <= 3 && (algo != 3 || has_mc), "allreduce_sgd: algo %d unavailable on this context", algo);
   if (algo == 1) {
     const int blocks = pick_blocks(nvec, max_blocks, 64);
@@ -862,6 +913,40 @@ extern "C" int tadnn_allreduce_sgd_emulated(tadnn_comm* const* comms, int world,
   const size_t g = grad_off, p = param_off;
   if (algo == 1) return launch_maybe_coop(dev, allreduce_sgd_oneshot_kernel, pick_blocks(nvec, 8, 8), 512, static_cast<cudaStream_t>(stream_), "allreduce_sgd_oneshot", dev, g, p, nvec, scale, lr, weight_decay, 0);
   return launch_maybe_coop(dev, allreduce_sgd_twoshot_kernel, pick_blocks(nvec / world + 1, 8, 8), 512, static_cast<cudaStream_t>(stream_), "allreduce_sgd_twoshot", dev, g, p, nvec, scale, lr, weight_decay, 0);
+}
+
+extern "C" int tadnn_allreduce_ll(tadnn_comm* c, unsigned long long ll_off, unsigned long long off_bytes, unsigned long long param_off,
+                                  unsigned long long count, float scale, int sgd, float lr, float weight_decay, unsigned int epoch,
+                                  tadnn_stream_t stream_) {
+  if (int rc = validate(c, 0, "allreduce_ll")) return rc;
+  TADNN_REQUIRE(count > 0 && count <= static_cast<unsigned long long>(kLLMaxFloats), "allreduce_ll: %llu floats exceed the %d the staging area holds", count, kLLMaxFloats);
+  TADNN_REQUIRE(epoch != 0, "allreduce_ll: epoch 0 is reserved (freshly zeroed staging)");
+  const unsigned long long need = 2ull * c->world * kLLMaxFloats * 8ull;
+  TADNN_REQUIRE(ll_off % 8 == 0 && ll_off + need <= c->heap_bytes && off_bytes % 4 == 0 && off_bytes + count * 4 <= c->heap_bytes,
+                "allreduce_ll: staging area or data range outside the heap");
+  const int n = static_cast<int>(count);
+  int blocks = (n + 511) / 512;
+  if (blocks > 32) blocks = 32;
+  if (sgd) allreduce_ll_kernel<1><<<blocks, 512, 0, static_cast<cudaStream_t>(stream_)>>>(c->dev, ll_off, off_bytes, param_off, n, scale, lr, weight_decay, epoch);
+  else allreduce_ll_kernel<0><<<blocks, 512, 0, static_cast<cudaStream_t>(stream_)>>>(c->dev, ll_off, off_bytes, 0, n, scale, 0.f, 0.f, epoch);
+  TADNN_LAUNCH_CHECK(sgd ? "allreduce_sgd_ll" : "allreduce_ll");
+  return 0;
+}
+
+extern "C" int tadnn_allreduce_ll_emulated(tadnn_comm* const* comms, int world, unsigned long long ll_off, unsigned long long off_bytes,
+                                           unsigned long long param_off, unsigned long long count, float scale, int sgd, float lr,
+                                           float weight_decay, unsigned int epoch, tadnn_stream_t stream_) {
+  TADNN_REQUIRE(comms && world >= 1 && world <= kMaxRanks && count > 0 && count <= static_cast<unsigned long long>(kLLMaxFloats) && epoch != 0,
+                "allreduce_ll_emulated: bad arguments");
+  CommDev dev = comms[0]->dev;
+  dev.rank = -1;
+  dev.world = world;
+  const int n = static_cast<int>(count);
+  int blocks = (n + 511) / 512;
+  if (blocks > 8) blocks = 8;
+  const size_t lo = ll_off, d = off_bytes, po = param_off;
+  if (sgd) return launch_maybe_coop(dev, allreduce_ll_kernel<1>, blocks, 512, static_cast<cudaStream_t>(stream_), "allreduce_sgd_ll", dev, lo, d, po, n, scale, lr, weight_decay, epoch);
+  return launch_maybe_coop(dev, allreduce_ll_kernel<0>, blocks, 512, static_cast<cudaStream_t>(stream_), "allreduce_ll", dev, lo, d, po, n, scale, lr, weight_decay, epoch);
 }
 
 extern "C" int tadnn_allreduce_emulated(tadnn_comm* const* comms, int world, unsigned long long off_bytes, unsigned long long count, int dtype, float scale, int algo, tadnn_stream_t stream) {

@@ -66,7 +66,38 @@ struct DevArgs {
   int ld_aux;
   int group_m;   // m-blocks per rasterisation group
   int n_rotate;  // tile column order starts at this n-block (reduce-scatter push: de-synchronises the ranks' targets)
+  // fused all-gather -> GEMM (see tadnn_gemm_args)
+  uint32_t* sig[8];
+  int n_sig, sig_src, flag_stride;
+  const uint32_t* wait_flags;
+  uint32_t wait_target;
+  int wait_cols_per_src;
 };
+
+__device__ __forceinline__ uint32_t ld_acquire_sys_u32(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void red_release_sys_add_u32(uint32_t* p, uint32_t v) {
+  asm volatile("red.release.sys.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+// Consumer side of the fused all-gather: spin until a peer's epilogue has delivered one (32-row block, source)
+// pair.  Gives up after 20 s (a dead peer must not wedge the GPU; the result is then garbage and the
+// communicator's own failure detection reports the rank).
+__device__ __forceinline__ void wait_flag(const uint32_t* f, uint32_t target) {
+  if (ld_acquire_sys_u32(f) >= target) return;
+  unsigned long long t0;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  uint32_t spins = 0;
+  while (ld_acquire_sys_u32(f) < target) {
+    if ((++spins & 1023u) == 0u) {
+      unsigned long long t1;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+      if (t1 - t0 > 20ull * 1000ull * 1000ull * 1000ull) return;
+    }
+  }
+}
 
 struct PushMaps {
   CUtensorMap m[8];
@@ -159,10 +190,12 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   __shared__ __align__(8) uint64_t tmem_full_bar[2];
   __shared__ __align__(8) uint64_t tmem_empty_bar[2];
   __shared__ uint32_t tmem_base_smem;
+  __shared__ int s_ready;   // fused all-gather: work items whose A blocks the watcher warp has seen arrive
   __shared__ __align__(16) float s_bias[4][64];
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) s_ready = 0;
 
   const int num_m = (p.M + BM - 1) / BM;
   const int num_n = (p.N + BN - 1) / BN;
@@ -197,13 +230,20 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int w = blockIdx.x; w < num_work; w += gridDim.x) {
+      int item = 0;
+      for (int w = blockIdx.x; w < num_work; w += gridDim.x, ++item) {
         const int split = w % splits;
         const int tile = w / splits;
         int m_blk, n_blk;
         decode_tile(tile, num_m, num_n, p.group_m, p.n_rotate, m_blk, n_blk);
         const int kb0 = split * kb_per_split;
         const int kb1 = min(num_kb, kb0 + kb_per_split);
+        if (p.wait_flags != nullptr) {
+          // A is a gathered matrix: the watcher warp has seen every block this work item reads arrive
+          while (*reinterpret_cast<volatile int*>(&s_ready) <= item) {
+          }
+          asm volatile("fence.proxy.async;" ::: "memory");  // the TMA (async proxy) reads below must see those writes
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::kStageBytes;
@@ -275,6 +315,47 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
       }
     }
     __syncwarp();
+  } else if (warp == 3 && p.wait_flags != nullptr) {
+    // ===================== flag watcher (fused all-gather -> GEMM) =====================
+    // One lane per (32-row block, source rank) pair that the next work item reads: all pairs are polled in
+    // parallel (a single thread doing it serially would cost an L2 round trip per pair), then the TMA producer
+    // is released through shared memory.
+    int item = 0;
+    for (int w = blockIdx.x; w < num_work; w += gridDim.x, ++item) {
+      const int split = w % splits;
+      const int tile = w / splits;
+      int m_blk, n_blk;
+      decode_tile(tile, num_m, num_n, p.group_m, p.n_rotate, m_blk, n_blk);
+      const int kb0 = split * kb_per_split;
+      const int kb1 = min(num_kb, kb0 + kb_per_split);
+      if (kb1 > kb0) {
+        if (!A_MN) {
+          // A [M, K] K-major: rows of this m-block, one source per wait_cols_per_src columns of K
+          const int src0 = (kb0 * BK) / p.wait_cols_per_src;
+          const int src1 = (min(p.K, kb1 * BK) - 1) / p.wait_cols_per_src;
+          const int rb_end = (p.M + 31) / 32;
+          const int count = (BM / 32) * (src1 - src0 + 1);
+          for (int i = lane; i < count; i += 32) {
+            const int rb = m_blk * (BM / 32) + (i & 3), src = src0 + (i >> 2);
+            if (rb < rb_end) wait_flag(p.wait_flags + static_cast<size_t>(rb) * p.flag_stride + src, p.wait_target);
+          }
+        } else {
+          // A [K, M] MN-major: 32-row blocks of the k-range, sources of this m-block's two 64-column chunks
+          const int rb0 = kb0 * (BK / 32);
+          const int rb1 = min((p.K + 31) / 32, kb1 * (BK / 32));
+          const int count = (rb1 - rb0) * (BM / 64);
+          for (int i = lane; i < count; i += 32) {
+            const int rb = rb0 + i / (BM / 64), col = m_blk * BM + (i % (BM / 64)) * 64;
+            if (col < p.M) wait_flag(p.wait_flags + static_cast<size_t>(rb) * p.flag_stride + col / p.wait_cols_per_src, p.wait_target);
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) {
+        __threadfence_block();
+        *reinterpret_cast<volatile int*>(&s_ready) = item + 1;
+      }
+    }
   } else if (warp >= 4) {
     // ===================== epilogue =====================
     const int wg = warp & 3;  // TMEM lane quarter this warp may touch
@@ -296,6 +377,7 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         const int row0 = m_blk * BM + wg * 32;
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(wg * 32) << 16) +
                                static_cast<uint32_t>(acc * BN);
+        int slabs_done = 0;
 #pragma unroll 1
         for (int c = 0; c < BN / 64; ++c) {
           const int col0 = n_blk * BN + c * 64;
@@ -372,9 +454,21 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
             asm volatile("cp.async.bulk.commit_group;" ::: "memory");
           }
           buf ^= 1;
+          ++slabs_done;
         }
         tc_fence_before_sync();
         mbar_arrive(&tmem_empty_bar[acc]);
+        if (p.n_sig > 0 && row0 < p.M) {
+          // fused all-gather, producer side: every slab of this 32-row block has been handed to the TMA unit;
+          // once the stores have completed, tell each target how many slabs of ours it now holds
+          if (lane == 0) {
+            asm volatile("cp.async.bulk.wait_group 0;" ::: "memory");
+            __threadfence_system();
+            for (int q = 0; q < p.n_sig; ++q)
+              red_release_sys_add_u32(p.sig[q] + static_cast<size_t>(row0 >> 5) * p.flag_stride + p.sig_src, static_cast<uint32_t>(slabs_done));
+          }
+          __syncwarp();
+        }
         if (++acc == 2) {
           acc = 0;
           acc_phase ^= 1;
@@ -532,7 +626,7 @@ extern "C" int tadnn_gemm_bf16(const tadnn_gemm_args* a, tadnn_stream_t stream_)
   // Large plain problems (K-major operands, bf16 output, no collective / split-K epilogue, tile width not
   // forced) go to the 2-CTA kernel: cta_group::2 pairs, 256x256 tiles, 1/3 less L2->shared traffic.
   if (!a->a_mn_major && !a->b_mn_major && !a->c_fp32 && !a->accumulate && a->split_k <= 1 && a->n_push == 0 &&
-      a->rs_width == 0 && a->aux_tanh_out == nullptr && a->tile_n == 0 && a->M >= 512 && a->N >= 256 && a->K >= 256 &&
+      a->rs_width == 0 && a->aux_tanh_out == nullptr && a->n_sig == 0 && a->wait_flags == nullptr && a->tile_n == 0 && a->M >= 512 && a->N >= 256 && a->K >= 256 &&
       a->lda % 8 == 0 && a->ldb % 8 == 0 && a->ldc % 8 == 0 &&
       ((reinterpret_cast<uintptr_t>(a->A) | reinterpret_cast<uintptr_t>(a->B) | reinterpret_cast<uintptr_t>(a->C)) & 15) == 0)
     return tadnn_gemm_bf16_2cta(a->A, a->lda, a->B, a->ldb, a->C, a->ldc, a->M, a->N, a->K, a->bias, a->act, a->alpha, stream_);
@@ -573,6 +667,16 @@ extern "C" int tadnn_gemm_bf16(const tadnn_gemm_args* a, tadnn_stream_t stream_)
   }
   d.aux = static_cast<const __nv_bfloat16*>(a->aux_tanh_out);
   d.ld_aux = a->ld_aux;
+  TADNN_REQUIRE(a->n_sig >= 0 && a->n_sig <= 8, "tadnn_gemm_bf16: n_sig=%d out of range", a->n_sig);
+  d.n_sig = a->n_sig;
+  for (int i = 0; i < a->n_sig; ++i) d.sig[i] = static_cast<uint32_t*>(a->sig_flags[i]);
+  d.sig_src = a->sig_src;
+  d.flag_stride = a->flag_stride;
+  d.wait_flags = static_cast<const uint32_t*>(a->wait_flags);
+  d.wait_target = a->wait_target;
+  d.wait_cols_per_src = a->wait_cols_per_src;
+  TADNN_REQUIRE(d.wait_flags == nullptr || (d.wait_cols_per_src > 0 && d.wait_cols_per_src % 64 == 0 && d.flag_stride > 0),
+                "tadnn_gemm_bf16: wait_flags needs wait_cols_per_src (a multiple of 64) and flag_stride");
   if (a->rs_width > 0) {
     TADNN_REQUIRE(!a->c_fp32 && !atomic, "tadnn_gemm_bf16: rs_width needs a bf16, non-accumulating output");
     TADNN_REQUIRE(a->rs_width % 64 == 0 && a->n_push * a->rs_width >= a->N && a->push_ldc % 8 == 0,
@@ -586,6 +690,7 @@ extern "C" int tadnn_gemm_bf16(const tadnn_gemm_args* a, tadnn_stream_t stream_)
       ok = (a->push_ldc % 8 == 0) && ((reinterpret_cast<uintptr_t>(a->push[i]) & 15) == 0) && (a->push_col_offset % 8 == 0);
     d.tma_store = ok ? 1 : 0;
   }
+  TADNN_REQUIRE(d.n_sig == 0 || (d.tma_store && a->rs_width == 0 && d.flag_stride > 0), "tadnn_gemm_bf16: sig_flags need the bf16 TMA-store epilogue (all-gather push form)");
   TADNN_REQUIRE(d.aux == nullptr || (d.tma_store && !a->a_mn_major && a->b_mn_major), "tadnn_gemm_bf16: aux_tanh_out needs the bf16 TMA-store epilogue and the dgrad operand layout (a K-major, b MN-major)");
 
   int bn = a->tile_n;

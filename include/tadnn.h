@@ -80,6 +80,21 @@ typedef struct tadnn_gemm_args {
    * staging, rows padded to a multiple of 32; slab s = (row/32)*(rs_width/64) + col/64, contents in
    * the SWIZZLE_128B order of the staging tile) -- tadnn_reduce_slots(slab_major=1) reads it. */
   int rs_slab_major;
+  /* Fused all-gather -> GEMM (K13: the backward of the model-parallel linears, nodemodule.lua:56-68,107-119,
+   * 165-167).  PRODUCER side (n_push > 0, bf16 TMA-store epilogue): after the 64-column slabs of a 32-row block
+   * have landed in every push target, the kernel adds their number to flag word
+   * sig_flags[q][(row/32)*flag_stride + sig_src] of each target q (release, system scope).  CONSUMER side: the A
+   * operand is such a gathered matrix whose column block c belongs to source rank c / wait_cols_per_src; the
+   * TMA producer warp spins (acquire, system scope) until wait_flags[(row/32)*flag_stride + src] >= wait_target
+   * before it loads a tile of those rows from that source.  No separate all-gather kernel and no rank barrier:
+   * tiles are consumed as they arrive.  Flags only ever grow; the caller keeps the running target. */
+  void* sig_flags[8];
+  int n_sig;
+  int sig_src;
+  int flag_stride;
+  const void* wait_flags;
+  unsigned int wait_target;
+  int wait_cols_per_src;
 } tadnn_gemm_args;
 
 int tadnn_gemm_bf16(const tadnn_gemm_args* args, tadnn_stream_t stream);
@@ -106,6 +121,7 @@ int tadnn_gemm_bf16_2cta(const void* A, int lda, const void* B, int ldb, void* C
 #define TADNN_COMM_CHANNELS 8
 #define TADNN_COMM_MAX_BLOCKS 512
 #define TADNN_IPC_HANDLE_BYTES 64
+#define TADNN_LL_MAX_FLOATS 16384 /* largest message of the low-latency all-reduce (64 KB) */
 
 typedef struct tadnn_comm tadnn_comm;
 
@@ -175,6 +191,21 @@ int tadnn_allreduce_sgd(tadnn_comm* c, unsigned long long grad_off_bytes, unsign
 int tadnn_allreduce_sgd_emulated(tadnn_comm* const* comms, int world, unsigned long long grad_off_bytes,
                                  unsigned long long param_off_bytes, unsigned long long count, float scale,
                                  float lr, float weight_decay, int algo, tadnn_stream_t stream);
+
+/* Low-latency all-reduce for small fp32 messages (<= TADNN_LL_MAX_FLOATS): every rank writes {value, epoch}
+ * pairs into its slot of every rank's staging area and sums its own staging area as the pairs arrive: one
+ * NVLink one-way trip, no barrier.  ll_off: a zero-initialised staging area of
+ * 2 * world * TADNN_LL_MAX_FLOATS * 8 bytes at the same heap offset on every rank; epoch: non-zero, +1 on every
+ * call that uses this staging area (all ranks make the same calls in the same order).  sgd != 0: the fused form
+ * of tadnn_allreduce_sgd (param_off = parameters, off = gradients, cleared).  This is the path the reference's
+ * own workload lives on: one sample per step, 40-byte to 8 KB messages (nodemodule.lua:52,103). */
+int tadnn_allreduce_ll(tadnn_comm* c, unsigned long long ll_off, unsigned long long off_bytes,
+                       unsigned long long param_off, unsigned long long count, float scale, int sgd, float lr,
+                       float weight_decay, unsigned int epoch, tadnn_stream_t stream);
+int tadnn_allreduce_ll_emulated(tadnn_comm* const* comms, int world, unsigned long long ll_off,
+                                unsigned long long off_bytes, unsigned long long param_off, unsigned long long count,
+                                float scale, int sgd, float lr, float weight_decay, unsigned int epoch,
+                                tadnn_stream_t stream);
 
 /* K4 broadcast of heap[off .. off+bytes) from `root` to every rank (push).  Replaces
  * mpinn.synchronizeParameters (datamodule.lua:33). */
@@ -362,6 +393,10 @@ int tadnn_head_forward_noalloc(const tadnn_head_args* a, tadnn_stream_t stream);
  * (datamodule.lua:142) for batched training on the flat buffer. */
 int tadnn_sgd_step(float* p, float* g, long long n, float lr, float weight_decay, int zero_grad,
                    tadnn_stream_t stream);
+/* SGD step (as tadnn_sgd_step, gradients left untouched) that also writes the bf16 copy of the updated weights
+ * the GEMMs read, so that no forward pass has to re-cast them. */
+int tadnn_sgd_step_shadow(float* p, const float* g, void* shadow_bf16, long long n, float lr, float weight_decay,
+                          tadnn_stream_t stream);
 int tadnn_cast_f32_bf16(const float* x, void* y, long long n, tadnn_stream_t stream);
 /* 2-D form with row pitches (elements): lets a layer of any width become a TMA operand (pitch rounded up to 8). */
 int tadnn_cast_f32_bf16_2d(const float* x, long long ldx, void* y, long long ldy, long long rows, int cols,

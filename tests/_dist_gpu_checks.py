@@ -61,6 +61,17 @@ def main():
                 got_all = gather_all(view.clone())
                 if any(not torch.equal(got_all[0], g) for g in got_all):
                     fails.append(f"allreduce n={n} {dtype} algo={algo}: ranks disagree bitwise")
+    # low-latency path (algo 4 = {value, epoch} pairs, no barrier): many calls in a row, varying sizes
+    for it in range(60):
+        n = (1, 7, 640, 4864, 16384)[it % 5]
+        view = big[:n]
+        x = torch.randn(n, device=dev)
+        view.copy_(x)
+        ref = torch.stack(gather_all(x)).sum(0) / P
+        ctx.allreduce_(view, scale=1.0 / P, algo=4)
+        if it % 7 == 0:
+            torch.cuda.synchronize()
+        expect(f"allreduce LL n={n} it={it}", view, ref, 1e-5)
     # repeated launches back-to-back (flag reuse without host sync)
     view = big[:50000]
     x = torch.randn(50000, device=dev)
@@ -164,7 +175,9 @@ def main():
 
     # ---- gradient all-reduce fused with the SGD step: every algo, vs the two-pass statement
     for n in (64, 4800, 114944, (1 << 20) + 64):
-        for algo in ((1, 2, 3) if ctx.has_multicast else (1, 2)):
+        for algo in ((1, 2, 3, 4) if ctx.has_multicast else (1, 2, 4)):
+            if algo == 4 and n > 16384:
+                continue
             if algo == 1 and n > (1 << 18):
                 continue
             reg3 = big[:2 * n]

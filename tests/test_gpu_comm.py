@@ -92,6 +92,56 @@ def test_allreduce_sgd_emulated_single_launch(world, algo):
             lib.tadnn_comm_destroy(C.c_void_p(comms[r]))
 
 
+@pytest.mark.parametrize("world", [2, 8])
+def test_allreduce_ll_emulated_single_launch(world):
+    """Low-latency all-reduce ({value, epoch} pairs, no barrier), plain and fused-SGD forms, several epochs in a
+    row (both parities of the double-buffered staging area), all ranks in one cooperative launch."""
+    from tadnn import _native
+    lib = _native.lib()
+    LL = 16384
+    ll_bytes = 2 * world * LL * 8
+    heap = 8 << 20
+    comms = (C.c_void_p * world)()
+    _native.check(lib.tadnn_comm_create_local(world, C.c_ulonglong(heap), comms), "create_local")
+    try:
+        views = [_heap_view(lib, C.c_void_p(comms[r]), heap, comms) for r in range(world)]
+        for v in views:
+            v[:ll_bytes].zero_()
+        f32 = [v[ll_bytes:].view(torch.float32) for v in views]
+        epoch = 0
+        for n in (1, 10, 2500, LL):
+            xs = [torch.randn(n, device="cuda") for _ in range(world)]
+            for v, x in zip(f32, xs):
+                v[:n].copy_(x)
+            torch.cuda.synchronize()
+            epoch += 1
+            _native.check(lib.tadnn_allreduce_ll_emulated(comms, world, C.c_ulonglong(0), C.c_ulonglong(ll_bytes), C.c_ulonglong(0),
+                                                          C.c_ulonglong(n), C.c_float(1.0 / world), 0, C.c_float(0), C.c_float(0),
+                                                          C.c_uint(epoch), C.c_void_p(_native.stream_ptr())), "ll")
+            torch.cuda.synchronize()
+            ref = torch.stack(xs).sum(0) / world
+            for v in f32:
+                assert (v[:n] - ref).abs().max().item() < 1e-5 and torch.equal(v[:n], f32[0][:n])
+        n = 4864
+        p0 = torch.randn(n, device="cuda")
+        gs = [torch.randn(n, device="cuda") for _ in range(world)]
+        for v, g in zip(f32, gs):
+            v[:n].copy_(g)
+            v[LL:LL + n].copy_(p0)
+        torch.cuda.synchronize()
+        epoch += 1
+        _native.check(lib.tadnn_allreduce_ll_emulated(comms, world, C.c_ulonglong(0), C.c_ulonglong(ll_bytes), C.c_ulonglong(ll_bytes + 4 * LL),
+                                                      C.c_ulonglong(n), C.c_float(1.0 / world), 1, C.c_float(0.1), C.c_float(0.01),
+                                                      C.c_uint(epoch), C.c_void_p(_native.stream_ptr())), "ll sgd")
+        torch.cuda.synchronize()
+        ref = p0 - 0.1 * (torch.stack(gs).sum(0) / world + 0.01 * p0)
+        for v in f32:
+            assert (v[LL:LL + n] - ref).abs().max().item() < 1e-5 and float(v[:n].abs().sum()) == 0.0
+    finally:
+        for r in range(world):
+            lib.tadnn_comm_destroy(C.c_void_p(comms[r]))
+
+
 def test_world1_context_and_flat_buffer_sync():
     """parallelize() on a single GPU: flat symmetric buffer, hooks fire, sync is a no-op average."""
     import tadnn

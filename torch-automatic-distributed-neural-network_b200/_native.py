@@ -32,6 +32,8 @@ class GemmArgs(C.Structure):
         ("n_push", C.c_int), ("push", C.c_void_p * 8),
         ("push_ldc", C.c_int), ("push_col_offset", C.c_int),
         ("tile_n", C.c_int), ("rs_width", C.c_int), ("aux_tanh_out", C.c_void_p), ("ld_aux", C.c_int), ("n_rotate", C.c_int), ("rs_slab_major", C.c_int),
+        ("sig_flags", C.c_void_p * 8), ("n_sig", C.c_int), ("sig_src", C.c_int), ("flag_stride", C.c_int),
+        ("wait_flags", C.c_void_p), ("wait_target", C.c_uint), ("wait_cols_per_src", C.c_int),
     ]
 
 

@@ -21,13 +21,17 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False,
               act: str | None = None, alpha: float = 1.0, accumulate: bool = False,
               split_k: int = 0, push=None, push_col_offset: int = 0, push_ldc: int = 0,
               tile_n: int = 0, rs_width: int = 0, aux_tanh_out: torch.Tensor | None = None,
-              n_rotate: int = 0, rs_slab_major: bool = False, stream=None) -> torch.Tensor:
+              n_rotate: int = 0, rs_slab_major: bool = False, sig_flags=None, sig_src: int = 0,
+              flag_stride: int = 0, wait_flags: int = 0, wait_target: int = 0, wait_cols_per_src: int = 0,
+              stream=None) -> torch.Tensor:
     """out[M,N] = act(alpha * A·Bᵀ + bias).
 
     a: [M,K] (or [K,M] if a_mn_major), b: [N,K] (or [K,N] if b_mn_major); bf16, last dim
     contiguous, row pitch a multiple of 8.  ``push`` is an optional list of raw device
     pointers (peer-mapped buffers) that receive a copy of every output tile at column
-    offset ``push_col_offset`` (fused all-gather).
+    offset ``push_col_offset`` (fused all-gather).  ``sig_flags`` (one raw pointer per target, own rank
+    included if it consumes too) makes that push self-announcing and ``wait_flags``/``wait_target``/
+    ``wait_cols_per_src`` make this GEMM the consumer of such a gathered A operand (K13, include/tadnn.h).
     """
     assert a.is_cuda and b.is_cuda and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
     assert a.dim() == 2 and b.dim() == 2 and a.stride(1) == 1 and b.stride(1) == 1
@@ -66,6 +70,12 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False,
     args.rs_width = int(rs_width)
     args.n_rotate = int(n_rotate)
     args.rs_slab_major = int(rs_slab_major)
+    sig = list(sig_flags or [])
+    args.n_sig = len(sig)
+    for i, ptr in enumerate(sig):
+        args.sig_flags[i] = int(ptr)
+    args.sig_src, args.flag_stride = int(sig_src), int(flag_stride)
+    args.wait_flags, args.wait_target, args.wait_cols_per_src = int(wait_flags), int(wait_target), int(wait_cols_per_src)
     if aux_tanh_out is not None:
         assert aux_tanh_out.dtype == torch.bfloat16 and aux_tanh_out.stride(1) == 1 and aux_tanh_out.shape == (M, N)
         args.aux_tanh_out, args.ld_aux = aux_tanh_out.data_ptr(), aux_tanh_out.stride(0)

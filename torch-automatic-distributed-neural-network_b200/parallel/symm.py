@@ -39,6 +39,7 @@ CH_DEFAULT = 0   # mpi.allreduceTensor & friends on the compute stream
 CH_DP = 1        # data-parallel gradient/parameter sync on the comm stream
 CH_TP = 2        # model-parallel layer collectives
 CH_BARRIER = 3
+LL_MAX_FLOATS = 16384  # TADNN_LL_MAX_FLOATS: largest message of the low-latency all-reduce
 
 
 class CommTimeout(_native.NativeError):
@@ -127,6 +128,15 @@ class SymmContext:
         self._live = {}
         self._staging_bytes = staging_mb << 20
         self._staging_off = self.alloc(self._staging_bytes)
+        # low-latency all-reduce staging ({value, epoch} pairs), one area per channel that uses it; zeroed before the
+        # barrier below, so no peer can write into it earlier
+        self._ll = {}
+        if self.world > 1:
+            ll_bytes = 2 * self.world * LL_MAX_FLOATS * 8
+            for ch in (CH_DEFAULT, CH_DP, CH_TP):
+                off = self.alloc(ll_bytes)
+                self._heap_u8[off:off + ll_bytes].zero_()
+                self._ll[ch] = [off, 0]
         if self.world > 1:
             torch.cuda.synchronize()
             dist.barrier()  # pads are zeroed and mapped everywhere before the first kernel
@@ -337,9 +347,27 @@ class SymmContext:
         _native.check(_native.lib().tadnn_barrier(self.handle, C.c_int(channel),
                                                   C.c_void_p(_native.stream_ptr(stream))), "tadnn_barrier")
 
+    def _ll_ok(self, count: int, dtype, algo: int, channel: int) -> bool:
+        return (algo in (0, 4) and dtype == torch.float32 and 0 < count <= LL_MAX_FLOATS and channel in self._ll
+                and os.environ.get("TADNN_COMM_LL", "1") not in ("0", "false"))
+
+    def _ll_launch(self, off: int, param_off: int, count: int, scale: float, sgd: bool, lr: float, wd: float, channel: int, stream):
+        ent = self._ll[channel]
+        ent[1] = ent[1] % 0xFFFFFFF0 + 1   # non-zero, same sequence on every rank
+        _native.check(_native.lib().tadnn_allreduce_ll(
+            self.handle, C.c_ulonglong(ent[0]), C.c_ulonglong(off), C.c_ulonglong(param_off), C.c_ulonglong(count),
+            C.c_float(scale), C.c_int(int(sgd)), C.c_float(lr), C.c_float(wd), C.c_uint(ent[1]),
+            C.c_void_p(_native.stream_ptr(stream))), "tadnn_allreduce_ll")
+
     def allreduce_offset(self, off: int, count: int, dtype: torch.dtype, scale: float = 1.0,
                          algo: int = 0, max_blocks: int = 0, channel: int = CH_DEFAULT, stream=None):
+        """``algo``: 0 auto (low-latency pairs up to 64 KB of fp32, then one-shot / NVLS / two-shot by size),
+        1 one-shot, 2 two-shot, 3 NVLS, 4 low-latency."""
         self.check()
+        if self._ll_ok(count, dtype, algo, channel):
+            return self._ll_launch(off, 0, count, scale, False, 0.0, 0.0, channel, stream)
+        if algo == 4:
+            raise ValueError("low-latency all-reduce: fp32 messages of at most 64 KB on channels 0-2 only")
         _native.check(_native.lib().tadnn_allreduce(
             self.handle, C.c_ulonglong(off), C.c_ulonglong(count), C.c_int(_DT[dtype]),
             C.c_float(scale), C.c_int(algo), C.c_int(max_blocks), C.c_int(channel),
@@ -349,6 +377,8 @@ class SymmContext:
                              weight_decay: float = 0.0, algo: int = 0, channel: int = CH_DP, stream=None):
         """Gradient all-reduce-average fused with the SGD update and the gradient clear (fp32; csrc/comm.cu)."""
         self.check()
+        if self._ll_ok(count, torch.float32, algo, channel):
+            return self._ll_launch(grad_off, param_off, count, scale, True, lr, weight_decay, channel, stream)
         _native.check(_native.lib().tadnn_allreduce_sgd(
             self.handle, C.c_ulonglong(grad_off), C.c_ulonglong(param_off), C.c_ulonglong(count), C.c_float(scale),
             C.c_float(lr), C.c_float(weight_decay), C.c_int(algo), C.c_int(0), C.c_int(channel),

@@ -72,6 +72,27 @@ class _Plan:
         self.small = ctx.empty((B * allo_pad,), torch.float32)        # small-layer partial sums (all-reduced in place)
         self._ctx, self._maxo = ctx, maxo
         self._part2 = None
+        # fused all-gather -> GEMM backward (K13): three gathered-gradient buffers (layer l uses l % 3: a peer may
+        # already push layer l-1's slices while this rank still reads layer l+1's) and, per buffer, one
+        # arrival counter per (32-row block, source rank); counters only grow, `gtarget` is their running goal
+        self.g3_off = None
+        self.gflag_off = None
+        self.gtarget = [0, 0, 0]
+        self._B, self._allo_pad = B, allo_pad
+
+    def gather_buffers(self):
+        if self.g3_off is None:
+            ctx, P = self._ctx, self._ctx.world
+            self.g3_off = [ctx.alloc(2 * self._B * self._allo_pad) for _ in range(3)]
+            nflag = (self._B + 31) // 32 * P
+            self.gflag_off = [ctx.alloc(4 * nflag) for _ in range(3)]
+            for off in self.gflag_off:
+                ctx.tensor(off, (nflag,), torch.float32).zero_()
+            torch.cuda.synchronize()
+            if P > 1:
+                import torch.distributed as dist
+                dist.barrier()  # nobody signals into counters that are not zeroed yet
+        return self.g3_off, self.gflag_off
 
     def part_off(self, parity: int) -> int:
         """NVLS mode: [B, o] bf16 partial-product buffers, double-buffered over layers (a peer may still be
@@ -114,7 +135,7 @@ class _Fn(torch.autograd.Function):
             W, b = params[2 * l], params[2 * l + 1]
             o = mod.sizes[l + 1]
             last = l == L - 1
-            wb = _cast_bf16(W)
+            wb = mod._weight_bf16(l, W)
             wbs.append(wb)
             mark(f"l{l}.cast")
             if o % (64 * P) == 0 and use_nvls:
@@ -208,6 +229,11 @@ class _Fn(torch.autograd.Function):
         cur = 0
         side = mod._side_stream()
         main = torch.cuda.current_stream()
+        import os
+        fused_gather = P > 1 and os.environ.get("TADNN_MP_FUSED_GATHER", "1") not in ("0", "false")
+        if fused_gather:
+            g3, gfl = plan.gather_buffers()
+        wait = None  # (flag pointer, target, columns per source) when g_full arrives through pushing GEMM epilogues
         for l in range(L - 1, -1, -1):
             o, i_sh = mod.sizes[l + 1], mod.sizes[l] // P
             pitch = (o + 7) // 8 * 8
@@ -215,14 +241,32 @@ class _Fn(torch.autograd.Function):
             a = acts[l]
             need_dx = l > 0 or ctx.needs_input_grad[1]
             gathered = None
+            wkw = {} if wait is None else dict(wait_flags=wait[0], wait_target=wait[1], wait_cols_per_src=wait[2], flag_stride=P)
+            nxt_wait, nxt_full = None, None
             if need_dx:
                 # g'_r [B, i/P] = (g · W_r) (⊙ tanh' of the layer input if that input is a tanh output)
                 tn = 256 if i_sh >= 256 else 0  # measured: 256-wide tiles beat 128-wide ones even at 1.7 waves
                 if _smalln_ok(o, a, "dgrad"):
                     gr = _smalln.linear_smalln_dgrad(gv, wbs[l], aux_tanh_out=a if l > 0 else None)
+                elif fused_gather and l > 0 and i_sh % 64 == 0:
+                    # K13: this GEMM's epilogue pushes every finished 32x64 slab of its slice into the gathered buffer
+                    # of ALL ranks and bumps their arrival counters; the GEMMs of layer l-1 consume the blocks as they
+                    # land (flag waits in their TMA producer).  No all-gather kernel, no rank barrier.
+                    d = (l - 1) % 3
+                    i_full = i_sh * P
+                    own = sc.tensor(g3[d], (B, i_full), torch.bfloat16)
+                    plan.gtarget[d] += i_sh // 64
+                    gemm_bf16(gv, wbs[l], b_mn_major=True, aux_tanh_out=a, tile_n=tn,
+                              out=own[:, r * i_sh:(r + 1) * i_sh],
+                              push=[sc.heap_ptrs[q] + g3[d] for q in range(P) if q != r], push_ldc=i_full, push_col_offset=r * i_sh,
+                              sig_flags=[sc.heap_ptrs[q] + gfl[d] for q in range(P)], sig_src=r,
+                              **(wkw or dict(flag_stride=P)))
+                    gr = None
+                    nxt_full = own
+                    nxt_wait = (sc.heap_ptrs[r] + gfl[d], plan.gtarget[d], i_sh)
                 else:
-                    gr = gemm_bf16(gv, wbs[l], b_mn_major=True, aux_tanh_out=a if l > 0 else None, tile_n=tn)
-                if P > 1:
+                    gr = gemm_bf16(gv, wbs[l], b_mn_major=True, aux_tanh_out=a if l > 0 else None, tile_n=tn, **wkw)
+                if P > 1 and gr is not None:
                     # all-gather of the slice gradients on a side stream, into the OTHER buffer, so that it
                     # overlaps this layer's wgrad GEMM (the gather kernel needs few registers and co-resides)
                     side.wait_event(main.record_event())
@@ -236,18 +280,21 @@ class _Fn(torch.autograd.Function):
             else:
                 tile_n = 256 if i_sh > 128 else (128 if i_sh > 64 else 64)
                 dW = gemm_bf16(gv, a, a_mn_major=True, b_mn_major=True, out_dtype=torch.float32,
-                               split_k=auto_split_k(o, i_sh, B, tile_n), tile_n=tile_n)
+                               split_k=auto_split_k(o, i_sh, B, tile_n), tile_n=tile_n, **wkw)
                 db = torch.zeros(o, device=dev, dtype=torch.float32)
-                colsum_bf16(gv, db)
+                colsum_bf16(gv, db)  # (runs after the wgrad GEMM, whose watcher has seen every block of g arrive)
             grads[2 * l], grads[2 * l + 1] = dW, db
             if not need_dx:
                 break
-            if P > 1:
+            if nxt_full is not None:
+                g_full, wait = nxt_full, nxt_wait
+            elif P > 1:
                 main.wait_event(gathered)
                 cur ^= 1
                 g_full = sc.tensor(offs[cur], (B, i_sh * P), torch.bfloat16)
+                wait = None
             else:
-                g_full = gr
+                g_full, wait = gr, None
             if l == 0:
                 gx = g_full.to(gy.dtype).clone()
         return (None, gx, *grads)
@@ -348,6 +395,42 @@ class FusedMPMLP(torch.nn.Module):
         if p is None:
             p = self._plans[B] = _Plan(self._ctx(), B, self.sizes)
         return p
+
+    def _weight_bf16(self, l: int, W: torch.Tensor) -> torch.Tensor:
+        """bf16 operand copy of layer l's weight: kept across steps and refreshed by ``sgd_step`` in the same pass
+        as the update; re-cast only when the fp32 master was changed behind its back (tensor version bump)."""
+        cache = self.__dict__.setdefault("_wb_cache", {})
+        ent = cache.get(l)
+        if ent is not None and ent[1] == W._version and ent[2] == W.data_ptr():
+            return ent[0]
+        wb = _cast_bf16(W)
+        cache[l] = (wb, W._version, W.data_ptr())
+        return wb
+
+    @torch.no_grad()
+    def sgd_step(self, lr: float, weight_decay: float = 0.0) -> None:
+        """In-place SGD on every weight/bias from ``.grad`` (then dropped), fp32 master and bf16 operand copy in one
+        kernel per weight (csrc/cnn.cu: tadnn_sgd_step_shadow).  The reference's in-place step: datamodule.lua:142."""
+        lib = _native.lib()
+        st = C.c_void_p(_native.stream_ptr())
+        cache = self.__dict__.setdefault("_wb_cache", {})
+        for l, (W, b) in enumerate(zip(self.weights, self.biases)):
+            if W.grad is not None:
+                g = W.grad if W.grad.is_contiguous() else W.grad.contiguous()
+                ent = cache.get(l)
+                fresh = ent is not None and ent[1] == W._version and ent[2] == W.data_ptr()
+                if W.is_cuda and W.numel() % 4 == 0 and W.is_contiguous() and g.dtype == torch.float32:
+                    wb = ent[0] if fresh else torch.empty(W.shape, device=W.device, dtype=torch.bfloat16)
+                    _native.check(lib.tadnn_sgd_step_shadow(C.c_void_p(W.data_ptr()), C.c_void_p(g.data_ptr()), C.c_void_p(wb.data_ptr()),
+                                                            C.c_longlong(W.numel()), C.c_float(lr), C.c_float(weight_decay), st),
+                                  "tadnn_sgd_step_shadow")
+                    cache[l] = (wb, W._version, W.data_ptr())
+                else:
+                    W.add_(g + weight_decay * W if weight_decay else g, alpha=-lr)
+                W.grad = None
+            if b.grad is not None:
+                b.add_(b.grad + weight_decay * b if weight_decay else b.grad, alpha=-lr)
+                b.grad = None
 
     def _params(self):
         out = []

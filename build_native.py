@@ -94,7 +94,9 @@ def dump_sass() -> None:
     instantiations (24 MB of listing); only two representative ones are kept in the tree."""
     out_dir = os.path.join(ROOT, "profiles", "sass")
     os.makedirs(out_dir, exist_ok=True)
-    keep_gemm = ("ILb0ELb0ELi256ELb0E", "ILb0ELb1ELi256ELb1E")  # forward (TN) and dgrad with fused tanh'
+    # forward (TN; also the reduce-scatter / all-gather push epilogues, which are run-time branches of it), dgrad with
+    # fused tanh' (the K13 producer), wgrad (MN-major operands; the K13 consumer with the flag-watcher warp)
+    keep_gemm = ("ILb0ELb0ELi256ELb0E", "ILb0ELb1ELi256ELb1E", "ILb1ELb1ELi256ELb0E")
     for f in sorted(os.listdir(OBJ)):
         if not f.endswith(".o"):
             continue

@@ -461,6 +461,7 @@ struct HeadArgs {
   int B, D, H, NC;
   float p;                   // dropout probability (0 in eval)
   uint32_t seed;
+  const uint32_t* seed_dev;  // optional device word mixed into the seed (lets a captured CUDA graph draw a new mask per replay)
   float* hbuf;               // [B, H] fp32 post-ReLU hidden (saved for backward)
   float* logp;               // [B, NC] fp32
   float* loss_partial;       // scratch: [gridDim.x] per-block partial sums  (+1 counter word after it)
@@ -507,6 +508,7 @@ __device__ __forceinline__ void stage8(float* dst, int n, int t, Load load) {
 __global__ void __launch_bounds__(256) head_fwd_kernel(HeadArgs a) {
   extern __shared__ __align__(16) float sm[];
   const int HP = head_hp(a.H);
+  const uint32_t seed = a.seed ^ (a.seed_dev != nullptr ? __ldg(a.seed_dev) * 0x9E3779B9u : 0u);
   float* w1t = sm;                          // [64][HP]   w1t[i*HP + j] = w1[j][i]
   float* w2s = w1t + kHeadD * HP;           // [NC][HP]
   float* b1 = w2s + a.NC * HP;              // [HP]
@@ -544,7 +546,7 @@ __global__ void __launch_bounds__(256) head_fwd_kernel(HeadArgs a) {
 #pragma unroll
       for (int u = 0; u < 8; ++u) {
         const int i = t + u * 256, s = i >> 6, d = i & 63;
-        sdt[d * kHeadS + s] = v[u] * dropout_scale(a.seed, static_cast<uint32_t>(base + s) * a.D + d, a.p);
+        sdt[d * kHeadS + s] = v[u] * dropout_scale(seed, static_cast<uint32_t>(base + s) * a.D + d, a.p);
       }
     }
     __syncthreads();
@@ -636,6 +638,7 @@ __global__ void __launch_bounds__(256) head_fwd_kernel(HeadArgs a) {
 __global__ void __launch_bounds__(256) head_bwd_kernel(HeadArgs a) {
   extern __shared__ __align__(16) float sm[];
   const int HP = head_hp(a.H);
+  const uint32_t seed = a.seed ^ (a.seed_dev != nullptr ? __ldg(a.seed_dev) * 0x9E3779B9u : 0u);
   float* w1s = sm;                          // [HP][64]  as stored (row j), zero padded
   float* w2s = w1s + HP * kHeadD;           // [NC][HP]
   float* sd = w2s + a.NC * HP;              // [32][64]  dropped input
@@ -692,7 +695,7 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(HeadArgs a) {
 #pragma unroll
     for (int u = 0; u < 8; ++u) {
       const int i = t + u * 256, s = i >> 6, d = i & 63;
-      sd[i] *= dropout_scale(a.seed, static_cast<uint32_t>(base + s) * a.D + d, a.p);
+      sd[i] *= dropout_scale(seed, static_cast<uint32_t>(base + s) * a.D + d, a.p);
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
@@ -745,8 +748,8 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(HeadArgs a) {
           const long long s = base + 4 * sg + x;
           if (s < a.B) {
             const uint32_t e = static_cast<uint32_t>(s) * a.D + 2 * ip;
-            const float g0 = acc[x][0] * dropout_scale(a.seed, e, a.p);
-            const float g1 = (2 * ip + 1 < a.D) ? acc[x][1] * dropout_scale(a.seed, e + 1, a.p) : 0.f;
+            const float g0 = acc[x][0] * dropout_scale(seed, e, a.p);
+            const float g1 = (2 * ip + 1 < a.D) ? acc[x][1] * dropout_scale(seed, e + 1, a.p) : 0.f;
             const uint32_t gp = pack_bf16x2(g0, g1);
             if ((a.D & 1) == 0) {
               if (a.dp2 != nullptr) *reinterpret_cast<uint32_t*>(a.dp2 + s * a.D + 2 * ip) = gp;
@@ -1069,6 +1072,7 @@ static HeadArgs to_dev(const tadnn_head_args* h) {
   a.target = h->target;
   a.B = h->B; a.D = h->D; a.H = h->H; a.NC = h->NC;
   a.p = h->dropout_p; a.seed = h->seed;
+  a.seed_dev = h->seed_dev;
   a.hbuf = h->hidden; a.logp = h->logp; a.loss = h->loss;
   a.gw1 = h->gw1; a.gb1 = h->gb1; a.gw2 = h->gw2; a.gb2 = h->gb2;
   a.dp2 = static_cast<__nv_bfloat16*>(h->dp2);

@@ -87,7 +87,10 @@ def main():
         log(f"trained {steps} steps of {mb} samples, last loss {last:.4f}")
     else:
         # the reference's per-sample loop (datamodule.lua:117-184), CrossEntropyCriterion on log-probs
-        seq = model.to_sequential()
+        # On a GPU the model itself goes to the trainer: StochasticGradient then runs every sample as one replay of
+        # a captured CUDA graph of the fused tadnn step (CifarCNN.native_sample_step).  On the CPU the same network
+        # as a Sequential of stock layers.
+        seq = model if use_gpu else model.to_sequential()
         seq._tadnn_sync = getattr(model, "_tadnn_sync", None)
         trainer = nn.StochasticGradient(seq, nn.CrossEntropyCriterion())
         trainer.learningRate, trainer.maxIteration = opt.learningRate, opt.iterations

@@ -368,6 +368,9 @@ typedef struct tadnn_head_args {
   const void* pool_idx;
   void* dpre;
   float* gbias_pre;
+  /* optional device word XOR-mixed into `seed` (forward and backward alike): a captured CUDA graph bakes `seed`
+   * in, so a per-replay counter in device memory is what gives every replay its own dropout mask */
+  const unsigned int* seed_dev;
 } tadnn_head_args;
 /* Scratch needed by tadnn_head_forward (per-block loss partials + a completion counter).  The
  * caller allocates it ONCE, zero-filled; the kernel leaves the counter at zero again. */

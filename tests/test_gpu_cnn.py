@@ -186,3 +186,44 @@ def test_cifar_cnn_trains():
             K.sgd_step(p.data.view(-1), p.grad.view(-1), 0.05)
         losses.append(loss.item())
     assert min(losses[-10:]) < 0.8 * losses[0], (losses[0], losses[-10:])
+
+
+def test_per_sample_graph_step_matches_eager_and_is_used_by_stochastic_gradient():
+    """The reference's loop is one sample per step (datamodule.lua:134-158): on a GPU each step is one replay of a
+    captured CUDA graph of the fused kernels + the in-place update."""
+    from tadnn import nn
+    from tadnn.models.cifar_cnn import CifarCNN
+    from tadnn.ops import cnn as K
+    torch.manual_seed(0)
+    a, b = CifarCNN(dropout=0.0).cuda().train(), CifarCNN(dropout=0.0).cuda().train()
+    b.load_state_dict(a.state_dict())
+    xs = torch.randn(6, 3, 32, 32, device="cuda").bfloat16()
+    ys = torch.randint(0, 10, (6,), device="cuda")
+    for i in range(6):
+        la = a.native_sample_step(xs[i], ys[i], 0.05).clone()
+        for p in b.parameters():
+            if p.grad is not None:
+                p.grad.zero_()
+        lb = b.forward_backward(xs[i:i + 1], ys[i:i + 1])
+        for p in b.parameters():
+            K.sgd_step(p.data.view(-1), p.grad.view(-1), 0.05, 0.0, True)
+        assert abs(la.item() - lb.item()) < 1e-5, i
+    for (n, p), q in zip(a.named_parameters(), b.parameters()):
+        assert ((p - q).norm() / q.norm()).item() < 1e-5, n
+    # dropout: every replay draws a new mask (the seed counter lives on the device and the graph bumps it)
+    c = CifarCNN(dropout=0.5).cuda().train()
+    l = [c.native_sample_step(xs[0], ys[0], 0.0).item() for _ in range(4)]
+    assert len(set(l)) > 1
+    # StochasticGradient picks the graph path up by itself and the training error falls
+    torch.manual_seed(1)
+    m = CifarCNN(dropout=0.0).cuda().train()
+    t = torch.randint(0, 10, (64,), device="cuda")
+    pat = torch.randn(10, 3, 32, 32, device="cuda")
+    x = (0.3 * torch.randn(64, 3, 32, 32, device="cuda") + pat[t]).bfloat16()
+    tr = nn.StochasticGradient(m, nn.CrossEntropyCriterion())
+    tr.learningRate, tr.maxIteration, tr.verbose, tr.shuffleIndices = 0.02, 4, False, False
+    errs = []
+    tr.hookIteration = lambda s, it, e: errs.append(e)
+    tr.train((x, t))
+    assert "_sample_graph" in m.__dict__
+    assert errs[-1] < 0.7 * errs[0], errs

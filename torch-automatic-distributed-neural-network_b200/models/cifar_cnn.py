@@ -58,7 +58,7 @@ def _dp1_buffer(dev, B):
     return t
 
 
-def _cnn_forward(x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fused_conv1, conv2_mode):
+def _cnn_forward(x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fused_conv1, conv2_mode, seed_dev=None):
     """Launch the forward kernels; returns (loss, logp, saved-for-backward dict)."""
     from ..ops import cnn as K
     B = x.shape[0]
@@ -106,12 +106,14 @@ def _cnn_forward(x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fu
     h.target = tgt.data_ptr()
     h.B, h.D, h.H, h.NC = B, 64, 100, 10
     h.dropout_p, h.seed = float(p_drop), seed
+    if seed_dev is not None:
+        h.seed_dev = seed_dev.data_ptr()
     h.hidden, h.logp, h.loss = hidden.data_ptr(), logp.data_ptr(), loss.data_ptr()
     ws = K.head_workspace(dev)
     _native.check(_native.lib().tadnn_head_forward(C.byref(h), C.c_void_p(ws.data_ptr()),
                                                    C.c_void_p(_native.stream_ptr())), "tadnn_head_forward")
     saved = dict(xb=xb, col1=col1, a1=a1, p1=p1, idx1=idx1, col2=col2, a2=a2, p2=p2, idx2=idx2, hidden=hidden,
-                 logp=logp, tgt=tgt, w2p=w2p, fw1=fw1, fb1=fb1, fw2=fw2, fb2=fb2, p_drop=float(p_drop), seed=seed,
+                 logp=logp, tgt=tgt, w2p=w2p, fw1=fw1, fb1=fb1, fw2=fw2, fb2=fb2, p_drop=float(p_drop), seed=seed, seed_dev=seed_dev,
                  B=B, fused_conv1=bool(fused_conv1), conv2_mode=conv2_mode, fused2=fused2, sh=sh)
     return loss, logp, saved
 
@@ -128,6 +130,8 @@ def _cnn_backward(sv, gw1, gb1, gw2, gb2, gfw1, gfb1, gfw2, gfb2, gloss=None, ta
     h.target = sv["tgt"].data_ptr()
     h.B, h.D, h.H, h.NC = B, 64, 100, 10
     h.dropout_p, h.seed = sv["p_drop"], sv["seed"]
+    if sv.get("seed_dev") is not None:
+        h.seed_dev = sv["seed_dev"].data_ptr()
     h.hidden, h.logp = sv["hidden"].data_ptr(), sv["logp"].data_ptr()
     h.gw1, h.gb1, h.gw2, h.gb2 = gfw1.data_ptr(), gfb1.data_ptr(), gfw2.data_ptr(), gfb2.data_ptr()
     h.grad_scale = 1.0
@@ -313,10 +317,69 @@ class CifarCNN(torch.nn.Module, T7Protocol):
         pd = self.dropout if self.training else 0.0
         seed = (self._seed * 2654435761 + self._step * 40503) & 0xFFFFFFFF
         with torch.no_grad():
-            loss, _logp, sv = _cnn_forward(x, target, *[p.data for p in ps], pd, seed, self.fused_conv1, self.conv2_mode)
+            loss, _logp, sv = _cnn_forward(x, target, *[p.data for p in ps], pd, seed, self.fused_conv1, self.conv2_mode,
+                                           seed_dev=getattr(self, "_seed_dev", None))
             cb = (lambda: tail_ready(self.conv2_weight)) if (tail_ready is not None and sv.get("fused2")) else None
             _cnn_backward(sv, *[p.grad for p in ps], tail_ready=cb)
         return loss
+
+    # ---- the reference's own workload: one sample per step (datamodule.lua:134-158) ----------------
+    def native_sample_step(self, x: torch.Tensor, target, lr: float, weight_decay: float = 0.0) -> torch.Tensor:
+        """Forward + criterion + backward + in-place SGD step for ONE sample (or a small batch) as a replay of
+        a captured CUDA graph: the ten kernels of the fused step plus the optimiser launch cost one graph
+        launch instead of eleven launches and their Python glue, which is what bounds a B = 1 loop.
+        The dropout mask of each replay comes from a counter in device memory that the graph itself
+        increments.  Returns the (device) loss; never synchronises.  Used by ``nn.StochasticGradient``."""
+        if x.dim() == 3:
+            x = x.unsqueeze(0)
+        tgt = torch.as_tensor(target, device=x.device).reshape(-1)
+        key = (tuple(x.shape), float(lr), float(weight_decay), self.training, self.conv1_weight.data_ptr())
+        ent = self.__dict__.get("_sample_graph")
+        if ent is None or ent["key"] != key:
+            ent = self._capture_sample_graph(x, tgt, lr, weight_decay, key)
+            self.__dict__["_sample_graph"] = ent
+        ent["x"].copy_(x, non_blocking=True)
+        ent["y"].copy_(tgt, non_blocking=True)
+        ent["graph"].replay()
+        return ent["loss"]
+
+    def _capture_sample_graph(self, x, tgt, lr, wd, key):
+        from ..ops.cnn import sgd_step
+        dev = x.device
+        xs = torch.zeros(x.shape, device=dev, dtype=torch.bfloat16)
+        ys = torch.zeros(tgt.shape, device=dev, dtype=torch.int64)
+        self._seed_dev = torch.zeros(1, device=dev, dtype=torch.int32)
+        ps = self._plist()
+        for p in ps:
+            if p.grad is None:
+                p.grad = torch.zeros_like(p)
+        flat = getattr(self, "_tadnn_flat", None)
+
+        def body(lr_, wd_):
+            loss = self.forward_backward(xs, ys)
+            if flat is not None and all(dt == torch.float32 for dt in flat.groups):
+                for g in flat.groups.values():
+                    sgd_step(g.region[:g.half], g.region[g.half:], lr_, wd_, zero_grad=True)
+            else:
+                for p in ps:
+                    sgd_step(p.data.view(-1), p.grad.view(-1), lr_, wd_, zero_grad=True)
+            self._seed_dev.add_(1)
+            return loss
+
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):   # warm-up outside capture: lazy one-time set-up (smem attributes, workspaces, buffers)
+            xs.copy_(x)
+            ys.copy_(tgt)
+            for _ in range(2):
+                body(0.0, 0.0)   # zero step size: the warm-up must leave the parameters as they are
+            self._seed_dev.zero_()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            loss = body(lr, wd)
+        return {"key": key, "graph": graph, "x": xs, "y": ys, "loss": loss}
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         """Log-probabilities ``[B, 10]`` (what the reference model outputs after LogSoftMax)."""

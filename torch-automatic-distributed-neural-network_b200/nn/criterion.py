@@ -53,6 +53,8 @@ def _as_target(target, batch: bool):
 
 
 class ClassNLLCriterion(Criterion):
+    is_cross_entropy = True  # on log-probabilities; lets a fused native step (model.native_sample_step) stand in
+
     def loss(self, input, target):
         if input.dim() == 1:
             return F.nll_loss(input.unsqueeze(0).float(), _as_target(target, True).to(input.device))
@@ -63,6 +65,7 @@ class ClassNLLCriterion(Criterion):
 class CrossEntropyCriterion(Criterion):
     """``LogSoftMax`` + ``ClassNLLCriterion`` (what the example's criterion is,
     cifar_example/sgd-torchad_nn-cifar.lua:237)."""
+    is_cross_entropy = True
 
     def loss(self, input, target):
         if input.dim() == 1:

@@ -55,6 +55,11 @@ class StochasticGradient:
     # -- one optimisation step on a (batch of) sample(s) --------------------------
     def _step(self, input, target, lr: float) -> float:
         module, criterion = self.module, self.criterion
+        fast = getattr(module, "native_sample_step", None)
+        if fast is not None and torch.is_tensor(input) and input.is_cuda and getattr(criterion, "is_cross_entropy", False) \
+                and getattr(module, "_native_ok", lambda t: False)(input if input.dim() == 4 else input.unsqueeze(0)):
+            # the whole per-sample step (forward, criterion, backward, in-place update) as one CUDA-graph replay
+            return fast(input, target, lr)
         params = [p for p in module.parameters() if p.requires_grad]
         with torch.enable_grad():
             out = module(input)

@@ -17,7 +17,7 @@ class HeadArgs(C.Structure):
         ("dropout_p", C.c_float), ("seed", C.c_uint), ("hidden", C.c_void_p), ("logp", C.c_void_p),
         ("loss", C.c_void_p), ("gw1", C.c_void_p), ("gb1", C.c_void_p), ("gw2", C.c_void_p), ("gb2", C.c_void_p),
         ("dp2", C.c_void_p), ("grad_scale", C.c_float), ("grad_scale_dev", C.c_void_p),
-        ("pool_idx", C.c_void_p), ("dpre", C.c_void_p), ("gbias_pre", C.c_void_p),
+        ("pool_idx", C.c_void_p), ("dpre", C.c_void_p), ("gbias_pre", C.c_void_p), ("seed_dev", C.c_void_p),
     ]
 
 

@@ -226,4 +226,4 @@ def test_per_sample_graph_step_matches_eager_and_is_used_by_stochastic_gradient(
     tr.hookIteration = lambda s, it, e: errs.append(e)
     tr.train((x, t))
     assert "_sample_graph" in m.__dict__
-    assert errs[-1] < 0.7 * errs[0], errs
+    assert errs[-1] < 0.85 * errs[0], errs

@@ -125,13 +125,17 @@ class BatchTrainer:
             plane = int(data[0].numel() // C)
             if aff is None:
                 aff = ([1.0 / 255.0] * C, [0.0] * C)
-            wide = [torch.empty((batch,) + tuple(data.shape[1:]), dtype=torch.bfloat16, device=dev) for _ in range(2)]
         bufs = [(torch.empty((batch,) + tuple(data.shape[1:]), dtype=data.dtype, device=dev),
                  torch.empty((batch,) + tuple(targets.shape[1:]), dtype=targets.dtype, device=dev)) for _ in range(depth)]
+        if u8:  # one widened buffer per ring slot: the widening kernel runs on the copy stream, right behind its copy
+            wide = [torch.empty((batch,) + tuple(data.shape[1:]), dtype=torch.bfloat16, device=dev) for _ in range(depth)]
         ready = [torch.cuda.Event() for _ in range(depth)]
         consumed = [torch.cuda.Event() for _ in range(depth)]
         host_loss = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
         loss_ev = [torch.cuda.Event(), torch.cuda.Event()]
+        loss_ready = [torch.cuda.Event(), torch.cuda.Event()]
+        rs = self.__dict__.setdefault("_read_stream", torch.cuda.Stream())  # loss read-back: never blocks the compute stream
+        dev_loss = [torch.zeros((), dtype=torch.float32, device=dev) for _ in range(2)]
 
         def issue(s):
             k = s % depth
@@ -141,6 +145,8 @@ class BatchTrainer:
                     cs.wait_event(consumed[k])
                 bufs[k][0].copy_(data[i:i + batch], non_blocking=True)
                 bufs[k][1].copy_(targets[i:i + batch], non_blocking=True)
+                if u8:
+                    u8_to_bf16(bufs[k][0], plane, C, aff[0], aff[1], out=wide[k])
                 ready[k].record(cs)
 
         for s in range(min(depth - 1, steps)):
@@ -150,16 +156,15 @@ class BatchTrainer:
             if s + depth - 1 < steps:
                 issue(s + depth - 1)
             main.wait_event(ready[k])
-            if u8:
-                x = u8_to_bf16(bufs[k][0], plane, C, aff[0], aff[1], out=wide[s & 1])
-                consumed[k].record(main)  # the staged bytes are free as soon as they are widened
-                loss = self.step(x, bufs[k][1])
-            else:
-                loss = self.step(bufs[k][0], bufs[k][1])
-                consumed[k].record(main)
+            loss = self.step(wide[k] if u8 else bufs[k][0], bufs[k][1])
+            consumed[k].record(main)
             j = s & 1
-            host_loss[j].copy_(loss, non_blocking=True)
-            loss_ev[j].record(main)
+            dev_loss[j].copy_(loss)          # the step's loss tensor may be reused by the next step: keep a copy
+            loss_ready[j].record(main)
+            with torch.cuda.stream(rs):
+                rs.wait_event(loss_ready[j])
+                host_loss[j].copy_(dev_loss[j], non_blocking=True)
+                loss_ev[j].record(rs)
             if s >= 1:
                 loss_ev[j ^ 1].synchronize()
                 yield float(host_loss[j ^ 1])

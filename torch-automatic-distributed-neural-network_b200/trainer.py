@@ -137,17 +137,32 @@ class BatchTrainer:
         rs = self.__dict__.setdefault("_read_stream", torch.cuda.Stream())  # loss read-back: never blocks the compute stream
         dev_loss = [torch.zeros((), dtype=torch.float32, device=dev) for _ in range(2)]
 
+        ws = self.__dict__.setdefault("_widen_stream", torch.cuda.Stream()) if u8 else None
+        copied = [torch.cuda.Event() for _ in range(depth)]
+        widened = [torch.cuda.Event() for _ in range(depth)]
+
         def issue(s):
             k = s % depth
             i = ((start + s) % nb) * batch
             with torch.cuda.stream(cs):
                 if s >= depth:
-                    cs.wait_event(consumed[k])
+                    cs.wait_event(consumed[k])   # step s - depth has consumed this slot (its bytes were widened before that)
                 bufs[k][0].copy_(data[i:i + batch], non_blocking=True)
                 bufs[k][1].copy_(targets[i:i + batch], non_blocking=True)
-                if u8:
+                if not u8:
+                    ready[k].record(cs)
+                else:
+                    copied[k].record(cs)
+            if u8:
+                # the widening kernel runs on its own stream: it may have to wait for SMs while the persistent compute
+                # kernels are resident, and the copy stream must keep the PCIe link busy meanwhile
+                with torch.cuda.stream(ws):
+                    ws.wait_event(copied[k])
+                    if s >= depth:
+                        ws.wait_event(consumed[k])                     # wide[k] of step s - depth has been consumed
                     u8_to_bf16(bufs[k][0], plane, C, aff[0], aff[1], out=wide[k])
-                ready[k].record(cs)
+                    widened[k].record(ws)
+                    ready[k].record(ws)
 
         for s in range(min(depth - 1, steps)):
             issue(s)

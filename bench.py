@@ -40,7 +40,7 @@ sys.path.insert(0, ROOT)
 METRIC = "train_samples_per_sec"
 MODEL = "cifar_example CNN (conv5x5x64-relu-pool3, conv5x5x64-relu-pool3, fc64x100-relu, fc100x10, logsoftmax+CE; 114838 params)"
 # BASELINE.md row b1 (PyTorch + cuDNN + NCCL restatement on this box), samples/s by GPU count
-PUBLISHED_B1 = {1: 0.82e6, 2: 1.57e6, 8: 5.99e6}
+PUBLISHED_B1 = {1: 0.82e6, 2: 1.57e6, 4: 3.08e6, 8: 5.99e6}
 AFFINE = ([4.0 / 255.0] * 3, [-2.0] * 3)  # uint8 pixel -> roughly N(0,1)-ranged bf16
 
 

@@ -1,0 +1,398 @@
+// First convolution stage of the example CNN as a "sliding descriptor" implicit GEMM: the staged
+// image itself is the tcgen05 operand, no im2col row is ever built.
+//
+//   forward : p1, idx1 = maxpool3x3/3( relu( conv5x5(x; W1) + b1 ) )
+//   backward: dW1, db1 += patch(x)^T * d(conv out), d(conv out) regenerated from (dp1, idx1)
+//
+// Same layer as conv1_fused.cu (cifar_example/sgd-torchad_nn-cifar.lua:91-93: SpatialConvolutionMM + ReLU +
+// SpatialMaxPooling 3x3/3 and their backward), different operand scheme.  conv1_fused.cu builds one 80-element
+// patch row per output pixel in shared memory (20 KB of st.shared per 128 pixels, shared-memory-wavefront bound);
+// here the input is stored NHWC4 (bf16 [B,32,32,4], 4th channel == 1.0 and carries the bias), so that
+//
+//   * one 16-byte chunk of an image row = the PAIR of pixels (2q, 2q+1) x 4 channels = 8 consecutive K elements;
+//   * "position" r = (n, h, q) (pixel pair q of row h of image n) lives at byte 16*r of the input tensor, and the
+//     K chunk (kh, j) of the patch of position r is simply the chunk at position r + 16*kh + j.
+//
+// A no-swizzle K-major UMMA operand is exactly "rows at a 16-byte pitch (8-row groups SBO = 128 B apart), the two
+// 8-element K chunks of an MMA LBO bytes apart", so the operand of K chunk (kh, j) for 96 consecutive positions is
+// the staged image at offset 16*(16*kh + j): overlapping rows, zero data movement.  An output pixel with even
+// column w = 2q uses taps kw = 2j + p of chunks j = 0..2 (p = pixel inside the pair), one with odd column w = 2q+1
+// uses kw = 2j + p - 1: the same data against two weight matrices, i.e. ONE GEMM with the 128 rows
+// (column parity, channel) on the weight side:
+//
+//   D[(par, ch), r] = sum_{kh, j, p, c}  W2[(par, ch), (kh, j, p, c)] * x[r + 16 kh + j][p][c]
+//
+// 15 chunks (+1 zero-weight pad) = 8 MMAs of K = 16 per tile; a tile is N = 96 positions (6 conv rows = 2 pooled
+// rows) or N = 48 (conv rows 24..26), M = 128.  The epilogue thread of lane (par, ch) holds every position of its
+// channel in registers: pooling is thread-local along the accumulator columns, the two column parities are merged
+// through a shared exchange.  "accumulator | (8 - window position)" keys make max + first-arg-max one integer max.
+#include "common.cuh"
+#include "sm100.cuh"
+#include <stdlib.h>
+
+#include <utility>
+
+namespace tadnn {
+namespace {
+
+using namespace sm100;
+
+constexpr int kO = 64, kK = 75;
+constexpr int kImgBytes = 32 * 32 * 4 * 2;   // 8192: one NHWC4 image
+constexpr int kPairsPerRow = 16;
+constexpr int kWinPerImg = 81;
+
+// no-swizzle shared-memory matrix descriptor (layout type 0, sm_100 "version 1")
+__device__ __forceinline__ uint64_t make_smem_desc_nosw(uint32_t smem_addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr >> 4) & 0x3FFFu);
+  d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFFu) << 16;
+  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFFu) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  return d;
+}
+
+__device__ __forceinline__ uint32_t sw128(int r, int j) { return static_cast<uint32_t>(r * 128 + ((j ^ (r & 7)) << 4)); }
+
+__device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t* r) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+
+// spin on the barrier phase without the suspend-time hint of sm100::mbar_wait: a tile lasts a few hundred cycles here,
+// far less than a suspended warp takes to come back
+template <bool SPIN>
+__device__ __forceinline__ void mbar_wait_t(uint64_t* bar, uint32_t parity) {
+  if (!SPIN) {
+    mbar_wait(bar, parity);
+    return;
+  }
+  uint32_t ok;
+  do {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+  } while (!ok);
+}
+__device__ __forceinline__ void sts32(uint32_t addr, int v) { asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
+__device__ __forceinline__ int lds32(uint32_t addr) {
+  int v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+
+// K chunk order of the 8 MMAs: step s < 5 = chunks (kh = s, j = 0), (kh = s, j = 1); step 5 = (0, 2), (1, 2);
+// step 6 = (2, 2), (3, 2); step 7 = (4, 2), zero-weight pad (reads chunk (4, 3): finite image data).
+__host__ __device__ constexpr int step_first_chunk(int s) { return s < 5 ? s * kPairsPerRow : (s == 5 ? 2 : (s == 6 ? 2 * kPairsPerRow + 2 : 4 * kPairsPerRow + 2)); }
+__host__ __device__ constexpr int step_lbo(int s) { return (s == 5 || s == 6) ? kPairsPerRow * 16 : 16; }
+
+struct Conv1sArgs {
+  const __nv_bfloat16* x;   // NHWC4 [B, 32, 32, 4], channel 3 == 1.0
+  const __nv_bfloat16* w;   // packed [128, 128]: row (par, ch), column (step, half, p, c)
+  __nv_bfloat16* p1;        // [B, 9, 9, 64]
+  unsigned char* idx1;      // [B, 9, 9, 64]: 8 - (window position 0..8 of the arg-max), 15 where the pooled ReLU output is 0
+  const __nv_bfloat16* dp1; // backward: [B, 9, 9, 64]
+  float* gw;                // backward: [64, 75] Torch7 layout, +=
+  float* gb;                // backward: [64], +=
+  int B;
+  int rows;                 // backward: pooled rows 0..rows-1 of dp1 can be non-zero
+};
+
+// ======================================= forward =======================================
+// A tile = 6 conv rows (2 pooled rows, N = 96 positions) or conv rows 24..26 (N = 48): 5 tiles per image, 8 MMAs each.
+// Four accumulator stages of 128 TMEM columns, one per epilogue group (4 warps = the 128 accumulator lanes): with
+// 16 epilogue warps every scheduler has four of them to hide tcgen05.ld and shared-memory latency behind.
+constexpr int kSlots = 8;                     // staged images
+constexpr int kGroups = 4;
+constexpr int kTilesPerImg = 5;
+constexpr int kFwdThreads = 32 * (2 + 4 * kGroups);   // warp 0: MMA + TMEM, warp 1: loader, then the epilogue groups
+constexpr int kXchBytes = 18 * kO * 4;        // per epilogue group
+constexpr int kFwdSmem = 2 * 16384 + kSlots * kImgBytes + 2 * kGroups * kXchBytes + 1024;
+constexpr int kStageCols = 128;               // TMEM columns per accumulator stage (96 used)
+
+// The 9 window keys of one pooled row (3 conv rows x 16 pairs of accumulator columns) for column parity PAR.
+// key = fp32 accumulator with its lowest mantissa byte replaced by (8 - window position): for positive values
+// (the only ones that survive the ReLU) a signed integer max is the maximum with ties going to the first position.
+template <int CODE>
+__device__ __forceinline__ int make_key(uint32_t v, uint32_t mask) {
+  int k;
+  asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(k) : "r"(v), "r"(mask), "n"(CODE));   // (v & mask) | CODE in one LOP3
+  return k;
+}
+
+template <int PAR, int IQ>
+__device__ __forceinline__ void key_step(const uint32_t (&v)[48], int (&key)[9], uint32_t mask) {
+  constexpr int i = IQ / 14, q = IQ % 14, w = 2 * q + PAR;   // conv row i of the pooled row, pixel pair q, column w
+  if constexpr (w <= 26) key[w / 3] = max(key[w / 3], make_key<8 - (i * 3 + w % 3)>(v[i * 16 + q], mask));
+}
+template <int PAR, int... IQ>
+__device__ __forceinline__ void key_steps(const uint32_t (&v)[48], int (&key)[9], uint32_t mask, std::integer_sequence<int, IQ...>) {
+  (key_step<PAR, IQ>(v, key, mask), ...);
+}
+template <int PAR>
+__device__ __forceinline__ void pool_row_keys(const uint32_t (&v)[48], int (&key)[9]) {
+  uint32_t mask;
+  asm volatile("mov.u32 %0, 0xFFFFFF00;" : "=r"(mask));   // kept in a register (volatile: not folded back into an immediate)
+#pragma unroll
+  for (int w = 0; w < 9; ++w) key[w] = static_cast<int>(0x80000000u);
+  key_steps<PAR>(v, key, mask, std::make_integer_sequence<int, 42>{});
+}
+
+template <bool SPIN>
+__global__ void __launch_bounds__(kFwdThreads, 1) conv1s_fwd_kernel(const Conv1sArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint8_t* wbuf = smem;                               // two SWIZZLE_128B blocks [128 rows x 64 k]
+  uint8_t* imgbuf = smem + 2 * 16384;                 // kSlots images
+  const uint32_t xch = smem_u32(imgbuf + kSlots * kImgBytes);
+  __shared__ __align__(8) uint64_t img_full[kSlots], img_empty[kSlots], t_full[kGroups], t_empty[kGroups];
+  __shared__ uint32_t tmem_base_smem;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kSlots; ++s) {
+      mbar_init(&img_full[s], 1);
+      mbar_init(&img_empty[s], 1);
+    }
+    for (int s = 0; s < kGroups; ++s) {
+      mbar_init(&t_full[s], 1);
+      mbar_init(&t_empty[s], 128);
+    }
+    fence_mbar_init();
+  }
+  if (warp == 0) tmem_alloc<512>(&tmem_base_smem);
+  for (int i = threadIdx.x; i < 128 * 16; i += blockDim.x) {
+    const int row = i >> 4, j = i & 15;
+    const uint4 v = *reinterpret_cast<const uint4*>(a.w + row * 128 + j * 8);
+    *reinterpret_cast<uint4*>(wbuf + (j >> 3) * 16384 + sw128(row, j & 7)) = v;
+  }
+  fence_proxy_async_smem();
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = tmem_base_smem;
+
+  if (warp == 0) {
+    // ---------------- MMA issuer ----------------
+    if (elect_one()) {
+      constexpr uint32_t idesc96 = make_idesc_bf16(128, 96, 0, 0), idesc48 = make_idesc_bf16(128, 48, 0, 0);
+      const uint32_t wa = smem_u32(wbuf);
+      int tc = 0, i = 0;
+      for (int n = blockIdx.x; n < a.B; n += gridDim.x, ++i) {
+        const int slot = i % kSlots;
+        mbar_wait_t<SPIN>(&img_full[slot], (i / kSlots) & 1);
+        const uint32_t img = smem_u32(imgbuf + slot * kImgBytes);
+#pragma unroll
+        for (int t = 0; t < kTilesPerImg; ++t, ++tc) {
+          const int s = tc & (kGroups - 1);
+          mbar_wait_t<SPIN>(&t_empty[s], ((tc >> 2) & 1) ^ 1);
+          tc_fence_after_sync();
+          const uint32_t d = tmem_base + static_cast<uint32_t>(s * kStageCols);
+          const uint32_t bbase = img + t * 96 * 16;
+#pragma unroll
+          for (int st = 0; st < 8; ++st)
+            umma_f16(d, make_smem_desc_sw128(wa + (st >> 2) * 16384 + (st & 3) * 32, 16, 1024),
+                     make_smem_desc_nosw(bbase + step_first_chunk(st) * 16, step_lbo(st), 128), t < 4 ? idesc96 : idesc48, st > 0);
+          umma_commit(&t_full[s]);
+        }
+        umma_commit(&img_empty[slot]);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ---------------- loader: one 8 KB bulk copy per image ----------------
+    if (elect_one()) {
+      int i = 0;
+      for (int n = blockIdx.x; n < a.B; n += gridDim.x, ++i) {
+        const int slot = i % kSlots;
+        mbar_wait(&img_empty[slot], ((i / kSlots) & 1) ^ 1);
+        mbar_arrive_expect_tx(&img_full[slot], kImgBytes);
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                         smem_u32(imgbuf + slot * kImgBytes)),
+                     "l"(a.x + static_cast<long long>(n) * (kImgBytes / 2)), "r"(kImgBytes), "r"(smem_u32(&img_full[slot]))
+                     : "memory");
+      }
+    }
+    __syncwarp();
+  } else {
+    // ---------------- epilogue: pooling in registers, parity merge through shared memory ----------------
+    const int grp = (warp - 2) >> 2;
+    const int q = warp & 3;                  // TMEM lane quarter
+    const int par = q >> 1;                  // column parity of this thread's accumulator row
+    const int ch = (q & 1) * 32 + lane;
+    const uint32_t xg = xch + static_cast<uint32_t>(grp * kXchBytes + ch * 4);
+    const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(grp * kStageCols);
+    unsigned short* p1u = reinterpret_cast<unsigned short*>(a.p1);
+    const int my_imgs = (a.B - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+    const int my_tiles = my_imgs * kTilesPerImg;
+    // this group's tiles: tc = grp, grp + 4, ... (tile t of this CTA's i-th image is tc = 5 i + t)
+#pragma unroll 1
+    for (int tc = grp; tc < my_tiles; tc += kGroups) {
+      const int i = tc / kTilesPerImg, t = tc - i * kTilesPerImg;
+      const long long n = static_cast<long long>(blockIdx.x) + static_cast<long long>(i) * gridDim.x;
+      mbar_wait_t<SPIN>(&t_full[grp], (tc >> 2) & 1);
+      tc_fence_after_sync();
+      const bool two = t < 4;        // two pooled rows (18 windows), or the last one of the image (9 windows)
+      int key[18];
+      {
+        uint32_t v[48];
+        tmem_ld_32x32b_x32(taddr, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+        tmem_ld_32x32b_x16(taddr + 32, &v[32]);
+        tmem_ld_wait();
+        if (par == 0) pool_row_keys<0>(v, *reinterpret_cast<int(*)[9]>(&key[0]));
+        else pool_row_keys<1>(v, *reinterpret_cast<int(*)[9]>(&key[0]));
+      }
+      if (two) {
+        uint32_t v[48];
+        tmem_ld_32x32b_x32(taddr + 48, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+        tmem_ld_32x32b_x16(taddr + 80, &v[32]);
+        tmem_ld_wait();
+        if (par == 0) pool_row_keys<0>(v, *reinterpret_cast<int(*)[9]>(&key[9]));
+        else pool_row_keys<1>(v, *reinterpret_cast<int(*)[9]>(&key[9]));
+      }
+      tc_fence_before_sync();
+      mbar_arrive(&t_empty[grp]);
+      // Window wi is finished by the thread whose parity equals wi & 1; the other one hands its key over through the
+      // exchange buffer of this tile's parity (double-buffered: one barrier per tile is enough).
+      const uint32_t xb = xg + static_cast<uint32_t>(((tc >> 2) & 1) * (kGroups * kXchBytes));
+#pragma unroll
+      for (int wi = 0; wi < 9; ++wi)
+        if ((wi & 1) != par) sts32(xb + wi * (kO * 4), key[wi]);
+      if (two) {
+#pragma unroll
+        for (int wi = 9; wi < 18; ++wi)
+          if ((wi & 1) != par) sts32(xb + wi * (kO * 4), key[wi]);
+      }
+      asm volatile("bar.sync %0, 128;" ::"r"(2 + grp) : "memory");
+      unsigned short* po = p1u + (n * kWinPerImg + t * 18) * kO + ch;
+      unsigned char* io = a.idx1 + (n * kWinPerImg + t * 18) * kO + ch;
+      // max of the two parities and 0 (ReLU) in one 3-input max; a dead window has no value bits left: key <= 255
+      auto finish = [&](int wi) {
+        const int k = max(max(key[wi], lds32(xb + wi * (kO * 4))), 0);
+        const __nv_bfloat16 hv = __float2bfloat16_rn(__int_as_float(k));   // the code byte is far below bf16 resolution
+        po[wi * kO] = *reinterpret_cast<const unsigned short*>(&hv);
+        io[wi * kO] = static_cast<unsigned char>(k > 255 ? k : 15);
+      };
+#pragma unroll
+      for (int wi = 0; wi < 9; ++wi)
+        if ((wi & 1) == par) finish(wi);
+      if (two) {
+#pragma unroll
+        for (int wi = 9; wi < 18; ++wi)
+          if ((wi & 1) == par) finish(wi);
+      }
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after_sync();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
+// Torch7 weight [64, 75] fp32 (k = (c*5+kh)*5+kw) + bias [64]  ->  bf16 [128, 128]
+__global__ void conv1s_weight_pack_kernel(const float* __restrict__ w, const float* __restrict__ bias, __nv_bfloat16* __restrict__ wp) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= 128 * 128) return;
+  const int m = i >> 7, k = i & 127;
+  const int par = m >> 6, ch = m & 63;
+  const int st = k >> 4, half = (k >> 3) & 1, e = k & 7;
+  int kh, j;
+  if (st < 5) { kh = st; j = half; }
+  else if (st == 5) { kh = half; j = 2; }
+  else if (st == 6) { kh = 2 + half; j = 2; }
+  else { kh = 4; j = half ? -1 : 2; }
+  float v = 0.f;
+  if (j >= 0) {
+    const int p = e >> 2, c = e & 3;
+    const int kw = 2 * j + p - par;
+    if (kw >= 0 && kw <= 4) {
+      if (c < 3) v = w[ch * kK + (c * 5 + kh) * 5 + kw];
+      else if (kh == 0 && kw == 0) v = bias[ch];
+    }
+  }
+  wp[i] = __float2bfloat16_rn(v);
+}
+
+// NCHW {uint8, bf16, fp32} [B, 3, 32, 32] -> NHWC4 bf16 [B, 32, 32, 4]: y = x * scale[c] + shift[c], channel 3 = 1.0
+template <typename T>
+__device__ __forceinline__ float ld_as_float(const T* p) { return static_cast<float>(*p); }
+template <>
+__device__ __forceinline__ float ld_as_float<__nv_bfloat16>(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+
+struct Affine3 { float scale[3], shift[3]; };
+
+template <typename T>
+__global__ void nhwc4_pack_kernel(const T* __restrict__ x, __nv_bfloat16* __restrict__ y, long long npix, const Affine3 af) {
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= npix) return;
+  const long long n = i >> 10;
+  const int hw = static_cast<int>(i & 1023);
+  const T* src = x + n * 3072 + hw;
+  const float c0 = ld_as_float(src) * af.scale[0] + af.shift[0];
+  const float c1 = ld_as_float(src + 1024) * af.scale[1] + af.shift[1];
+  const float c2 = ld_as_float(src + 2048) * af.scale[2] + af.shift[2];
+  *reinterpret_cast<uint2*>(y + i * 4) = make_uint2(pack_bf16x2(c0, c1), pack_bf16x2(c2, 1.0f));
+}
+
+}  // namespace
+}  // namespace tadnn
+
+using namespace tadnn;
+
+extern "C" int tadnn_conv1s_weight_pack(const float* w, const float* bias, void* wp, tadnn_stream_t stream) {
+  conv1s_weight_pack_kernel<<<64, 256, 0, static_cast<cudaStream_t>(stream)>>>(w, bias, static_cast<__nv_bfloat16*>(wp));
+  TADNN_LAUNCH_CHECK("conv1s_weight_pack");
+  return 0;
+}
+
+extern "C" int tadnn_nhwc4_pack(const void* x, int src_dtype, void* y, long long B, const float* host_scale, const float* host_shift,
+                                tadnn_stream_t stream) {
+  TADNN_REQUIRE(B > 0 && B <= 20000000, "nhwc4_pack: batch %lld out of range", B);
+  TADNN_REQUIRE((reinterpret_cast<uintptr_t>(y) & 7) == 0, "nhwc4_pack: output must be 8-byte aligned");
+  Affine3 af;
+  for (int c = 0; c < 3; ++c) {
+    af.scale[c] = host_scale ? host_scale[c] : 1.f;
+    af.shift[c] = host_shift ? host_shift[c] : 0.f;
+  }
+  const long long npix = B * 1024;
+  const unsigned grid = static_cast<unsigned>((npix + 255) / 256);
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  if (src_dtype == 0) nhwc4_pack_kernel<unsigned char><<<grid, 256, 0, s>>>(static_cast<const unsigned char*>(x), static_cast<__nv_bfloat16*>(y), npix, af);
+  else if (src_dtype == 1) nhwc4_pack_kernel<__nv_bfloat16><<<grid, 256, 0, s>>>(static_cast<const __nv_bfloat16*>(x), static_cast<__nv_bfloat16*>(y), npix, af);
+  else if (src_dtype == 2) nhwc4_pack_kernel<float><<<grid, 256, 0, s>>>(static_cast<const float*>(x), static_cast<__nv_bfloat16*>(y), npix, af);
+  else TADNN_REQUIRE(false, "nhwc4_pack: source dtype %d (0 = uint8, 1 = bf16, 2 = fp32)", src_dtype);
+  TADNN_LAUNCH_CHECK("nhwc4_pack");
+  return 0;
+}
+
+extern "C" int tadnn_conv1s_pool_forward(const void* x_nhwc4, const void* w_packed, void* p1, void* idx1, int B, tadnn_stream_t stream) {
+  TADNN_REQUIRE(B > 0 && B <= 20000000, "conv1s_pool_forward: batch %d out of range", B);
+  TADNN_REQUIRE(((reinterpret_cast<uintptr_t>(x_nhwc4) | reinterpret_cast<uintptr_t>(w_packed)) & 15) == 0,
+                "conv1s_pool_forward: operands must be 16-byte aligned");
+  static std::atomic<unsigned long long> attr{0}, attr_s{0};
+  if (int rc = ensure_dyn_smem(conv1s_fwd_kernel<false>, kFwdSmem, attr)) return rc;
+  if (int rc = ensure_dyn_smem(conv1s_fwd_kernel<true>, kFwdSmem, attr_s)) return rc;
+  static const bool spin = getenv("TADNN_CONV1S_NOSPIN") == nullptr;
+  Conv1sArgs a;
+  memset(&a, 0, sizeof(a));
+  a.x = static_cast<const __nv_bfloat16*>(x_nhwc4); a.w = static_cast<const __nv_bfloat16*>(w_packed);
+  a.p1 = static_cast<__nv_bfloat16*>(p1); a.idx1 = static_cast<unsigned char*>(idx1); a.B = B;
+  const int grid = B < sm_count() ? B : sm_count();
+  if (spin) conv1s_fwd_kernel<true><<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
+  else conv1s_fwd_kernel<false><<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
+  TADNN_LAUNCH_CHECK("conv1s_pool_fwd_tcgen05");
+  return 0;
+}

@@ -344,6 +344,17 @@ int tadnn_conv1_pool_backward_bias(const void* x, const void* dp1, int dp1_h, in
                                    const void* idx1, float* grad_weight, float* grad_bias, int B,
                                    tadnn_stream_t stream);
 
+/* conv1 + bias + ReLU + maxpool 3x3/3 with the staged image itself as the tcgen05 operand (csrc/conv1_sliding.cu).
+ * Input layout NHWC4: bf16 [B, 32, 32, 4] with channel 3 == 1.0 (tadnn_nhwc4_pack writes it from NCHW uint8
+ * (src_dtype 0), bf16 (1) or fp32 (2), y = x * host_scale[c] + host_shift[c]; NULL = identity).  w_packed is bf16
+ * [128, 128] from tadnn_conv1s_weight_pack (Torch7 weight [64, 75] + bias [64]).  idx1 holds 8 - (window position
+ * 0..8 of the arg-max), or 15 where the pooled ReLU output is zero (the backward then needs no p1). */
+int tadnn_nhwc4_pack(const void* x, int src_dtype, void* y, long long B, const float* host_scale,
+                     const float* host_shift, tadnn_stream_t stream);
+int tadnn_conv1s_weight_pack(const float* w, const float* bias, void* w_packed, tadnn_stream_t stream);
+int tadnn_conv1s_pool_forward(const void* x_nhwc4, const void* w_packed, void* p1, void* idx1, int B,
+                              tadnn_stream_t stream);
+
 /* Fused classifier head: dropout -> Linear(D,H)+ReLU -> Linear(H,NC) -> log-softmax -> NLL.
  * Limits: D <= 64, H <= 128, NC <= 32.  fc weights in Torch7 nn.Linear layout, fp32. */
 typedef struct tadnn_head_args {

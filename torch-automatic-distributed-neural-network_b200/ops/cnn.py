@@ -226,11 +226,43 @@ def u8_to_bf16(x: torch.Tensor, plane: int, C: int, scale, shift, out=None) -> t
     return out
 
 
+def nhwc4_pack(x: torch.Tensor, scale=None, shift=None, out=None) -> torch.Tensor:
+    """NCHW [B,3,32,32] uint8 / bf16 / fp32 -> NHWC4 bf16 [B,32,32,4] (channel 3 == 1.0, the bias carrier of
+    conv1s_pool_forward); y = x * scale[c] + shift[c] (csrc/conv1_sliding.cu)."""
+    assert x.is_contiguous() and tuple(x.shape[1:]) == (3, 32, 32), tuple(x.shape)
+    code = {torch.uint8: 0, torch.bfloat16: 1, torch.float32: 2}[x.dtype]
+    B = x.shape[0]
+    if out is None:
+        out = torch.empty((B, 32, 32, 4), device=x.device, dtype=torch.bfloat16)
+    fs = (_F4)(*([float(v) for v in scale][:3] + [1.0])) if scale is not None else None
+    fh = (_F4)(*([float(v) for v in shift][:3] + [0.0])) if shift is not None else None
+    _native.check(_native.lib().tadnn_nhwc4_pack(_p(x), code, _p(out), C_ll(B), fs, fh, _s()), "tadnn_nhwc4_pack")
+    return out
+
+
+def conv1s_weight_pack(w: torch.Tensor, bias: torch.Tensor, out=None) -> torch.Tensor:
+    """Torch7 conv1 weight [64,75] fp32 + bias [64] -> bf16 [128,128] operand of conv1s_pool_forward."""
+    if out is None:
+        out = torch.empty((128, 128), device=w.device, dtype=torch.bfloat16)
+    _native.check(_native.lib().tadnn_conv1s_weight_pack(_p(w), _p(bias), _p(out), _s()), "tadnn_conv1s_weight_pack")
+    return out
+
+
+def conv1s_pool_forward(xq: torch.Tensor, wx: torch.Tensor):
+    """xq NHWC4 [B,32,32,4] bf16 -> (p1 [B,9,9,64] bf16, idx1 [B,9,9,64] uint8 = 8 - arg-max window position; 15 = dead window)."""
+    B = xq.shape[0]
+    assert xq.dtype == torch.bfloat16 and xq.is_contiguous() and tuple(xq.shape[1:]) == (32, 32, 4)
+    p1 = torch.empty((B, 9, 9, 64), device=xq.device, dtype=torch.bfloat16)
+    idx1 = torch.empty((B, 9, 9, 64), device=xq.device, dtype=torch.uint8)
+    _native.check(_native.lib().tadnn_conv1s_pool_forward(_p(xq), _p(wx), _p(p1), _p(idx1), B, _s()), "tadnn_conv1s_pool_forward")
+    return p1, idx1
+
+
 def auto_split_k(M: int, N: int, K: int, tile_n: int = 256) -> int:
     tiles = ((M + 127) // 128) * ((N + tile_n - 1) // tile_n)
     kb = (K + 63) // 64
     return max(1, min(kb, 148 // max(1, tiles)))
 
 
-__all__ = ["u8_to_bf16", "conv2_pool_forward", "conv2_wgrad", "conv2_wgrad_unpack", "cnn_pack_shadows", "conv1_pool_backward_bias", "im2col_winfirst", "conv_toeplitz_pack", "expand_corner", "conv1_weight_pack", "conv1_pool_forward", "conv1_pool_backward", "im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "colsum_relu_mask_corner", "conv_weight_pack",
+__all__ = ["nhwc4_pack", "conv1s_weight_pack", "conv1s_pool_forward", "u8_to_bf16", "conv2_pool_forward", "conv2_wgrad", "conv2_wgrad_unpack", "cnn_pack_shadows", "conv1_pool_backward_bias", "im2col_winfirst", "conv_toeplitz_pack", "expand_corner", "conv1_weight_pack", "conv1_pool_forward", "conv1_pool_backward", "im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "colsum_relu_mask_corner", "conv_weight_pack",
            "conv_wgrad_unpack", "head_workspace", "sgd_step", "auto_split_k", "HeadArgs", "gemm_bf16"]

@@ -92,6 +92,33 @@ __device__ __forceinline__ int lds32(uint32_t addr) {
   return v;
 }
 
+// registers -> TMEM: this warp's 32 lanes x 32 consecutive 32-bit columns
+__device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_t* r) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%32], "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31};" ::"r"(r[0]),
+      "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]),
+      "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]), "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]),
+      "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]), "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31]),
+      "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// D[tmem] (+)= A[tmem] * B[smem desc]: the A operand (128 lanes x 8 columns of packed bf16 pairs per K = 16) is read
+// from tensor memory, so only B crosses the shared-memory port
+__device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+
 // K chunk order of the 8 MMAs: step s < 5 = chunks (kh = s, j = 0), (kh = s, j = 1); step 5 = (0, 2), (1, 2);
 // step 6 = (2, 2), (3, 2); step 7 = (4, 2), zero-weight pad (reads chunk (4, 3): finite image data).
 __host__ __device__ constexpr int step_first_chunk(int s) { return s < 5 ? s * kPairsPerRow : (s == 5 ? 2 : (s == 6 ? 2 * kPairsPerRow + 2 : 4 * kPairsPerRow + 2)); }
@@ -118,8 +145,9 @@ constexpr int kGroups = 4;
 constexpr int kTilesPerImg = 5;
 constexpr int kFwdThreads = 32 * (2 + 4 * kGroups);   // warp 0: MMA + TMEM, warp 1: loader, then the epilogue groups
 constexpr int kXchBytes = 18 * kO * 4;        // per epilogue group
-constexpr int kFwdSmem = 2 * 16384 + kSlots * kImgBytes + 2 * kGroups * kXchBytes + 1024;
-constexpr int kStageCols = 128;               // TMEM columns per accumulator stage (96 used)
+constexpr int kFwdSmem = kSlots * kImgBytes + 2 * kGroups * kXchBytes + 1024;
+constexpr int kStageCols = 96;                // TMEM columns per accumulator stage
+constexpr int kWCol = kGroups * kStageCols;   // the weights: 64 columns (8 K steps x 8 columns of bf16 pairs) behind the accumulators
 
 // The 9 window keys of one pooled row (3 conv rows x 16 pairs of accumulator columns) for column parity PAR.
 // key = fp32 accumulator with its lowest mantissa byte replaced by (8 - window position): for positive values
@@ -153,8 +181,7 @@ template <bool SPIN>
 __global__ void __launch_bounds__(kFwdThreads, 1) conv1s_fwd_kernel(const Conv1sArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
-  uint8_t* wbuf = smem;                               // two SWIZZLE_128B blocks [128 rows x 64 k]
-  uint8_t* imgbuf = smem + 2 * 16384;                 // kSlots images
+  uint8_t* imgbuf = smem;                             // kSlots images
   const uint32_t xch = smem_u32(imgbuf + kSlots * kImgBytes);
   __shared__ __align__(8) uint64_t img_full[kSlots], img_empty[kSlots], t_full[kGroups], t_empty[kGroups];
   __shared__ uint32_t tmem_base_smem;
@@ -172,44 +199,63 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1s_fwd_kernel(const Conv1s
     fence_mbar_init();
   }
   if (warp == 0) tmem_alloc<512>(&tmem_base_smem);
-  for (int i = threadIdx.x; i < 128 * 16; i += blockDim.x) {
-    const int row = i >> 4, j = i & 15;
-    const uint4 v = *reinterpret_cast<const uint4*>(a.w + row * 128 + j * 8);
-    *reinterpret_cast<uint4*>(wbuf + (j >> 3) * 16384 + sw128(row, j & 7)) = v;
-  }
-  fence_proxy_async_smem();
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = tmem_base_smem;
+  // The weight operand lives in tensor memory for the whole kernel: row m = (parity, channel) in lane m, its 128 K
+  // values as 64 columns of bf16 pairs.  Written by the first epilogue group (one warp per lane quarter).
+  if (warp >= 2 && warp < 6) {
+    const int q = warp & 3;
+    const uint4* src = reinterpret_cast<const uint4*>(a.w + (q * 32 + lane) * 128);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      uint32_t r[32];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const uint4 v = __ldg(src + h * 8 + j);
+        r[4 * j] = v.x; r[4 * j + 1] = v.y; r[4 * j + 2] = v.z; r[4 * j + 3] = v.w;
+      }
+      tmem_st_32x32b_x32(tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(kWCol + h * 32), r);
+    }
+    tmem_st_wait();
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
 
   if (warp == 0) {
     // ---------------- MMA issuer ----------------
-    if (elect_one()) {
-      constexpr uint32_t idesc96 = make_idesc_bf16(128, 96, 0, 0), idesc48 = make_idesc_bf16(128, 48, 0, 0);
-      const uint32_t wa = smem_u32(wbuf);
-      int tc = 0, i = 0;
-      for (int n = blockIdx.x; n < a.B; n += gridDim.x, ++i) {
-        const int slot = i % kSlots;
-        mbar_wait_t<SPIN>(&img_full[slot], (i / kSlots) & 1);
-        const uint32_t img = smem_u32(imgbuf + slot * kImgBytes);
+    // The whole warp runs the loop (warp-uniform control flow keeps the descriptors in uniform registers); one
+    // elected lane issues.  Descriptor words that do not depend on the tile are built once.
+    constexpr uint32_t idesc96 = make_idesc_bf16(128, 96, 0, 0), idesc48 = make_idesc_bf16(128, 48, 0, 0);
+    const uint32_t img0 = smem_u32(imgbuf);
+    const uint32_t wt = tmem_base + static_cast<uint32_t>(kWCol);
+    uint64_t bdesc[8];
 #pragma unroll
-        for (int t = 0; t < kTilesPerImg; ++t, ++tc) {
-          const int s = tc & (kGroups - 1);
-          mbar_wait_t<SPIN>(&t_empty[s], ((tc >> 2) & 1) ^ 1);
-          tc_fence_after_sync();
-          const uint32_t d = tmem_base + static_cast<uint32_t>(s * kStageCols);
-          const uint32_t bbase = img + t * 96 * 16;
+    for (int st = 0; st < 8; ++st) {
+      bdesc[st] = make_smem_desc_nosw(img0 + step_first_chunk(st) * 16, step_lbo(st), 128);   // + (slot * 512 + t * 96) in the address field
+    }
+    int tc = 0, i = 0;
+    for (int n = blockIdx.x; n < a.B; n += gridDim.x, ++i) {
+      const int slot = i % kSlots;
+      mbar_wait_t<SPIN>(&img_full[slot], (i / kSlots) & 1);
 #pragma unroll
-          for (int st = 0; st < 8; ++st)
-            umma_f16(d, make_smem_desc_sw128(wa + (st >> 2) * 16384 + (st & 3) * 32, 16, 1024),
-                     make_smem_desc_nosw(bbase + step_first_chunk(st) * 16, step_lbo(st), 128), t < 4 ? idesc96 : idesc48, st > 0);
+      for (int t = 0; t < kTilesPerImg; ++t, ++tc) {
+        const int s = tc & (kGroups - 1);
+        mbar_wait_t<SPIN>(&t_empty[s], ((tc >> 2) & 1) ^ 1);
+        tc_fence_after_sync();
+        const uint32_t d = tmem_base + static_cast<uint32_t>(s * kStageCols);
+        const uint64_t boff = static_cast<uint64_t>(slot * (kImgBytes / 16) + t * 96);
+        if (elect_one()) {
+#pragma unroll
+          for (int st = 0; st < 8; ++st) umma_f16_ts(d, wt + st * 8, bdesc[st] + boff, t < 4 ? idesc96 : idesc48, st > 0);
           umma_commit(&t_full[s]);
+          if (t == kTilesPerImg - 1) umma_commit(&img_empty[slot]);
         }
-        umma_commit(&img_empty[slot]);
+        __syncwarp();
       }
     }
-    __syncwarp();
   } else if (warp == 1) {
     // ---------------- loader: one 8 KB bulk copy per image ----------------
     if (elect_one()) {

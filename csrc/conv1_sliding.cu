@@ -143,7 +143,8 @@ struct Conv1sArgs {
 constexpr int kSlots = 8;                     // staged images
 constexpr int kGroups = 4;
 constexpr int kTilesPerImg = 5;
-constexpr int kFwdThreads = 32 * (2 + 4 * kGroups);   // warp 0: MMA + TMEM, warp 1: loader, then the epilogue groups
+constexpr int kIssuers = 2;
+constexpr int kFwdThreads = 32 * (kIssuers + 1 + 4 * kGroups);   // warps 0-1: MMA issuers (even / odd tiles), warp 2: loader, then the epilogue groups
 constexpr int kXchBytes = 18 * kO * 4;        // per epilogue group
 constexpr int kFwdSmem = kSlots * kImgBytes + 2 * kGroups * kXchBytes + 1024;
 constexpr int kStageCols = 96;                // TMEM columns per accumulator stage
@@ -190,7 +191,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1s_fwd_kernel(const Conv1s
   if (threadIdx.x == 0) {
     for (int s = 0; s < kSlots; ++s) {
       mbar_init(&img_full[s], 1);
-      mbar_init(&img_empty[s], 1);
+      mbar_init(&img_empty[s], kIssuers);   // each issuer warp has at least two of the 5 tiles of an image
     }
     for (int s = 0; s < kGroups; ++s) {
       mbar_init(&t_full[s], 1);
@@ -205,7 +206,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1s_fwd_kernel(const Conv1s
   const uint32_t tmem_base = tmem_base_smem;
   // The weight operand lives in tensor memory for the whole kernel: row m = (parity, channel) in lane m, its 128 K
   // values as 64 columns of bf16 pairs.  Written by the first epilogue group (one warp per lane quarter).
-  if (warp >= 2 && warp < 6) {
+  if (warp >= kIssuers + 1 && warp < kIssuers + 5) {
     const int q = warp & 3;
     const uint4* src = reinterpret_cast<const uint4*>(a.w + (q * 32 + lane) * 128);
 #pragma unroll
@@ -224,39 +225,52 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1s_fwd_kernel(const Conv1s
   __syncthreads();
   tc_fence_after_sync();
 
-  if (warp == 0) {
-    // ---------------- MMA issuer ----------------
-    // The whole warp runs the loop (warp-uniform control flow keeps the descriptors in uniform registers); one
-    // elected lane issues.  Descriptor words that do not depend on the tile are built once.
+  if (warp < kIssuers) {
+    // ---------------- MMA issuers ----------------
+    // Warp w issues the tiles tc = w, w + 2, ... (tile t of this CTA's i-th image is tc = 5 i + t, accumulator stage
+    // tc & 3): the 8 MMAs of a tile are 400 cycles of math behind some 70 instructions of waits and descriptor
+    // set-up, more than one warp issues in that time.  The whole warp runs the loop (warp-uniform control flow),
+    // one elected lane issues.  Descriptor words that do not depend on the tile are built once.
     constexpr uint32_t idesc96 = make_idesc_bf16(128, 96, 0, 0), idesc48 = make_idesc_bf16(128, 48, 0, 0);
     const uint32_t img0 = smem_u32(imgbuf);
     const uint32_t wt = tmem_base + static_cast<uint32_t>(kWCol);
     uint64_t bdesc[8];
 #pragma unroll
-    for (int st = 0; st < 8; ++st) {
+    for (int st = 0; st < 8; ++st)
       bdesc[st] = make_smem_desc_nosw(img0 + step_first_chunk(st) * 16, step_lbo(st), 128);   // + (slot * 512 + t * 96) in the address field
-    }
-    int tc = 0, i = 0;
-    for (int n = blockIdx.x; n < a.B; n += gridDim.x, ++i) {
+    const int my_imgs = (a.B - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+    const int my_tiles = my_imgs * kTilesPerImg;
+    int last_i = -1;
+#pragma unroll 1
+    for (int tc = warp; tc < my_tiles; tc += kIssuers) {
+      const int s = tc & (kGroups - 1);
+      const uint32_t d = tmem_base + static_cast<uint32_t>(s * kStageCols);
+      const int i = tc / kTilesPerImg, t = tc - i * kTilesPerImg;
       const int slot = i % kSlots;
-      mbar_wait_t<SPIN>(&img_full[slot], (i / kSlots) & 1);
-#pragma unroll
-      for (int t = 0; t < kTilesPerImg; ++t, ++tc) {
-        const int s = tc & (kGroups - 1);
-        mbar_wait_t<SPIN>(&t_empty[s], ((tc >> 2) & 1) ^ 1);
-        tc_fence_after_sync();
-        const uint32_t d = tmem_base + static_cast<uint32_t>(s * kStageCols);
-        const uint64_t boff = static_cast<uint64_t>(slot * (kImgBytes / 16) + t * 96);
-        if (elect_one()) {
-#pragma unroll
-          for (int st = 0; st < 8; ++st) umma_f16_ts(d, wt + st * 8, bdesc[st] + boff, t < 4 ? idesc96 : idesc48, st > 0);
-          umma_commit(&t_full[s]);
-          if (t == kTilesPerImg - 1) umma_commit(&img_empty[slot]);
-        }
+      if (i != last_i) {
+        if (last_i >= 0 && elect_one()) umma_commit(&img_empty[last_i % kSlots]);   // this warp's MMAs on that image are all issued
         __syncwarp();
+        mbar_wait_t<SPIN>(&img_full[slot], (i / kSlots) & 1);
+        last_i = i;
       }
+      mbar_wait_t<SPIN>(&t_empty[s], ((tc >> 2) & 1) ^ 1);
+      tc_fence_after_sync();
+      const uint64_t boff = static_cast<uint64_t>(slot * (kImgBytes / 16) + t * 96);
+      if (elect_one()) {
+        if (t < 4) {
+#pragma unroll
+          for (int st = 0; st < 8; ++st) umma_f16_ts(d, wt + st * 8, bdesc[st] + boff, idesc96, st > 0);
+        } else {
+#pragma unroll
+          for (int st = 0; st < 8; ++st) umma_f16_ts(d, wt + st * 8, bdesc[st] + boff, idesc48, st > 0);
+        }
+        umma_commit(&t_full[s]);
+      }
+      __syncwarp();
     }
-  } else if (warp == 1) {
+    if (last_i >= 0 && elect_one()) umma_commit(&img_empty[last_i % kSlots]);
+    __syncwarp();
+  } else if (warp == kIssuers) {
     // ---------------- loader: one 8 KB bulk copy per image ----------------
     if (elect_one()) {
       int i = 0;
@@ -273,7 +287,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1s_fwd_kernel(const Conv1s
     __syncwarp();
   } else {
     // ---------------- epilogue: pooling in registers, parity merge through shared memory ----------------
-    const int grp = (warp - 2) >> 2;
+    const int grp = (warp - kIssuers - 1) >> 2;
     const int q = warp & 3;                  // TMEM lane quarter
     const int par = q >> 1;                  // column parity of this thread's accumulator row
     const int ch = (q & 1) * 32 + lane;

@@ -362,6 +362,242 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1s_fwd_kernel(const Conv1s
   }
 }
 
+// ======================================= backward =======================================
+//   D_j[(par, ch), (kh', p, c)] += sum over positions r = (h, q) of  dY[(par, ch), r] * x[r + 16 kh' + j][p][c]      j = 0, 1, 2
+// and dW[ch][c][kh][kw] = sum over (par, j, p) with 2 j + p - par == kw of D_j[(par, ch), (kh, p, c)];  channel c = 3 is the
+// constant 1.0, so its tap (kh, kw) = (0, 0) is the bias gradient.
+//   A = dY^T, in TENSOR MEMORY: lane (par, ch), K = the 16 pair positions of one conv row = 8 columns of bf16 pairs,
+//       written with tcgen05.st by the thread of that lane from (dp1, idx1): the pooled gradient goes to the window's
+//       arg-max position when the window is alive and that position has this lane's column parity.
+//   B = the staged image, MN-major no-swizzle: N = (kh' = 0..5, 8 elements of a pair chunk) with the kh' groups one
+//       image row (SBO = 256 B) apart, K = 16 positions at a 16-byte pitch (8-position groups LBO = 128 B apart);
+//       kh' = 5 is read (N must be a multiple of 16) and ignored.
+// One K step = one conv row, 3 MMAs (j = 0, 1, 2; M = 128, N = 48) into three accumulators that live for the whole
+// kernel; pooled row = 3 conv rows = one 24-column slot of a 14-slot operand ring in tensor memory.
+constexpr int kXS = 4;                         // staged images (B operand)
+constexpr int kGS = 4;                         // staged (dp1, idx1) images
+constexpr int kGIdxOff = 81 * kO * 2;          // 10368: idx1 part of a gradient slot
+constexpr int kGSlotBytes = 15616;             // 10368 + 5184 = 15552, rounded up to a multiple of 128
+constexpr int kDStride = 64;                   // accumulator j: columns 64 j .. 64 j + 47
+constexpr int kASlots = 14, kASlotCols = 24;
+constexpr int kACol0 = 176;                    // operand ring: columns 176 .. 511
+static_assert(kACol0 + kASlots * kASlotCols <= 512, "operand ring exceeds tensor memory");
+constexpr int kBGroups = 4;
+constexpr int kBwdThreads = 32 * (2 + 4 * kBGroups);   // warp 0: MMA issuer + TMEM, warp 1: loader, then the builder groups
+constexpr int kBwdSmem = kXS * kImgBytes + 128 + kGS * kGSlotBytes + 64 * 77 * 4 + 1024;
+
+__device__ __forceinline__ void tmem_st_32x32b_x8(uint32_t taddr, const uint32_t* r) {
+  asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%8], {%0, %1, %2, %3, %4, %5, %6, %7};" ::"r"(r[0]), "r"(r[1]), "r"(r[2]),
+               "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(taddr)
+               : "memory");
+}
+__device__ __forceinline__ uint32_t lds_u16(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u16 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u8(uint32_t addr) {
+  uint32_t v;
+  asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src), "r"(bytes),
+               "r"(smem_u32(bar))
+               : "memory");
+}
+
+// One conv row (I = 0..2 of the pooled row) of dY^T for column parity PAR: 8 words of bf16 pairs (positions 2k, 2k+1).
+template <int PAR, int I, int K2>
+__device__ __forceinline__ uint32_t dy_word(const uint32_t (&g)[9], const uint32_t (&cd)[9]) {
+  // position q = 2 K2 + h  <->  column w = 2 q + PAR, window pw = w / 3, window position I * 3 + w % 3
+  uint32_t half[2];
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const int q = 2 * K2 + h, w = 2 * q + PAR;
+    if (w <= 26) half[h] = (cd[w / 3] == static_cast<uint32_t>(8 - (I * 3 + w % 3))) ? g[w / 3] : 0u;
+    else half[h] = 0u;
+  }
+  return half[0] | (half[1] << 16);
+}
+template <int PAR, int I>
+__device__ __forceinline__ void dy_row(const uint32_t (&g)[9], const uint32_t (&cd)[9], uint32_t (&r)[8]) {
+  r[0] = dy_word<PAR, I, 0>(g, cd); r[1] = dy_word<PAR, I, 1>(g, cd); r[2] = dy_word<PAR, I, 2>(g, cd); r[3] = dy_word<PAR, I, 3>(g, cd);
+  r[4] = dy_word<PAR, I, 4>(g, cd); r[5] = dy_word<PAR, I, 5>(g, cd); r[6] = dy_word<PAR, I, 6>(g, cd); r[7] = 0u;
+}
+
+__global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1sArgs a) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  uint8_t* ximg = smem;                                   // kXS images (+128 B of zeros: kh' = 5 of the last rows reads past the last one)
+  uint8_t* gbuf = smem + kXS * kImgBytes + 128;           // kGS x (dp1 rows | idx1 rows)
+  float* red = reinterpret_cast<float*>(gbuf + kGS * kGSlotBytes);   // [64][77] final reduction
+  __shared__ __align__(8) uint64_t x_full[kXS], x_empty[kXS], g_full[kGS], g_empty[kGS], a_full[kASlots], a_empty[kASlots], done_bar;
+  __shared__ uint32_t tmem_base_smem;
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int rows = a.rows;
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kXS; ++s) { mbar_init(&x_full[s], 1); mbar_init(&x_empty[s], 1); }
+    for (int s = 0; s < kGS; ++s) { mbar_init(&g_full[s], 1); mbar_init(&g_empty[s], static_cast<uint32_t>(rows * 128)); }
+    for (int s = 0; s < kASlots; ++s) { mbar_init(&a_full[s], 128); mbar_init(&a_empty[s], 1); }
+    mbar_init(&done_bar, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) tmem_alloc<512>(&tmem_base_smem);
+  if (threadIdx.x < 32) reinterpret_cast<uint32_t*>(ximg + kXS * kImgBytes)[threadIdx.x] = 0u;
+  fence_proxy_async_smem();
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = tmem_base_smem;
+  const int my_imgs = (a.B - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+
+  if (warp == 0) {
+    // ---------------- MMA issuer (whole warp in the loop, one elected lane issues) ----------------
+    constexpr uint32_t idesc = make_idesc_bf16(128, 48, 0, 1);
+    const uint32_t x0 = smem_u32(ximg);
+    const uint64_t bdesc0 = make_smem_desc_nosw(x0, 128, 256);   // MN-major no-swizzle: LBO = next 8 K rows, SBO = next 8 N elements
+    const uint32_t acol = tmem_base + static_cast<uint32_t>(kACol0);
+    int slot = 0, sph = 0;     // operand ring position and phase
+#pragma unroll 1
+    for (int i = 0; i < my_imgs; ++i) {
+      const int xs = i % kXS;
+      mbar_wait_t<true>(&x_full[xs], (i / kXS) & 1);
+      const uint64_t bimg = bdesc0 + static_cast<uint64_t>(xs * (kImgBytes / 16));
+#pragma unroll
+      for (int pr = 0; pr < 9; ++pr) {
+        if (pr < rows) {
+          mbar_wait_t<true>(&a_full[slot], sph);
+          tc_fence_after_sync();
+          const uint32_t at = acol + static_cast<uint32_t>(slot * kASlotCols);
+          if (elect_one()) {
+#pragma unroll
+            for (int r = 0; r < 3; ++r)
+#pragma unroll
+              for (int j = 0; j < 3; ++j)
+                umma_f16_ts(tmem_base + static_cast<uint32_t>(j * kDStride), at + r * 8, bimg + static_cast<uint64_t>((3 * pr + r) * kPairsPerRow + j), idesc,
+                            (i > 0 || pr > 0 || r > 0) ? 1u : 0u);
+            umma_commit(&a_empty[slot]);
+          }
+          __syncwarp();
+          if (++slot == kASlots) { slot = 0; sph ^= 1; }
+        }
+      }
+      if (elect_one()) umma_commit(&x_empty[xs]);
+      __syncwarp();
+    }
+    if (elect_one()) umma_commit(&done_bar);
+    __syncwarp();
+  } else if (warp == 1) {
+    // ---------------- loader: image, dp1 rows and idx1 rows of one sample per step ----------------
+    if (elect_one()) {
+      const uint32_t gbytes = static_cast<uint32_t>(rows * 9 * kO * 2), ibytes = static_cast<uint32_t>(rows * 9 * kO);
+      for (int i = 0; i < my_imgs; ++i) {
+        const long long n = static_cast<long long>(blockIdx.x) + static_cast<long long>(i) * gridDim.x;
+        const int xs = i % kXS, gs = i % kGS;
+        mbar_wait(&g_empty[gs], ((i / kGS) & 1) ^ 1);
+        mbar_arrive_expect_tx(&g_full[gs], gbytes + ibytes);
+        bulk_g2s(smem_u32(gbuf + gs * kGSlotBytes), a.dp1 + n * (kWinPerImg * kO), gbytes, &g_full[gs]);
+        bulk_g2s(smem_u32(gbuf + gs * kGSlotBytes + kGIdxOff), a.idx1 + n * (kWinPerImg * kO), ibytes, &g_full[gs]);
+        mbar_wait(&x_empty[xs], ((i / kXS) & 1) ^ 1);
+        mbar_arrive_expect_tx(&x_full[xs], kImgBytes);
+        bulk_g2s(smem_u32(ximg + xs * kImgBytes), a.x + n * (kImgBytes / 2), kImgBytes, &x_full[xs]);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ---------------- builders: dY^T of one pooled row (3 conv rows) per step, straight into tensor memory ----------------
+    const int grp = (warp - 2) >> 2;
+    const int q = warp & 3;
+    const int par = q >> 1;
+    const int ch = (q & 1) * 32 + lane;
+    const uint32_t g0 = smem_u32(gbuf) + static_cast<uint32_t>(ch * 2), i0 = smem_u32(gbuf) + static_cast<uint32_t>(kGIdxOff + ch);
+    const uint32_t arow = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(kACol0);
+    const int chunks = my_imgs * rows;
+#pragma unroll 1
+    for (int cg = grp; cg < chunks; cg += kBGroups) {
+      const int i = cg / rows, pr = cg - i * rows;
+      const int gs = i % kGS;
+      const int slot = cg % kASlots;
+      mbar_wait(&g_full[gs], (i / kGS) & 1);
+      uint32_t g[9], cd[9];
+      const uint32_t goff = static_cast<uint32_t>(gs * kGSlotBytes + pr * 9 * kO * 2), ioff = static_cast<uint32_t>(gs * kGSlotBytes + pr * 9 * kO);
+#pragma unroll
+      for (int pw = 0; pw < 9; ++pw) {
+        g[pw] = lds_u16(g0 + goff + pw * (kO * 2));
+        cd[pw] = lds_u8(i0 + ioff + pw * kO);
+      }
+      mbar_arrive(&g_empty[gs]);
+      uint32_t r0[8], r1[8], r2[8];
+      if (par == 0) { dy_row<0, 0>(g, cd, r0); dy_row<0, 1>(g, cd, r1); dy_row<0, 2>(g, cd, r2); }
+      else { dy_row<1, 0>(g, cd, r0); dy_row<1, 1>(g, cd, r1); dy_row<1, 2>(g, cd, r2); }
+      mbar_wait(&a_empty[slot], ((cg / kASlots) & 1) ^ 1);
+      tc_fence_after_sync();
+      const uint32_t at = arow + static_cast<uint32_t>(slot * kASlotCols);
+      tmem_st_32x32b_x8(at, r0);
+      tmem_st_32x32b_x8(at + 8, r1);
+      tmem_st_32x32b_x8(at + 16, r2);
+      tmem_st_wait();
+      tc_fence_before_sync();
+      mbar_arrive(&a_full[slot]);
+    }
+    // ---------------- final reduction (first builder group): accumulators -> gw, gb ----------------
+    if (grp == 0 && my_imgs > 0) {
+      mbar_wait(&done_bar, 0);
+      tc_fence_after_sync();
+      const uint32_t drow = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+      // red[ch][k], k = Torch7 index (c*5+kh)*5+kw for k < 75, k = 75: bias.  Parity 0 writes, then parity 1 adds.
+#pragma unroll 1
+      for (int pass = 0; pass < 2; ++pass) {
+        if (pass == par) {
+#pragma unroll
+          for (int j = 0; j < 3; ++j) {
+            uint32_t v[48];
+            tmem_ld_32x32b_x32(drow + j * kDStride, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+            tmem_ld_32x32b_x16(drow + j * kDStride + 32, &v[32]);
+            tmem_ld_wait();
+#pragma unroll
+            for (int kh = 0; kh < 5; ++kh)
+#pragma unroll
+              for (int e = 0; e < 8; ++e) {
+                const int p = e >> 2, c = e & 3;
+                const float val = __uint_as_float(v[kh * 8 + e]);
+                if (par == 0) {
+                  const int kw = 2 * j + p;
+                  if (kw <= 4) {
+                    if (c < 3) red[ch * 77 + (c * 5 + kh) * 5 + kw] = val;
+                    else if (kh == 0 && kw == 0) red[ch * 77 + 75] = val;
+                  }
+                } else {
+                  const int kw = 2 * j + p - 1;
+                  if (kw >= 0 && kw <= 4) {
+                    if (c < 3) red[ch * 77 + (c * 5 + kh) * 5 + kw] += val;
+                    else if (kh == 0 && kw == 0) red[ch * 77 + 75] += val;
+                  }
+                }
+              }
+          }
+        }
+        asm volatile("bar.sync 2, 128;" ::: "memory");
+      }
+      const int t = threadIdx.x - 64;
+      for (int e = t; e < kO * 76; e += 128) {
+        const int c2 = e / 76, k = e - c2 * 76;
+        const float val = red[c2 * 77 + k];
+        if (k < kK) atomicAdd(a.gw + c2 * kK + k, val);
+        else if (a.gb != nullptr) atomicAdd(a.gb + c2, val);
+      }
+    }
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after_sync();
+    tmem_dealloc<512>(tmem_base);
+  }
+}
+
 // Torch7 weight [64, 75] fp32 (k = (c*5+kh)*5+kw) + bias [64]  ->  bf16 [128, 128]
 __global__ void conv1s_weight_pack_kernel(const float* __restrict__ w, const float* __restrict__ bias, __nv_bfloat16* __restrict__ wp) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -442,17 +678,33 @@ extern "C" int tadnn_conv1s_pool_forward(const void* x_nhwc4, const void* w_pack
   TADNN_REQUIRE(B > 0 && B <= 20000000, "conv1s_pool_forward: batch %d out of range", B);
   TADNN_REQUIRE(((reinterpret_cast<uintptr_t>(x_nhwc4) | reinterpret_cast<uintptr_t>(w_packed)) & 15) == 0,
                 "conv1s_pool_forward: operands must be 16-byte aligned");
-  static std::atomic<unsigned long long> attr{0}, attr_s{0};
-  if (int rc = ensure_dyn_smem(conv1s_fwd_kernel<false>, kFwdSmem, attr)) return rc;
-  if (int rc = ensure_dyn_smem(conv1s_fwd_kernel<true>, kFwdSmem, attr_s)) return rc;
-  static const bool spin = getenv("TADNN_CONV1S_NOSPIN") == nullptr;
+  static std::atomic<unsigned long long> attr{0};
+  if (int rc = ensure_dyn_smem(conv1s_fwd_kernel<true>, kFwdSmem, attr)) return rc;
   Conv1sArgs a;
   memset(&a, 0, sizeof(a));
   a.x = static_cast<const __nv_bfloat16*>(x_nhwc4); a.w = static_cast<const __nv_bfloat16*>(w_packed);
   a.p1 = static_cast<__nv_bfloat16*>(p1); a.idx1 = static_cast<unsigned char*>(idx1); a.B = B;
   const int grid = B < sm_count() ? B : sm_count();
-  if (spin) conv1s_fwd_kernel<true><<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
-  else conv1s_fwd_kernel<false><<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
+  conv1s_fwd_kernel<true><<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
   TADNN_LAUNCH_CHECK("conv1s_pool_fwd_tcgen05");
+  return 0;
+}
+
+extern "C" int tadnn_conv1s_pool_backward(const void* x_nhwc4, const void* dp1, const void* idx1, float* grad_weight, float* grad_bias,
+                                          int rows, int B, tadnn_stream_t stream) {
+  TADNN_REQUIRE(B > 0 && B <= 20000000, "conv1s_pool_backward: batch %d out of range", B);
+  TADNN_REQUIRE(rows >= 1 && rows <= 9, "conv1s_pool_backward: %d pooled rows (1..9)", rows);
+  TADNN_REQUIRE(((reinterpret_cast<uintptr_t>(x_nhwc4) | reinterpret_cast<uintptr_t>(dp1) | reinterpret_cast<uintptr_t>(idx1)) & 15) == 0,
+                "conv1s_pool_backward: operands must be 16-byte aligned");
+  static std::atomic<unsigned long long> attr{0};
+  if (int rc = ensure_dyn_smem(conv1s_bwd_kernel, kBwdSmem, attr)) return rc;
+  Conv1sArgs a;
+  memset(&a, 0, sizeof(a));
+  a.x = static_cast<const __nv_bfloat16*>(x_nhwc4); a.dp1 = static_cast<const __nv_bfloat16*>(dp1);
+  a.idx1 = const_cast<unsigned char*>(static_cast<const unsigned char*>(idx1));
+  a.gw = grad_weight; a.gb = grad_bias; a.B = B; a.rows = rows;
+  const int grid = B < sm_count() ? B : sm_count();
+  conv1s_bwd_kernel<<<grid, kBwdThreads, kBwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
+  TADNN_LAUNCH_CHECK("conv1s_pool_bwd_tcgen05");
   return 0;
 }

@@ -354,6 +354,12 @@ int tadnn_nhwc4_pack(const void* x, int src_dtype, void* y, long long B, const f
 int tadnn_conv1s_weight_pack(const float* w, const float* bias, void* w_packed, tadnn_stream_t stream);
 int tadnn_conv1s_pool_forward(const void* x_nhwc4, const void* w_packed, void* p1, void* idx1, int B,
                               tadnn_stream_t stream);
+/* grad_weight[64,75] (Torch7 layout) and grad_bias[64] (may be NULL) += the conv1 gradients for the pooled gradient
+ * dp1 [B,9,9,64] bf16 and the idx1 written by tadnn_conv1s_pool_forward; only pooled rows 0..rows-1 of dp1 are read
+ * (7 for the example CNN: conv2 + pool2 never touch the last two).  d(conv out) is rebuilt in tensor memory and is the
+ * A operand of the MMAs; the B operand is the staged image. */
+int tadnn_conv1s_pool_backward(const void* x_nhwc4, const void* dp1, const void* idx1, float* grad_weight,
+                               float* grad_bias, int rows, int B, tadnn_stream_t stream);
 
 /* Fused classifier head: dropout -> Linear(D,H)+ReLU -> Linear(H,NC) -> log-softmax -> NLL.
  * Limits: D <= 64, H <= 128, NC <= 32.  fc weights in Torch7 nn.Linear layout, fp32. */

@@ -57,3 +57,42 @@ def test_conv1s_forward_matches_pytorch(B):
     p_old, idx_old = K.conv1_pool_forward(x, K.conv1_weight_pack(w), b)
     assert (p1.float() - p_old.float()).abs().max().item() <= 0.02 * max(1.0, p_ref.abs().max().item())
     assert ((pos == idx_old.long()) | (p_old <= 0)).float().mean().item() > 0.995
+
+
+def _ref_backward(x, dp1, idx1, rows):
+    """dW, db of conv1 for d(conv out) rebuilt from (dp1, idx1) in plain PyTorch fp32."""
+    B = x.shape[0]
+    dy = torch.zeros(B, 64, 28, 28, device=x.device)
+    g = dp1.float().clone()
+    g[:, rows:] = 0
+    pos = 8 - idx1.long()
+    alive = idx1 != 15
+    py = torch.arange(9, device=x.device).view(1, 9, 1, 1).expand(B, 9, 9, 64)
+    px = torch.arange(9, device=x.device).view(1, 1, 9, 1).expand(B, 9, 9, 64)
+    oy, ox = 3 * py + pos // 3, 3 * px + pos % 3
+    n = torch.arange(B, device=x.device).view(B, 1, 1, 1).expand(B, 9, 9, 64)
+    c = torch.arange(64, device=x.device).view(1, 1, 1, 64).expand(B, 9, 9, 64)
+    dy[n[alive], c[alive], oy[alive], ox[alive]] = g[alive]
+    gw = torch.nn.grad.conv2d_weight(x.float(), (64, 3, 5, 5), dy)
+    return gw.reshape(64, 75), dy.sum(dim=(0, 2, 3))
+
+
+@pytest.mark.parametrize("B,rows", [(1, 9), (2, 7), (150, 7), (333, 9)])
+def test_conv1s_backward_matches_pytorch(B, rows):
+    from tadnn.ops import cnn as K
+    torch.manual_seed(B)
+    x = torch.randn(B, 3, 32, 32, device="cuda").bfloat16()
+    w = torch.randn(64, 75, device="cuda") * 0.2
+    b = torch.randn(64, device="cuda") * 0.1
+    xq = K.nhwc4_pack(x)
+    p1, idx1 = K.conv1s_pool_forward(xq, K.conv1s_weight_pack(w, b))
+    dp1 = torch.randn(B, 9, 9, 64, device="cuda").bfloat16()
+    gw = torch.full((64, 75), 0.5, device="cuda")
+    gb = torch.full((64,), -0.25, device="cuda")
+    K.conv1s_pool_backward(xq, dp1, idx1, gw, gb, rows=rows)
+    gw_ref, gb_ref = _ref_backward(x, dp1, idx1, rows)
+    assert ((gw - 0.5 - gw_ref).norm() / gw_ref.norm()).item() < 2e-3
+    assert ((gb + 0.25 - gb_ref).norm() / gb_ref.norm()).item() < 2e-3
+    # accumulates: a second call doubles the increment
+    K.conv1s_pool_backward(xq, dp1, idx1, gw, gb, rows=rows)
+    assert ((gw - 0.5 - 2 * gw_ref).norm() / gw_ref.norm()).item() < 4e-3

@@ -65,6 +65,23 @@ def main():
         err = (p1.float() - r).abs()
         print(f"B={Bn}: max err {err.max().item():.4f} frac>1e-6 {(err > 1e-6).float().mean().item():.5f} "
               f"by pooled row {[round(v, 3) for v in err.amax(dim=(0, 2, 3)).tolist()]}")
+    if hasattr(K, "conv1s_pool_backward"):
+        sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests"))
+        from test_gpu_conv1_sliding import _ref_backward
+        for Bn, rows in ((1, 9), (3, 7), (200, 7)):
+            x = torch.randn(Bn, 3, 32, 32, device=dev).bfloat16()
+            w = torch.randn(64, 75, device=dev) * 0.2
+            b = torch.randn(64, device=dev) * 0.1
+            xq = K.nhwc4_pack(x)
+            p1, idx1 = K.conv1s_pool_forward(xq, K.conv1s_weight_pack(w, b))
+            dp1 = torch.randn(Bn, 9, 9, 64, device=dev).bfloat16()
+            gw, gb = torch.zeros(64, 75, device=dev), torch.zeros(64, device=dev)
+            K.conv1s_pool_backward(xq, dp1, idx1, gw, gb, rows=rows)
+            gw_ref, gb_ref = _ref_backward(x, dp1, idx1, rows)
+            e = (gw - gw_ref).view(64, 3, 5, 5)
+            print(f"bwd B={Bn} rows={rows}: rel gw {((gw - gw_ref).norm() / gw_ref.norm()).item():.5f} rel gb {((gb - gb_ref).norm() / gb_ref.norm()).item():.5f}"
+                  f" | err by kh {[round(v, 3) for v in e.abs().amax(dim=(0, 1, 3)).tolist()]} by kw {[round(v, 3) for v in e.abs().amax(dim=(0, 1, 2)).tolist()]}"
+                  f" by c {[round(v, 3) for v in e.abs().amax(dim=(0, 2, 3)).tolist()]} ref max {gw_ref.abs().max().item():.2f}")
     Bn = 4096
     x = torch.randn(Bn, 3, 32, 32, device=dev).bfloat16()
     xu = torch.randint(0, 256, (Bn, 3, 32, 32), device=dev, dtype=torch.uint8)

@@ -258,11 +258,22 @@ def conv1s_pool_forward(xq: torch.Tensor, wx: torch.Tensor):
     return p1, idx1
 
 
+def conv1s_pool_backward(xq, dp1, idx1, grad_weight, grad_bias=None, rows: int = 9):
+    """grad_weight [64,75] (+ grad_bias [64]) += conv1 gradients from dp1 [B,9,9,64] bf16 (pooled rows < ``rows`` are read)
+    and the idx1 of conv1s_pool_forward."""
+    assert dp1.dtype == torch.bfloat16 and dp1.is_contiguous() and tuple(dp1.shape[1:]) == (9, 9, 64)
+    assert idx1.dtype == torch.uint8 and idx1.is_contiguous() and xq.is_contiguous()
+    _native.check(_native.lib().tadnn_conv1s_pool_backward(_p(xq), _p(dp1), _p(idx1), _p(grad_weight),
+                                                           _p(grad_bias) if grad_bias is not None else None, int(rows),
+                                                           xq.shape[0], _s()), "tadnn_conv1s_pool_backward")
+    return grad_weight
+
+
 def auto_split_k(M: int, N: int, K: int, tile_n: int = 256) -> int:
     tiles = ((M + 127) // 128) * ((N + tile_n - 1) // tile_n)
     kb = (K + 63) // 64
     return max(1, min(kb, 148 // max(1, tiles)))
 
 
-__all__ = ["nhwc4_pack", "conv1s_weight_pack", "conv1s_pool_forward", "u8_to_bf16", "conv2_pool_forward", "conv2_wgrad", "conv2_wgrad_unpack", "cnn_pack_shadows", "conv1_pool_backward_bias", "im2col_winfirst", "conv_toeplitz_pack", "expand_corner", "conv1_weight_pack", "conv1_pool_forward", "conv1_pool_backward", "im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "colsum_relu_mask_corner", "conv_weight_pack",
+__all__ = ["nhwc4_pack", "conv1s_weight_pack", "conv1s_pool_forward", "conv1s_pool_backward", "u8_to_bf16", "conv2_pool_forward", "conv2_wgrad", "conv2_wgrad_unpack", "cnn_pack_shadows", "conv1_pool_backward_bias", "im2col_winfirst", "conv_toeplitz_pack", "expand_corner", "conv1_weight_pack", "conv1_pool_forward", "conv1_pool_backward", "im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "colsum_relu_mask_corner", "conv_weight_pack",
            "conv_wgrad_unpack", "head_workspace", "sgd_step", "auto_split_k", "HeadArgs", "gemm_bf16"]

@@ -58,6 +58,8 @@ def parse():
     ap.add_argument("--no-baseline", action="store_true", help="skip the in-process comparator arm")
     ap.add_argument("--no-extra", action="store_true", help="skip the MP-MLP / all-reduce-sweep block (N > 1)")
     ap.add_argument("--extra-steps", type=int, default=10)
+    ap.add_argument("--conv1", default="sliding", choices=["sliding", "rows"],
+                    help="fused conv1 kernels: the staged NHWC4 image as the tensor-core operand, or im2col rows built in shared memory")
     ap.add_argument("--conv2", default="dense", choices=["dense", "pooled", "legacy"],
                     help="conv2 forward: all 5x5 output pixels (reference behaviour) or only the 3x3 that pool2 reads")
     return ap.parse_args()
@@ -177,12 +179,13 @@ def main():
 
     # ================================ tadnn arm ================================
     if a.impl == "tadnn":
-        model = CifarCNN(conv2_mode=a.conv2).to(dev)
+        model = CifarCNN(conv2_mode=a.conv2, conv1_kernel=a.conv1).to(dev)
         d, t, n = tadnn.parallelize(data, labels, model, total, h, None, 1, verbose=False)
         assert n == B * nb
         trainer = tadnn.BatchTrainer(model, learningRate=a.lr)
-        # device-resident pool for the kernel-path number: 8 x 25 MB of bf16 (> L2), widened once
-        d_dev = u8_to_bf16(d.to(dev), 1024, 3, *AFFINE)
+        # device-resident pool for the kernel-path number: 8 batches (> L2), widened once into the model's input layout
+        # (NHWC4 bf16 for the sliding-operand conv1: 33.5 MB per batch; plain NCHW bf16, 25 MB, otherwise)
+        d_dev = model.pack_input(d.to(dev), AFFINE) if model.packs_input else u8_to_bf16(d.to(dev), 1024, 3, *AFFINE)
         t_dev = t.to(dev)
         torch.cuda.synchronize()
         sampler = ClockSampler(torch.cuda.current_device()).start() if rank == 0 else None
@@ -198,7 +201,8 @@ def main():
             e2e = {"value": a.steps * B * P / (ms2 / 1e3), "unit": "samples/s",
                    "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
                    "ms_per_step": ms2 / a.steps, "last_loss": last,
-                   "input": "uint8 images + int64 labels from pinned host memory, widened to bf16 on the device (tadnn_u8_to_bf16)"}
+                   "input": "uint8 images + int64 labels from pinned host memory, widened to bf16 on the device "
+                            + ("(tadnn_nhwc4_pack)" if model.packs_input else "(tadnn_u8_to_bf16)")}
         if sampler:
             sampler.stop()
         value = a.steps * B * P / (ms / 1e3)
@@ -210,8 +214,8 @@ def main():
             "config": {"model": MODEL, "global_batch": B * P, "per_gpu_batch": B, "seq_len": None,
                        "input": "3x32x32 (uint8 on the host, bf16 on the device)", "parallelism": f"dp{P}",
                        "sync": "params+grads all-reduce-average every step (batchSize=1)",
-                       "conv2_forward": a.conv2, "optimizer": "SGD",
-                       "l2_policy": f"inputs cycle through {nb} device batches = {nb * B * 3072 * 2 / 1e6:.0f} MB per GPU (> 126 MB L2)",
+                       "conv1_kernel": a.conv1, "conv2_forward": a.conv2, "optimizer": "SGD",
+                       "l2_policy": f"inputs cycle through {nb} device batches = {nb * d_dev[0].numel() * B * 2 / 1e6:.0f} MB per GPU (> 126 MB L2)",
                        "vs_baseline_denominator": "BASELINE.md row b1 (PyTorch+cuDNN+NCCL restatement, round-1 measurement at this N)"},
             "clocks": sampler.summary() if sampler else None,
             "gpu_launches": launches,

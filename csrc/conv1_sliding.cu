@@ -28,6 +28,7 @@
 // through a shared exchange.  "accumulator | (8 - window position)" keys make max + first-arg-max one integer max.
 #include "common.cuh"
 #include "sm100.cuh"
+#include "conv1s_pack.cuh"
 #include <stdlib.h>
 
 #include <utility>
@@ -601,25 +602,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
 // Torch7 weight [64, 75] fp32 (k = (c*5+kh)*5+kw) + bias [64]  ->  bf16 [128, 128]
 __global__ void conv1s_weight_pack_kernel(const float* __restrict__ w, const float* __restrict__ bias, __nv_bfloat16* __restrict__ wp) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= 128 * 128) return;
-  const int m = i >> 7, k = i & 127;
-  const int par = m >> 6, ch = m & 63;
-  const int st = k >> 4, half = (k >> 3) & 1, e = k & 7;
-  int kh, j;
-  if (st < 5) { kh = st; j = half; }
-  else if (st == 5) { kh = half; j = 2; }
-  else if (st == 6) { kh = 2 + half; j = 2; }
-  else { kh = 4; j = half ? -1 : 2; }
-  float v = 0.f;
-  if (j >= 0) {
-    const int p = e >> 2, c = e & 3;
-    const int kw = 2 * j + p - par;
-    if (kw >= 0 && kw <= 4) {
-      if (c < 3) v = w[ch * kK + (c * 5 + kh) * 5 + kw];
-      else if (kh == 0 && kw == 0) v = bias[ch];
-    }
-  }
-  wp[i] = __float2bfloat16_rn(v);
+  if (i < 128 * 128) wp[i] = __float2bfloat16_rn(conv1s_weight_value(w, bias, i));
 }
 
 // NCHW {uint8, bf16, fp32} [B, 3, 32, 32] -> NHWC4 bf16 [B, 32, 32, 4]: y = x * scale[c] + shift[c], channel 3 = 1.0

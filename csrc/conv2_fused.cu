@@ -16,6 +16,7 @@
 // weight gradient, whose reduction dimension is (image, window pixel).
 #include "common.cuh"
 #include "sm100.cuh"
+#include "conv1s_pack.cuh"
 
 namespace tadnn {
 namespace {
@@ -346,13 +347,16 @@ constexpr int kTtRows = kWin * kWin * kO;        // 576
 constexpr int kTtFH = 7, kTtFW = 9;
 constexpr int kTtCols = kTtFH * kTtFW * kC;      // 4032
 
-__global__ void __launch_bounds__(256) cnn_pack_shadows_kernel(const float* __restrict__ w1, const float* __restrict__ w2,
+// b1 != nullptr: w1p is the [128, 128] operand of the sliding-operand conv1 (bias folded in), else the [64, 80] patch-row one
+__global__ void __launch_bounds__(256) cnn_pack_shadows_kernel(const float* __restrict__ w1, const float* __restrict__ b1, const float* __restrict__ w2,
                                                                __nv_bfloat16* __restrict__ w1p, __nv_bfloat16* __restrict__ w2p,
                                                                uint4* __restrict__ Tt) {
-  const int n_w1 = 64 * 80, n_w2 = kO * kTaps * kC / 8, n_t = kTtRows * kTtCols / 8;
+  const int n_w1 = b1 ? 128 * 128 : 64 * 80, n_w2 = kO * kTaps * kC / 8, n_t = kTtRows * kTtCols / 8;
   const int total = n_w1 + n_w2 + n_t;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
-    if (i < n_w1) {
+    if (i < n_w1 && b1) {
+      w1p[i] = __float2bfloat16_rn(conv1s_weight_value(w1, b1, i));
+    } else if (i < n_w1) {
       const int o = i / 80, k = i % 80;
       float v = 0.f;
       if (k < 75) {
@@ -476,7 +480,19 @@ extern "C" int tadnn_cnn_pack_shadows(const float* w1, const float* w2, void* w1
   TADNN_REQUIRE(((reinterpret_cast<uintptr_t>(w2_packed) | reinterpret_cast<uintptr_t>(toeplitz_t)) & 15) == 0, "cnn_pack_shadows: outputs must be 16-byte aligned");
   const int total = 64 * 80 + kO * kTaps * kC / 8 + kTtRows * kTtCols / 8;
   cnn_pack_shadows_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-      w1, w2, static_cast<__nv_bfloat16*>(w1_packed), static_cast<__nv_bfloat16*>(w2_packed), static_cast<uint4*>(toeplitz_t));
+      w1, nullptr, w2, static_cast<__nv_bfloat16*>(w1_packed), static_cast<__nv_bfloat16*>(w2_packed), static_cast<uint4*>(toeplitz_t));
+  TADNN_LAUNCH_CHECK("cnn_pack_shadows");
+  return 0;
+}
+
+extern "C" int tadnn_cnn_pack_shadows_sliding(const float* w1, const float* b1, const float* w2, void* w1x_packed, void* w2_packed,
+                                              void* toeplitz_t, tadnn_stream_t stream_) {
+  TADNN_REQUIRE(w1 && b1 && w2 && w1x_packed && w2_packed && toeplitz_t, "cnn_pack_shadows_sliding: null argument");
+  TADNN_REQUIRE(((reinterpret_cast<uintptr_t>(w2_packed) | reinterpret_cast<uintptr_t>(toeplitz_t) | reinterpret_cast<uintptr_t>(w1x_packed)) & 15) == 0,
+                "cnn_pack_shadows_sliding: outputs must be 16-byte aligned");
+  const int total = 128 * 128 + kO * kTaps * kC / 8 + kTtRows * kTtCols / 8;
+  cnn_pack_shadows_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      w1, b1, w2, static_cast<__nv_bfloat16*>(w1x_packed), static_cast<__nv_bfloat16*>(w2_packed), static_cast<uint4*>(toeplitz_t));
   TADNN_LAUNCH_CHECK("cnn_pack_shadows");
   return 0;
 }

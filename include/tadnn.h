@@ -332,6 +332,9 @@ int tadnn_conv2_wgrad(const void* p1, const void* da2w, float* dw_packed, int B,
 int tadnn_conv2_wgrad_unpack(float* dw_packed, float* grad_weight, tadnn_stream_t stream);
 int tadnn_cnn_pack_shadows(const float* w1, const float* w2, void* w1_packed, void* w2_packed,
                            void* toeplitz_t, tadnn_stream_t stream);
+/* Same with the conv1 operand of the sliding-operand kernels (bf16 [128, 128], bias folded in) instead of w1_packed. */
+int tadnn_cnn_pack_shadows_sliding(const float* w1, const float* b1, const float* w2, void* w1x_packed,
+                                   void* w2_packed, void* toeplitz_t, tadnn_stream_t stream);
 int tadnn_conv1_pool_forward(const void* x, const void* w_packed, const float* bias, void* p1,
                              void* idx1, int B, tadnn_stream_t stream);
 /* dp1 may be stored compactly as [B, dp1_h, dp1_w, 64] (its non-zero top-left corner); pass 9, 9

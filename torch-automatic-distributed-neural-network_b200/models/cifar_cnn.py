@@ -39,6 +39,7 @@ def _shadows(dev, wkey: int):
         if len(_SHADOWS) > 8:
             _SHADOWS.clear()
         sh = {"w1p": torch.empty((64, 80), device=dev, dtype=torch.bfloat16),
+              "w1x": torch.empty((128, 128), device=dev, dtype=torch.bfloat16),
               "w2p": torch.empty((64, 1600), device=dev, dtype=torch.bfloat16),
               "Tt": torch.empty((576, 4032), device=dev, dtype=torch.bfloat16),
               "dwp": torch.zeros((64, 1600), device=dev, dtype=torch.float32)}
@@ -58,16 +59,37 @@ def _dp1_buffer(dev, B):
     return t
 
 
-def _cnn_forward(x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fused_conv1, conv2_mode, seed_dev=None):
+def is_packed_input(x) -> bool:
+    """NHWC4 bf16 [B,32,32,4] (channel 3 == 1.0): what ``CifarCNN.pack_input`` returns."""
+    return x.dim() == 4 and tuple(x.shape[1:]) == (32, 32, 4) and x.dtype == torch.bfloat16
+
+
+def _cnn_forward(x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fused_conv1, conv2_mode, seed_dev=None,
+                 sliding=True):
     """Launch the forward kernels; returns (loss, logp, saved-for-backward dict)."""
     from ..ops import cnn as K
     B = x.shape[0]
     dev = x.device
-    xb = x if x.dtype == torch.bfloat16 else x.to(torch.bfloat16)
-    xb = xb.contiguous()
     col1 = a1 = col2 = a2 = sh = None
     fused2 = conv2_mode == "dense" and fused_conv1
-    if fused2:
+    sliding = bool(sliding) and fused2
+    packed = is_packed_input(x)
+    if packed and not sliding:
+        raise ValueError("a packed (NHWC4) input needs the fused path with the sliding-operand conv1")
+    if sliding:
+        # conv1 reads the image itself as its tensor-core operand (csrc/conv1_sliding.cu): NHWC4 bf16, channel 3 == 1.0
+        xb = x.contiguous() if packed else K.nhwc4_pack(x.contiguous())
+        sh = _shadows(dev, w2.data_ptr())
+        K.cnn_pack_shadows_sliding(w1, b1, w2, sh["w1x"], sh["w2p"], sh["Tt"])
+        w2p = sh["w2p"]
+        p1, idx1 = K.conv1s_pool_forward(xb, sh["w1x"])
+        p2, idx2 = K.conv2_pool_forward(p1, w2p, b2)
+    else:
+        xb = x if x.dtype == torch.bfloat16 else x.to(torch.bfloat16)
+        xb = xb.contiguous()
+    if sliding:
+        pass
+    elif fused2:
         # one launch refreshes every bf16 operand copy of the fp32 master weights (they may have been changed
         # by the optimiser, a synchronisation or a load since the last step)
         sh = _shadows(dev, w2.data_ptr())
@@ -114,7 +136,7 @@ def _cnn_forward(x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fu
                                                    C.c_void_p(_native.stream_ptr())), "tadnn_head_forward")
     saved = dict(xb=xb, col1=col1, a1=a1, p1=p1, idx1=idx1, col2=col2, a2=a2, p2=p2, idx2=idx2, hidden=hidden,
                  logp=logp, tgt=tgt, w2p=w2p, fw1=fw1, fb1=fb1, fw2=fw2, fb2=fb2, p_drop=float(p_drop), seed=seed, seed_dev=seed_dev,
-                 B=B, fused_conv1=bool(fused_conv1), conv2_mode=conv2_mode, fused2=fused2, sh=sh)
+                 B=B, fused_conv1=bool(fused_conv1), conv2_mode=conv2_mode, fused2=fused2, sh=sh, sliding=sliding)
     return loss, logp, saved
 
 
@@ -153,7 +175,10 @@ def _cnn_backward(sv, gw1, gb1, gw2, gb2, gfw1, gfb1, gfw2, gfb2, gloss=None, ta
         K.gemm_bf16(da2w.view(B, 576), sh["Tt"], b_mn_major=True, out=dp1.view(B, 81 * 64)[:, :7 * 9 * 64])
         if tail_ready is not None:
             tail_ready()  # every gradient except conv1's is complete (and nothing below reads those parameters)
-        K.conv1_pool_backward_bias(sv["xb"], dp1, p1, idx1, gw1, gb1)
+        if sv.get("sliding"):
+            K.conv1s_pool_backward(sv["xb"], dp1, idx1, gw1, gb1, rows=7)   # dp1 rows 7, 8 are never written (zero)
+        else:
+            K.conv1_pool_backward_bias(sv["xb"], dp1, p1, idx1, gw1, gb1)
         return
     dp2 = torch.empty((B, 1, 1, 64), device=dev, dtype=torch.bfloat16)
     h.dp2 = dp2.data_ptr()
@@ -197,8 +222,9 @@ class _CnnLoss(torch.autograd.Function):
     of launch sequences without autograd, accumulating straight into ``param.grad``."""
 
     @staticmethod
-    def forward(ctx, x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fused_conv1, conv2_mode):
-        loss, logp, sv = _cnn_forward(x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fused_conv1, conv2_mode)
+    def forward(ctx, x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fused_conv1, conv2_mode, sliding=True):
+        loss, logp, sv = _cnn_forward(x, target, w1, b1, w2, b2, fw1, fb1, fw2, fb2, p_drop, seed, fused_conv1, conv2_mode,
+                                      sliding=sliding)
         ctx.sv = sv
         ctx.mark_non_differentiable(logp)
         return loss, logp
@@ -216,7 +242,7 @@ class _CnnLoss(torch.autograd.Function):
             off += n
         _cnn_backward(sv, *grads, gloss=gloss)
         ctx.sv = None
-        return (None, None, *grads, None, None, None, None)
+        return (None, None, *grads, None, None, None, None, None)
 
 
 class CifarCNN(torch.nn.Module, T7Protocol):
@@ -224,11 +250,16 @@ class CifarCNN(torch.nn.Module, T7Protocol):
     # dataset is shipped as bytes (the reference's own preprocessing is utils/preprocess.py)
     input_affine = ([4.0 / 255.0] * 3, [-2.0] * 3)
 
-    def __init__(self, dropout: float = 0.5, seed: int = 1, fused_conv1: bool = True, conv2_mode: str = "dense"):
+    def __init__(self, dropout: float = 0.5, seed: int = 1, fused_conv1: bool = True, conv2_mode: str = "dense",
+                 conv1_kernel: str = "sliding"):
         super().__init__()
         assert conv2_mode in ("dense", "pooled", "legacy")
+        assert conv1_kernel in ("sliding", "rows")
         self.dropout = dropout
         self.fused_conv1 = fused_conv1  # False: im2col + GEMM + separate pooling kernels (generic path)
+        # fused conv1 kernels: "sliding" = the staged NHWC4 image is the tensor-core operand (csrc/conv1_sliding.cu; fused
+        # "dense" path only), "rows" = one im2col row per pixel built in shared memory (csrc/conv1_fused.cu)
+        self.conv1_kernel = conv1_kernel
         # conv2 forward: "dense" evaluates all 5x5 output pixels like the reference; "pooled" only the
         # 3x3 that pool2 reads (identical loss and gradients); both use the sparse-gradient backward.
         # "legacy": raster-order im2col, 25-tap dgrad GEMM + col2im (first implementation, kept as oracle).
@@ -262,7 +293,9 @@ class CifarCNN(torch.nn.Module, T7Protocol):
         x = x.float()
         # the fused conv1 carries its bias through the GEMM as a bf16 operand column
         y = F.conv2d(x, r(self.conv1_weight).view(64, 3, 5, 5), r(self.conv1_bias) if self.fused_conv1 else self.conv1_bias)
-        y = F.max_pool2d(r(F.relu(y)), 3, 3)
+        # the sliding-operand conv1 pools the fp32 accumulators and rounds the winner (same values, since rounding is
+        # monotonic, but a tie between two values that round to the same bf16 goes to the larger fp32 one, not to the first)
+        y = r(F.max_pool2d(F.relu(y), 3, 3)) if self.packs_input else F.max_pool2d(r(F.relu(y)), 3, 3)
         y = F.conv2d(y, r(self.conv2_weight).view(64, 64, 5, 5), self.conv2_bias)
         y = F.max_pool2d(r(F.relu(y)), 3, 3).reshape(-1, 64)
         if dropout_scale is not None:
@@ -274,7 +307,21 @@ class CifarCNN(torch.nn.Module, T7Protocol):
         return F.log_softmax(y, dim=-1)
 
     def _native_ok(self, x) -> bool:
-        return x.is_cuda and x.dim() == 4 and tuple(x.shape[1:]) == (3, 32, 32)
+        return x.is_cuda and x.dim() == 4 and (tuple(x.shape[1:]) == (3, 32, 32) or (self.packs_input and is_packed_input(x)))
+
+    @property
+    def packs_input(self) -> bool:
+        """True when the fused path reads its input as NHWC4 bf16 (``pack_input``)."""
+        return self.fused_conv1 and self.conv2_mode == "dense" and self.conv1_kernel == "sliding"
+
+    def pack_input(self, x: torch.Tensor, affine=None, out=None) -> torch.Tensor:
+        """[B,3,32,32] uint8 / bf16 / fp32 on the device -> the fused path's own input layout, NHWC4 bf16 with channel
+        3 == 1.0 (the bias rides on it), ``y = x * scale[c] + shift[c]`` for ``affine = (scale, shift)``.  Every entry point
+        also takes the plain NCHW tensor and packs it itself (one more launch per step); a data pipeline that packs once
+        (``BatchTrainer.fit`` does, in the kernel that widens the uint8 bytes) saves that launch."""
+        from ..ops import cnn as K
+        sc, sh = affine if affine is not None else (None, None)
+        return K.nhwc4_pack(x.contiguous(), sc, sh, out=out)
 
     def loss_and_logp(self, x: torch.Tensor, target: torch.Tensor):
         """Mean cross-entropy (differentiable) and log-probabilities."""
@@ -286,7 +333,7 @@ class CifarCNN(torch.nn.Module, T7Protocol):
             seed = (self._seed * 2654435761 + self._step * 40503) & 0xFFFFFFFF
             return _CnnLoss.apply(x, target.to(x.device), self.conv1_weight, self.conv1_bias, self.conv2_weight,
                                   self.conv2_bias, self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias, p, seed,
-                                  self.fused_conv1, self.conv2_mode)
+                                  self.fused_conv1, self.conv2_mode, self.conv1_kernel == "sliding")
         logp = self.reference_logp(x)
         return F.nll_loss(logp, target.long().to(logp.device)), logp.detach()
 
@@ -318,7 +365,7 @@ class CifarCNN(torch.nn.Module, T7Protocol):
         seed = (self._seed * 2654435761 + self._step * 40503) & 0xFFFFFFFF
         with torch.no_grad():
             loss, _logp, sv = _cnn_forward(x, target, *[p.data for p in ps], pd, seed, self.fused_conv1, self.conv2_mode,
-                                           seed_dev=getattr(self, "_seed_dev", None))
+                                           seed_dev=getattr(self, "_seed_dev", None), sliding=self.conv1_kernel == "sliding")
             cb = (lambda: tail_ready(self.conv2_weight)) if (tail_ready is not None and sv.get("fused2")) else None
             _cnn_backward(sv, *[p.grad for p in ps], tail_ready=cb)
         return loss

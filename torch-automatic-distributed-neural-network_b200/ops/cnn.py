@@ -179,6 +179,13 @@ def cnn_pack_shadows(w1, w2, w1p, w2p, Tt):
     _native.check(_native.lib().tadnn_cnn_pack_shadows(_p(w1), _p(w2), _p(w1p), _p(w2p), _p(Tt), _s()), "tadnn_cnn_pack_shadows")
 
 
+def cnn_pack_shadows_sliding(w1, b1, w2, w1x, w2p, Tt):
+    """One launch: conv1 operand of the sliding-operand kernels (bf16 [128,128], bias folded in), packed conv2 filters and
+    the Toeplitz matrix of the transposed conv2."""
+    _native.check(_native.lib().tadnn_cnn_pack_shadows_sliding(_p(w1), _p(b1), _p(w2), _p(w1x), _p(w2p), _p(Tt), _s()),
+                  "tadnn_cnn_pack_shadows_sliding")
+
+
 def conv1_pool_backward_bias(x, dp1, p1, idx1, grad_weight, grad_bias):
     _native.check(_native.lib().tadnn_conv1_pool_backward_bias(_p(x), _p(dp1), int(dp1.shape[1]), int(dp1.shape[2]), _p(p1), _p(idx1),
                                                                _p(grad_weight), _p(grad_bias), x.shape[0], _s()),
@@ -275,5 +282,5 @@ def auto_split_k(M: int, N: int, K: int, tile_n: int = 256) -> int:
     return max(1, min(kb, 148 // max(1, tiles)))
 
 
-__all__ = ["nhwc4_pack", "conv1s_weight_pack", "conv1s_pool_forward", "conv1s_pool_backward", "u8_to_bf16", "conv2_pool_forward", "conv2_wgrad", "conv2_wgrad_unpack", "cnn_pack_shadows", "conv1_pool_backward_bias", "im2col_winfirst", "conv_toeplitz_pack", "expand_corner", "conv1_weight_pack", "conv1_pool_forward", "conv1_pool_backward", "im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "colsum_relu_mask_corner", "conv_weight_pack",
+__all__ = ["nhwc4_pack", "conv1s_weight_pack", "conv1s_pool_forward", "conv1s_pool_backward", "cnn_pack_shadows_sliding", "u8_to_bf16", "conv2_pool_forward", "conv2_wgrad", "conv2_wgrad_unpack", "cnn_pack_shadows", "conv1_pool_backward_bias", "im2col_winfirst", "conv_toeplitz_pack", "expand_corner", "conv1_weight_pack", "conv1_pool_forward", "conv1_pool_backward", "im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "colsum_relu_mask_corner", "conv_weight_pack",
            "conv_wgrad_unpack", "head_workspace", "sgd_step", "auto_split_k", "HeadArgs", "gemm_bf16"]

@@ -100,7 +100,8 @@ class BatchTrainer:
         ``data`` may be ``uint8`` (what CIFAR is on disk: 3 KB per image instead of 6 KB as bf16):
         the bytes are what crosses PCIe, and the device widens them to bf16 with the affine map
         ``input_affine = (scale[C], shift[C])`` (default: the model's ``input_affine`` attribute, else
-        ``x/255``) in one small kernel (csrc/preprocess.cu: tadnn_u8_to_bf16) before the step.
+        ``x/255``) in one small kernel (csrc/preprocess.cu: tadnn_u8_to_bf16; a model with its own input layout —
+        ``CifarCNN.pack_input``, NHWC4 — has that kernel write the layout directly) before the step.
         ``depth`` staging buffers are kept in flight on the copy stream (the reference instead
         keeps its whole shard on the GPU, cifar_example/sgd-torchad_nn-cifar.lua:239-245)."""
         n = data.shape[0]
@@ -127,7 +128,11 @@ class BatchTrainer:
                 aff = ([1.0 / 255.0] * C, [0.0] * C)
         bufs = [(torch.empty((batch,) + tuple(data.shape[1:]), dtype=data.dtype, device=dev),
                  torch.empty((batch,) + tuple(targets.shape[1:]), dtype=targets.dtype, device=dev)) for _ in range(depth)]
-        if u8:  # one widened buffer per ring slot: the widening kernel runs on the copy stream, right behind its copy
+        # a model whose fused path has its own input layout (CifarCNN: NHWC4) gets it written by the widening kernel itself
+        packer = getattr(self.model, "pack_input", None) if (u8 and getattr(self.model, "packs_input", False)) else None
+        if packer is not None:
+            wide = [packer(bufs[k][0], aff) for k in range(depth)]
+        elif u8:  # one widened buffer per ring slot
             wide = [torch.empty((batch,) + tuple(data.shape[1:]), dtype=torch.bfloat16, device=dev) for _ in range(depth)]
         ready = [torch.cuda.Event() for _ in range(depth)]
         consumed = [torch.cuda.Event() for _ in range(depth)]
@@ -160,7 +165,10 @@ class BatchTrainer:
                     ws.wait_event(copied[k])
                     if s >= depth:
                         ws.wait_event(consumed[k])                     # wide[k] of step s - depth has been consumed
-                    u8_to_bf16(bufs[k][0], plane, C, aff[0], aff[1], out=wide[k])
+                    if packer is not None:
+                        packer(bufs[k][0], aff, out=wide[k])
+                    else:
+                        u8_to_bf16(bufs[k][0], plane, C, aff[0], aff[1], out=wide[k])
                     widened[k].record(ws)
                     ready[k].record(ws)
 

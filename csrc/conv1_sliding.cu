@@ -29,6 +29,7 @@
 #include "common.cuh"
 #include "sm100.cuh"
 #include "conv1s_pack.cuh"
+#include <cuda_fp16.h>
 #include <stdlib.h>
 
 #include <utility>
@@ -375,7 +376,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1s_fwd_kernel(const Conv1s
 //       kh' = 5 is read (N must be a multiple of 16) and ignored.
 // One K step = one conv row, 3 MMAs (j = 0, 1, 2; M = 128, N = 48) into three accumulators that live for the whole
 // kernel; pooled row = 3 conv rows = one 24-column slot of a 14-slot operand ring in tensor memory.
-constexpr int kXS = 4;                         // staged images (B operand)
+constexpr int kXS = 8;                         // staged images (B operand)
 constexpr int kGS = 4;                         // staged (dp1, idx1) images
 constexpr int kGIdxOff = 81 * kO * 2;          // 10368: idx1 part of a gradient slot
 constexpr int kGSlotBytes = 15616;             // 10368 + 5184 = 15552, rounded up to a multiple of 128
@@ -384,7 +385,7 @@ constexpr int kASlots = 14, kASlotCols = 24;
 constexpr int kACol0 = 176;                    // operand ring: columns 176 .. 511
 static_assert(kACol0 + kASlots * kASlotCols <= 512, "operand ring exceeds tensor memory");
 constexpr int kBGroups = 4;
-constexpr int kBwdThreads = 32 * (2 + 4 * kBGroups);   // warp 0: MMA issuer + TMEM, warp 1: loader, then the builder groups
+constexpr int kBwdThreads = 32 * (4 + 4 * kBGroups);   // warps 0-2: MMA issuers (one per accumulator j), warp 3: loader, then the builder groups
 constexpr int kBwdSmem = kXS * kImgBytes + 128 + kGS * kGSlotBytes + 64 * 77 * 4 + 1024;
 
 __device__ __forceinline__ void tmem_st_32x32b_x8(uint32_t taddr, const uint32_t* r) {
@@ -408,23 +409,40 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
                : "memory");
 }
 
-// One conv row (I = 0..2 of the pooled row) of dY^T for column parity PAR: 8 words of bf16 pairs (positions 2k, 2k+1).
-template <int PAR, int I, int K2>
-__device__ __forceinline__ uint32_t dy_word(const uint32_t (&g)[9], const uint32_t (&cd)[9]) {
-  // position q = 2 K2 + h  <->  column w = 2 q + PAR, window pw = w / 3, window position I * 3 + w % 3
-  uint32_t half[2];
-#pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    const int q = 2 * K2 + h, w = 2 * q + PAR;
-    if (w <= 26) half[h] = (cd[w / 3] == static_cast<uint32_t>(8 - (I * 3 + w % 3))) ? g[w / 3] : 0u;
-    else half[h] = 0u;
+// dY^T of one pooled row for column parity PAR: word K2 of conv row I holds positions q = 2 K2 (low half) and 2 K2 + 1
+// (high half), i.e. columns w = 4 K2 + PAR and 4 K2 + 2 + PAR.  A position gets its window's pooled gradient when the
+// window's arg-max code equals the position's code (8 - (3 I + w % 3)); codes are compared two at a time as fp16 numbers
+// (0x4000 | code: distinct normal values), the pair of gradients and the pair of codes are shared by the three rows.
+template <int PAR, int K2>
+__device__ __forceinline__ void dy_words(const uint32_t (&g)[9], const uint32_t (&cdh)[9], uint32_t& r0, uint32_t& r1, uint32_t& r2) {
+  constexpr int wa = 4 * K2 + PAR, wb = 4 * K2 + 2 + PAR;
+  constexpr bool vb = wb <= 26;
+  constexpr int pa = wa / 3, pb = vb ? wb / 3 : pa;
+  const uint32_t P = __byte_perm(g[pa], g[pb], 0x5410);
+  const uint32_t C = __byte_perm(cdh[pa], cdh[pb], 0x5410);
+  const __half2 c2 = *reinterpret_cast<const __half2*>(&C);
+#define TADNN_DY_ROW(I, OUT)                                                                                          \
+  {                                                                                                                   \
+    constexpr uint32_t k = (0x4000u | static_cast<uint32_t>(8 - (3 * I + wa % 3))) |                                  \
+                           ((vb ? (0x4000u | static_cast<uint32_t>(8 - (3 * I + wb % 3))) : 0x7C00u) << 16);         \
+    const uint32_t kk = k;                                                                                            \
+    OUT = P & __heq2_mask(c2, *reinterpret_cast<const __half2*>(&kk));                                               \
   }
-  return half[0] | (half[1] << 16);
+  TADNN_DY_ROW(0, r0)
+  TADNN_DY_ROW(1, r1)
+  TADNN_DY_ROW(2, r2)
+#undef TADNN_DY_ROW
 }
-template <int PAR, int I>
-__device__ __forceinline__ void dy_row(const uint32_t (&g)[9], const uint32_t (&cd)[9], uint32_t (&r)[8]) {
-  r[0] = dy_word<PAR, I, 0>(g, cd); r[1] = dy_word<PAR, I, 1>(g, cd); r[2] = dy_word<PAR, I, 2>(g, cd); r[3] = dy_word<PAR, I, 3>(g, cd);
-  r[4] = dy_word<PAR, I, 4>(g, cd); r[5] = dy_word<PAR, I, 5>(g, cd); r[6] = dy_word<PAR, I, 6>(g, cd); r[7] = 0u;
+template <int PAR>
+__device__ __forceinline__ void dy_rows(const uint32_t (&g)[9], const uint32_t (&cdh)[9], uint32_t (&r0)[8], uint32_t (&r1)[8], uint32_t (&r2)[8]) {
+  dy_words<PAR, 0>(g, cdh, r0[0], r1[0], r2[0]);
+  dy_words<PAR, 1>(g, cdh, r0[1], r1[1], r2[1]);
+  dy_words<PAR, 2>(g, cdh, r0[2], r1[2], r2[2]);
+  dy_words<PAR, 3>(g, cdh, r0[3], r1[3], r2[3]);
+  dy_words<PAR, 4>(g, cdh, r0[4], r1[4], r2[4]);
+  dy_words<PAR, 5>(g, cdh, r0[5], r1[5], r2[5]);
+  dy_words<PAR, 6>(g, cdh, r0[6], r1[6], r2[6]);
+  r0[7] = r1[7] = r2[7] = 0u;
 }
 
 __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1sArgs a) {
@@ -439,10 +457,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int rows = a.rows;
   if (threadIdx.x == 0) {
-    for (int s = 0; s < kXS; ++s) { mbar_init(&x_full[s], 1); mbar_init(&x_empty[s], 1); }
+    for (int s = 0; s < kXS; ++s) { mbar_init(&x_full[s], 1); mbar_init(&x_empty[s], 3); }
     for (int s = 0; s < kGS; ++s) { mbar_init(&g_full[s], 1); mbar_init(&g_empty[s], static_cast<uint32_t>(rows * 128)); }
-    for (int s = 0; s < kASlots; ++s) { mbar_init(&a_full[s], 128); mbar_init(&a_empty[s], 1); }
-    mbar_init(&done_bar, 1);
+    for (int s = 0; s < kASlots; ++s) { mbar_init(&a_full[s], 128); mbar_init(&a_empty[s], 3); }
+    mbar_init(&done_bar, 3);
     fence_mbar_init();
   }
   if (warp == 0) tmem_alloc<512>(&tmem_base_smem);
@@ -454,12 +472,16 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
   const uint32_t tmem_base = tmem_base_smem;
   const int my_imgs = (a.B - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
 
-  if (warp == 0) {
-    // ---------------- MMA issuer (whole warp in the loop, one elected lane issues) ----------------
+  if (warp < 3) {
+    // ---------------- MMA issuers: warp j owns accumulator j (whole warp in the loop, one elected lane issues) ----------------
+    // One warp issues an instruction every ~8 cycles here (waits, uniform-register set-up, the MMAs themselves): with
+    // all 63 MMAs of a sample in one instruction stream the tensor pipe was busy 40 % of the time.
     constexpr uint32_t idesc = make_idesc_bf16(128, 48, 0, 1);
+    const int j = warp;
     const uint32_t x0 = smem_u32(ximg);
-    const uint64_t bdesc0 = make_smem_desc_nosw(x0, 128, 256);   // MN-major no-swizzle: LBO = next 8 K rows, SBO = next 8 N elements
+    const uint64_t bdesc0 = make_smem_desc_nosw(x0, 128, 256) + static_cast<uint64_t>(j);   // MN-major no-swizzle: LBO = next 8 K rows, SBO = next 8 N elements
     const uint32_t acol = tmem_base + static_cast<uint32_t>(kACol0);
+    const uint32_t d = tmem_base + static_cast<uint32_t>(j * kDStride);
     int slot = 0, sph = 0;     // operand ring position and phase
 #pragma unroll 1
     for (int i = 0; i < my_imgs; ++i) {
@@ -475,10 +497,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
           if (elect_one()) {
 #pragma unroll
             for (int r = 0; r < 3; ++r)
-#pragma unroll
-              for (int j = 0; j < 3; ++j)
-                umma_f16_ts(tmem_base + static_cast<uint32_t>(j * kDStride), at + r * 8, bimg + static_cast<uint64_t>((3 * pr + r) * kPairsPerRow + j), idesc,
-                            (i > 0 || pr > 0 || r > 0) ? 1u : 0u);
+              umma_f16_ts(d, at + r * 8, bimg + static_cast<uint64_t>((3 * pr + r) * kPairsPerRow), idesc, (i > 0 || pr > 0 || r > 0) ? 1u : 0u);
             umma_commit(&a_empty[slot]);
           }
           __syncwarp();
@@ -490,7 +509,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
     }
     if (elect_one()) umma_commit(&done_bar);
     __syncwarp();
-  } else if (warp == 1) {
+  } else if (warp == 3) {
     // ---------------- loader: image, dp1 rows and idx1 rows of one sample per step ----------------
     if (elect_one()) {
       const uint32_t gbytes = static_cast<uint32_t>(rows * 9 * kO * 2), ibytes = static_cast<uint32_t>(rows * 9 * kO);
@@ -509,31 +528,31 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
     __syncwarp();
   } else {
     // ---------------- builders: dY^T of one pooled row (3 conv rows) per step, straight into tensor memory ----------------
-    const int grp = (warp - 2) >> 2;
+    const int grp = (warp - 4) >> 2;
     const int q = warp & 3;
     const int par = q >> 1;
     const int ch = (q & 1) * 32 + lane;
     const uint32_t g0 = smem_u32(gbuf) + static_cast<uint32_t>(ch * 2), i0 = smem_u32(gbuf) + static_cast<uint32_t>(kGIdxOff + ch);
     const uint32_t arow = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(kACol0);
-    const int chunks = my_imgs * rows;
+    // chunk cg = (sample i, pooled row pr) = i * rows + pr; this group takes cg = grp, grp + 4, ...; ring slot cg % 14
+    int i = 0, pr = grp, slot = grp, aph = 1;
+    while (pr >= rows) { pr -= rows; ++i; }
 #pragma unroll 1
-    for (int cg = grp; cg < chunks; cg += kBGroups) {
-      const int i = cg / rows, pr = cg - i * rows;
-      const int gs = i % kGS;
-      const int slot = cg % kASlots;
+    while (i < my_imgs) {
+      const int gs = i & (kGS - 1);
       mbar_wait(&g_full[gs], (i / kGS) & 1);
-      uint32_t g[9], cd[9];
+      uint32_t g[9], cdh[9];
       const uint32_t goff = static_cast<uint32_t>(gs * kGSlotBytes + pr * 9 * kO * 2), ioff = static_cast<uint32_t>(gs * kGSlotBytes + pr * 9 * kO);
 #pragma unroll
       for (int pw = 0; pw < 9; ++pw) {
         g[pw] = lds_u16(g0 + goff + pw * (kO * 2));
-        cd[pw] = lds_u8(i0 + ioff + pw * kO);
+        cdh[pw] = lds_u8(i0 + ioff + pw * kO) | 0x4000u;
       }
       mbar_arrive(&g_empty[gs]);
       uint32_t r0[8], r1[8], r2[8];
-      if (par == 0) { dy_row<0, 0>(g, cd, r0); dy_row<0, 1>(g, cd, r1); dy_row<0, 2>(g, cd, r2); }
-      else { dy_row<1, 0>(g, cd, r0); dy_row<1, 1>(g, cd, r1); dy_row<1, 2>(g, cd, r2); }
-      mbar_wait(&a_empty[slot], ((cg / kASlots) & 1) ^ 1);
+      if (par == 0) dy_rows<0>(g, cdh, r0, r1, r2);
+      else dy_rows<1>(g, cdh, r0, r1, r2);
+      mbar_wait(&a_empty[slot], aph);
       tc_fence_after_sync();
       const uint32_t at = arow + static_cast<uint32_t>(slot * kASlotCols);
       tmem_st_32x32b_x8(at, r0);
@@ -542,6 +561,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
       tmem_st_wait();
       tc_fence_before_sync();
       mbar_arrive(&a_full[slot]);
+      pr += kBGroups;
+      while (pr >= rows) { pr -= rows; ++i; }
+      slot += kBGroups;
+      if (slot >= kASlots) { slot -= kASlots; aph ^= 1; }
     }
     // ---------------- final reduction (first builder group): accumulators -> gw, gb ----------------
     if (grp == 0 && my_imgs > 0) {
@@ -582,7 +605,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
         }
         asm volatile("bar.sync 2, 128;" ::: "memory");
       }
-      const int t = threadIdx.x - 64;
+      const int t = threadIdx.x - 128;
       for (int e = t; e < kO * 76; e += 128) {
         const int c2 = e / 76, k = e - c2 * 76;
         const float val = red[c2 * 77 + k];

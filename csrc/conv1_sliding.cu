@@ -375,13 +375,15 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1s_fwd_kernel(const Conv1s
 //       image row (SBO = 256 B) apart, K = 16 positions at a 16-byte pitch (8-position groups LBO = 128 B apart);
 //       kh' = 5 is read (N must be a multiple of 16) and ignored.
 // One K step = one conv row, 3 MMAs (j = 0, 1, 2; M = 128, N = 48) into three accumulators that live for the whole
-// kernel; pooled row = 3 conv rows = one 24-column slot of a 14-slot operand ring in tensor memory.
+// kernel; a pooled row = 3 conv rows = 24 operand columns; the operand ring in tensor memory has two slots of 7 pooled
+// rows (the 7 rows the example CNN back-propagates through = one sample; 9 rows = a slot of 7 and a slot of 2), so an
+// issuer waits once and issues 21 MMAs back to back.
 constexpr int kXS = 8;                         // staged images (B operand)
 constexpr int kGS = 4;                         // staged (dp1, idx1) images
 constexpr int kGIdxOff = 81 * kO * 2;          // 10368: idx1 part of a gradient slot
 constexpr int kGSlotBytes = 15616;             // 10368 + 5184 = 15552, rounded up to a multiple of 128
 constexpr int kDStride = 64;                   // accumulator j: columns 64 j .. 64 j + 47
-constexpr int kASlots = 14, kASlotCols = 24;
+constexpr int kASlots = 2, kRowCols = 24, kSlotRows = 7, kASlotCols = kSlotRows * kRowCols;
 constexpr int kACol0 = 176;                    // operand ring: columns 176 .. 511
 static_assert(kACol0 + kASlots * kASlotCols <= 512, "operand ring exceeds tensor memory");
 constexpr int kBGroups = 4;
@@ -459,7 +461,10 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
   if (threadIdx.x == 0) {
     for (int s = 0; s < kXS; ++s) { mbar_init(&x_full[s], 1); mbar_init(&x_empty[s], 3); }
     for (int s = 0; s < kGS; ++s) { mbar_init(&g_full[s], 1); mbar_init(&g_empty[s], static_cast<uint32_t>(rows * 128)); }
-    for (int s = 0; s < kASlots; ++s) { mbar_init(&a_full[s], 128); mbar_init(&a_empty[s], 3); }
+    // slot 0 takes pooled rows 0..6 of a sample, slot 1 the next sample's (rows <= 7) or rows 7, 8 of the same one
+    mbar_init(&a_full[0], static_cast<uint32_t>((rows < kSlotRows ? rows : kSlotRows) * 128));
+    mbar_init(&a_full[1], static_cast<uint32_t>((rows > kSlotRows ? rows - kSlotRows : rows) * 128));
+    for (int s = 0; s < kASlots; ++s) mbar_init(&a_empty[s], 3);
     mbar_init(&done_bar, 3);
     fence_mbar_init();
   }
@@ -482,26 +487,31 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
     const uint64_t bdesc0 = make_smem_desc_nosw(x0, 128, 256) + static_cast<uint64_t>(j);   // MN-major no-swizzle: LBO = next 8 K rows, SBO = next 8 N elements
     const uint32_t acol = tmem_base + static_cast<uint32_t>(kACol0);
     const uint32_t d = tmem_base + static_cast<uint32_t>(j * kDStride);
-    int slot = 0, sph = 0;     // operand ring position and phase
+    const int nsc = rows > kSlotRows ? 2 : 1;   // operand slots per sample
 #pragma unroll 1
     for (int i = 0; i < my_imgs; ++i) {
       const int xs = i % kXS;
       mbar_wait_t<true>(&x_full[xs], (i / kXS) & 1);
       const uint64_t bimg = bdesc0 + static_cast<uint64_t>(xs * (kImgBytes / 16));
 #pragma unroll
-      for (int pr = 0; pr < 9; ++pr) {
-        if (pr < rows) {
-          mbar_wait_t<true>(&a_full[slot], sph);
+      for (int c = 0; c < 2; ++c) {
+        if (c < nsc) {
+          const int sc = i * nsc + c, slot = sc & 1;
+          mbar_wait_t<true>(&a_full[slot], (sc >> 1) & 1);
           tc_fence_after_sync();
           const uint32_t at = acol + static_cast<uint32_t>(slot * kASlotCols);
           if (elect_one()) {
 #pragma unroll
-            for (int r = 0; r < 3; ++r)
-              umma_f16_ts(d, at + r * 8, bimg + static_cast<uint64_t>((3 * pr + r) * kPairsPerRow), idesc, (i > 0 || pr > 0 || r > 0) ? 1u : 0u);
+            for (int prl = 0; prl < kSlotRows; ++prl)
+              if (c * kSlotRows + prl < rows) {
+#pragma unroll
+                for (int r = 0; r < 3; ++r)
+                  umma_f16_ts(d, at + prl * kRowCols + r * 8, bimg + static_cast<uint64_t>((3 * (c * kSlotRows + prl) + r) * kPairsPerRow), idesc,
+                              (i > 0 || c > 0 || prl > 0 || r > 0) ? 1u : 0u);
+              }
             umma_commit(&a_empty[slot]);
           }
           __syncwarp();
-          if (++slot == kASlots) { slot = 0; sph ^= 1; }
         }
       }
       if (elect_one()) umma_commit(&x_empty[xs]);
@@ -534,8 +544,9 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
     const int ch = (q & 1) * 32 + lane;
     const uint32_t g0 = smem_u32(gbuf) + static_cast<uint32_t>(ch * 2), i0 = smem_u32(gbuf) + static_cast<uint32_t>(kGIdxOff + ch);
     const uint32_t arow = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(kACol0);
-    // chunk cg = (sample i, pooled row pr) = i * rows + pr; this group takes cg = grp, grp + 4, ...; ring slot cg % 14
-    int i = 0, pr = grp, slot = grp, aph = 1;
+    // pooled row cg = i * rows + pr of this CTA's work; this group takes cg = grp, grp + 4, ...
+    const int nsc = rows > kSlotRows ? 2 : 1;
+    int i = 0, pr = grp;
     while (pr >= rows) { pr -= rows; ++i; }
 #pragma unroll 1
     while (i < my_imgs) {
@@ -552,9 +563,11 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
       uint32_t r0[8], r1[8], r2[8];
       if (par == 0) dy_rows<0>(g, cdh, r0, r1, r2);
       else dy_rows<1>(g, cdh, r0, r1, r2);
-      mbar_wait(&a_empty[slot], aph);
+      const int c = pr >= kSlotRows ? 1 : 0;
+      const int sc = i * nsc + c, slot = sc & 1;
+      mbar_wait(&a_empty[slot], ((sc >> 1) & 1) ^ 1);
       tc_fence_after_sync();
-      const uint32_t at = arow + static_cast<uint32_t>(slot * kASlotCols);
+      const uint32_t at = arow + static_cast<uint32_t>(slot * kASlotCols + (pr - c * kSlotRows) * kRowCols);
       tmem_st_32x32b_x8(at, r0);
       tmem_st_32x32b_x8(at + 8, r1);
       tmem_st_32x32b_x8(at + 16, r2);
@@ -563,8 +576,6 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
       mbar_arrive(&a_full[slot]);
       pr += kBGroups;
       while (pr >= rows) { pr -= rows; ++i; }
-      slot += kBGroups;
-      if (slot >= kASlots) { slot -= kASlots; aph ^= 1; }
     }
     // ---------------- final reduction (first builder group): accumulators -> gw, gb ----------------
     if (grp == 0 && my_imgs > 0) {

@@ -413,8 +413,9 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
 
 // dY^T of one pooled row for column parity PAR: word K2 of conv row I holds positions q = 2 K2 (low half) and 2 K2 + 1
 // (high half), i.e. columns w = 4 K2 + PAR and 4 K2 + 2 + PAR.  A position gets its window's pooled gradient when the
-// window's arg-max code equals the position's code (8 - (3 I + w % 3)); codes are compared two at a time as fp16 numbers
-// (0x4000 | code: distinct normal values), the pair of gradients and the pair of codes are shared by the three rows.
+// window's arg-max code equals the position's code (8 - (3 I + w % 3)); codes are compared two at a time as the fp16
+// numbers their bit patterns denote (0..15: zero and subnormals, all distinct; fp16 compares do not flush them), the
+// pair of gradients and the pair of codes are shared by the three rows.
 template <int PAR, int K2>
 __device__ __forceinline__ void dy_words(const uint32_t (&g)[9], const uint32_t (&cdh)[9], uint32_t& r0, uint32_t& r1, uint32_t& r2) {
   constexpr int wa = 4 * K2 + PAR, wb = 4 * K2 + 2 + PAR;
@@ -425,8 +426,8 @@ __device__ __forceinline__ void dy_words(const uint32_t (&g)[9], const uint32_t 
   const __half2 c2 = *reinterpret_cast<const __half2*>(&C);
 #define TADNN_DY_ROW(I, OUT)                                                                                          \
   {                                                                                                                   \
-    constexpr uint32_t k = (0x4000u | static_cast<uint32_t>(8 - (3 * I + wa % 3))) |                                  \
-                           ((vb ? (0x4000u | static_cast<uint32_t>(8 - (3 * I + wb % 3))) : 0x7C00u) << 16);         \
+    constexpr uint32_t k = static_cast<uint32_t>(8 - (3 * I + wa % 3)) |                                              \
+                           ((vb ? static_cast<uint32_t>(8 - (3 * I + wb % 3)) : 0x7C00u) << 16);                      \
     const uint32_t kk = k;                                                                                            \
     OUT = P & __heq2_mask(c2, *reinterpret_cast<const __half2*>(&kk));                                               \
   }
@@ -546,18 +547,21 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
     const uint32_t arow = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(kACol0);
     // pooled row cg = i * rows + pr of this CTA's work; this group takes cg = grp, grp + 4, ...
     const int nsc = rows > kSlotRows ? 2 : 1;
-    int i = 0, pr = grp;
+    int i = 0, pr = grp, waited = -1;
     while (pr >= rows) { pr -= rows; ++i; }
 #pragma unroll 1
     while (i < my_imgs) {
       const int gs = i & (kGS - 1);
-      mbar_wait(&g_full[gs], (i / kGS) & 1);
+      if (i != waited) {   // this thread still owes an arrival on g_empty for every row it reads: the slot cannot be refilled under it
+        mbar_wait(&g_full[gs], (i / kGS) & 1);
+        waited = i;
+      }
       uint32_t g[9], cdh[9];
       const uint32_t goff = static_cast<uint32_t>(gs * kGSlotBytes + pr * 9 * kO * 2), ioff = static_cast<uint32_t>(gs * kGSlotBytes + pr * 9 * kO);
 #pragma unroll
       for (int pw = 0; pw < 9; ++pw) {
         g[pw] = lds_u16(g0 + goff + pw * (kO * 2));
-        cdh[pw] = lds_u8(i0 + ioff + pw * kO) | 0x4000u;
+        cdh[pw] = lds_u8(i0 + ioff + pw * kO);
       }
       mbar_arrive(&g_empty[gs]);
       uint32_t r0[8], r1[8], r2[8];

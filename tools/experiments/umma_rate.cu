@@ -30,10 +30,11 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int N, int bsw, int rounds
   tc_fence_after_sync();
   const uint32_t tb = tbase;
   if (threadIdx.x < 32) {
-    const uint32_t idesc = make_idesc_bf16(128, N, 0, 0);
+    const uint32_t idesc = make_idesc_bf16(128, N, 0, bsw == 2 ? 1 : 0);
     const uint32_t sa = smem_u32(smem), sb = smem_u32(smem + 16384);
     const uint64_t adesc = make_smem_desc_sw128(sa, 16, 1024);
-    const uint64_t bdesc = bsw ? make_smem_desc_sw128(sb, 16, 1024) : desc_nosw(sb, 16, 128);
+    // bsw 0: K-major no-swizzle (rows 16 B apart), 1: K-major SWIZZLE_128B, 2: MN-major no-swizzle (8-K groups 128 B, 8-N groups 256 B apart)
+    const uint64_t bdesc = bsw == 1 ? make_smem_desc_sw128(sb, 16, 1024) : (bsw == 2 ? desc_nosw(sb, 128, 256) : desc_nosw(sb, 16, 128));
     constexpr int stride = 512 / (CHAINS + (MODE == 1 ? 1 : 0)) / 32 * 32;   // accumulator column stride; last slot = A when in TMEM
     const uint32_t ta = tb + CHAINS * stride;
     long long t0 = 0, t1 = 0;
@@ -80,7 +81,7 @@ int main() {
   long long* out;
   cudaMallocManaged(&out, 16);
   printf("%-4s %-5s %-6s %-4s %10s %10s\n", "A", "N", "chains", "Bsw", "issue/mma", "cyc/mma");
-  for (int bsw = 0; bsw < 2; ++bsw)
+  for (int bsw = 0; bsw < 3; ++bsw)
     for (int N : {48, 96, 128, 192, 256}) {
       run<0, 1>(N, bsw, out); run<0, 2>(N, bsw, out); run<0, 4>(N, bsw, out);
       run<1, 1>(N, bsw, out); run<1, 2>(N, bsw, out); run<1, 4>(N, bsw, out);

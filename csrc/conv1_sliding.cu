@@ -197,7 +197,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1s_fwd_kernel(const Conv1s
     }
     for (int s = 0; s < kGroups; ++s) {
       mbar_init(&t_full[s], 1);
-      mbar_init(&t_empty[s], 128);
+      mbar_init(&t_empty[s], 4);      // one arrival per epilogue warp
     }
     fence_mbar_init();
   }
@@ -324,7 +324,8 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1s_fwd_kernel(const Conv1s
         else pool_row_keys<1>(v, *reinterpret_cast<int(*)[9]>(&key[9]));
       }
       tc_fence_before_sync();
-      mbar_arrive(&t_empty[grp]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&t_empty[grp]);   // 128 arrivals on one shared-memory word would serialise
       // Window wi is finished by the thread whose parity equals wi & 1; the other one hands its key over through the
       // exchange buffer of this tile's parity (double-buffered: one barrier per tile is enough).
       const uint32_t xb = xg + static_cast<uint32_t>(((tc >> 2) & 1) * (kGroups * kXchBytes));
@@ -461,10 +462,11 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
   const int rows = a.rows;
   if (threadIdx.x == 0) {
     for (int s = 0; s < kXS; ++s) { mbar_init(&x_full[s], 1); mbar_init(&x_empty[s], 3); }
-    for (int s = 0; s < kGS; ++s) { mbar_init(&g_full[s], 1); mbar_init(&g_empty[s], static_cast<uint32_t>(rows * 128)); }
+    // consumer barriers count one arrival per warp (lane 0 after __syncwarp): 128 arrivals on one shared-memory word serialise
+    for (int s = 0; s < kGS; ++s) { mbar_init(&g_full[s], 1); mbar_init(&g_empty[s], static_cast<uint32_t>(rows * 4)); }
     // slot 0 takes pooled rows 0..6 of a sample, slot 1 the next sample's (rows <= 7) or rows 7, 8 of the same one
-    mbar_init(&a_full[0], static_cast<uint32_t>((rows < kSlotRows ? rows : kSlotRows) * 128));
-    mbar_init(&a_full[1], static_cast<uint32_t>((rows > kSlotRows ? rows - kSlotRows : rows) * 128));
+    mbar_init(&a_full[0], static_cast<uint32_t>((rows < kSlotRows ? rows : kSlotRows) * 4));
+    mbar_init(&a_full[1], static_cast<uint32_t>((rows > kSlotRows ? rows - kSlotRows : rows) * 4));
     for (int s = 0; s < kASlots; ++s) mbar_init(&a_empty[s], 3);
     mbar_init(&done_bar, 3);
     fence_mbar_init();
@@ -563,7 +565,8 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
         g[pw] = lds_u16(g0 + goff + pw * (kO * 2));
         cdh[pw] = lds_u8(i0 + ioff + pw * kO);
       }
-      mbar_arrive(&g_empty[gs]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&g_empty[gs]);
       uint32_t r0[8], r1[8], r2[8];
       if (par == 0) dy_rows<0>(g, cdh, r0, r1, r2);
       else dy_rows<1>(g, cdh, r0, r1, r2);
@@ -577,7 +580,8 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
       tmem_st_32x32b_x8(at + 16, r2);
       tmem_st_wait();
       tc_fence_before_sync();
-      mbar_arrive(&a_full[slot]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&a_full[slot]);
       pr += kBGroups;
       while (pr >= rows) { pr -= rows; ++i; }
     }

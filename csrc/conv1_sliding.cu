@@ -278,7 +278,7 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1s_fwd_kernel(const Conv1s
       int i = 0;
       for (int n = blockIdx.x; n < a.B; n += gridDim.x, ++i) {
         const int slot = i % kSlots;
-        mbar_wait(&img_empty[slot], ((i / kSlots) & 1) ^ 1);
+        mbar_wait_t<true>(&img_empty[slot], ((i / kSlots) & 1) ^ 1);
         mbar_arrive_expect_tx(&img_full[slot], kImgBytes);
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
                          smem_u32(imgbuf + slot * kImgBytes)),
@@ -529,11 +529,11 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
       for (int i = 0; i < my_imgs; ++i) {
         const long long n = static_cast<long long>(blockIdx.x) + static_cast<long long>(i) * gridDim.x;
         const int xs = i % kXS, gs = i % kGS;
-        mbar_wait(&g_empty[gs], ((i / kGS) & 1) ^ 1);
+        mbar_wait_t<true>(&g_empty[gs], ((i / kGS) & 1) ^ 1);
         mbar_arrive_expect_tx(&g_full[gs], gbytes + ibytes);
         bulk_g2s(smem_u32(gbuf + gs * kGSlotBytes), a.dp1 + n * (kWinPerImg * kO), gbytes, &g_full[gs]);
         bulk_g2s(smem_u32(gbuf + gs * kGSlotBytes + kGIdxOff), a.idx1 + n * (kWinPerImg * kO), ibytes, &g_full[gs]);
-        mbar_wait(&x_empty[xs], ((i / kXS) & 1) ^ 1);
+        mbar_wait_t<true>(&x_empty[xs], ((i / kXS) & 1) ^ 1);
         mbar_arrive_expect_tx(&x_full[xs], kImgBytes);
         bulk_g2s(smem_u32(ximg + xs * kImgBytes), a.x + n * (kImgBytes / 2), kImgBytes, &x_full[xs]);
       }
@@ -555,7 +555,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
     while (i < my_imgs) {
       const int gs = i & (kGS - 1);
       if (i != waited) {   // this thread still owes an arrival on g_empty for every row it reads: the slot cannot be refilled under it
-        mbar_wait(&g_full[gs], (i / kGS) & 1);
+        mbar_wait_t<true>(&g_full[gs], (i / kGS) & 1);
         waited = i;
       }
       uint32_t g[9], cdh[9];
@@ -572,7 +572,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
       else dy_rows<1>(g, cdh, r0, r1, r2);
       const int c = pr >= kSlotRows ? 1 : 0;
       const int sc = i * nsc + c, slot = sc & 1;
-      mbar_wait(&a_empty[slot], ((sc >> 1) & 1) ^ 1);
+      mbar_wait_t<true>(&a_empty[slot], ((sc >> 1) & 1) ^ 1);
       tc_fence_after_sync();
       const uint32_t at = arow + static_cast<uint32_t>(slot * kASlotCols + (pr - c * kSlotRows) * kRowCols);
       tmem_st_32x32b_x8(at, r0);
@@ -587,7 +587,7 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
     }
     // ---------------- final reduction (first builder group): accumulators -> gw, gb ----------------
     if (grp == 0 && my_imgs > 0) {
-      mbar_wait(&done_bar, 0);
+      mbar_wait_t<true>(&done_bar, 0);
       tc_fence_after_sync();
       const uint32_t drow = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
       // red[ch][k], k = Torch7 index (c*5+kh)*5+kw for k < 75, k = 75: bias.  Parity 0 writes, then parity 1 adds.

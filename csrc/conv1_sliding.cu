@@ -54,7 +54,6 @@ __device__ __forceinline__ uint64_t make_smem_desc_nosw(uint32_t smem_addr, uint
   return d;
 }
 
-__device__ __forceinline__ uint32_t sw128(int r, int j) { return static_cast<uint32_t>(r * 128 + ((j ^ (r & 7)) << 4)); }
 
 __device__ __forceinline__ void tmem_ld_32x32b_x16(uint32_t taddr, uint32_t* r) {
   asm volatile(
@@ -389,7 +388,7 @@ constexpr int kACol0 = 176;                    // operand ring: columns 176 .. 5
 static_assert(kACol0 + kASlots * kASlotCols <= 512, "operand ring exceeds tensor memory");
 constexpr int kBGroups = 4;
 constexpr int kBwdThreads = 32 * (4 + 4 * kBGroups);   // warps 0-2: MMA issuers (one per accumulator j), warp 3: loader, then the builder groups
-constexpr int kBwdSmem = kXS * kImgBytes + 128 + kGS * kGSlotBytes + 64 * 77 * 4 + 1024;
+constexpr int kBwdSmem = kXS * kImgBytes + 128 + kGS * kGSlotBytes + 2 * 64 * 77 * 4 + 1024;
 
 __device__ __forceinline__ void tmem_st_32x32b_x8(uint32_t taddr, const uint32_t* r) {
   asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%8], {%0, %1, %2, %3, %4, %5, %6, %7};" ::"r"(r[0]), "r"(r[1]), "r"(r[2]),
@@ -454,7 +453,6 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* ximg = smem;                                   // kXS images (+128 B of zeros: kh' = 5 of the last rows reads past the last one)
   uint8_t* gbuf = smem + kXS * kImgBytes + 128;           // kGS x (dp1 rows | idx1 rows)
-  float* red = reinterpret_cast<float*>(gbuf + kGS * kGSlotBytes);   // [64][77] final reduction
   __shared__ __align__(8) uint64_t x_full[kXS], x_empty[kXS], g_full[kGS], g_empty[kGS], a_full[kASlots], a_empty[kASlots], done_bar;
   __shared__ uint32_t tmem_base_smem;
 
@@ -585,51 +583,51 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
       pr += kBGroups;
       while (pr >= rows) { pr -= rows; ++i; }
     }
-    // ---------------- final reduction (first builder group): accumulators -> gw, gb ----------------
-    if (grp == 0 && my_imgs > 0) {
-      mbar_wait_t<true>(&done_bar, 0);
-      tc_fence_after_sync();
-      const uint32_t drow = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-      // red[ch][k], k = Torch7 index (c*5+kh)*5+kw for k < 75, k = 75: bias.  Parity 0 writes, then parity 1 adds.
-#pragma unroll 1
-      for (int pass = 0; pass < 2; ++pass) {
-        if (pass == par) {
+    // ---------------- final reduction: accumulators -> gw, gb ----------------
+    // The first builder group moves its accumulator rows to shared memory in Torch7 order, one plane per column
+    // parity; then every builder thread adds the two planes into the global gradients.  CTA b starts its sweep at a
+    // different element: the CTAs finish together, and 148 atomics queued on the same line at the same time serialise.
+    const uint32_t red = smem_u32(gbuf + kGS * kGSlotBytes);   // [2][64][77] floats
+    if (my_imgs > 0) {
+      if (grp == 0) {
+        mbar_wait_t<true>(&done_bar, 0);
+        tc_fence_after_sync();
+        const uint32_t drow = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+        const uint32_t mine = red + static_cast<uint32_t>((par * kO + ch) * 77 * 4);
 #pragma unroll
-          for (int j = 0; j < 3; ++j) {
-            uint32_t v[48];
-            tmem_ld_32x32b_x32(drow + j * kDStride, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
-            tmem_ld_32x32b_x16(drow + j * kDStride + 32, &v[32]);
-            tmem_ld_wait();
+        for (int j = 0; j < 3; ++j) {
+          uint32_t v[48];
+          tmem_ld_32x32b_x32(drow + j * kDStride, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+          tmem_ld_32x32b_x16(drow + j * kDStride + 32, &v[32]);
+          tmem_ld_wait();
 #pragma unroll
-            for (int kh = 0; kh < 5; ++kh)
+          for (int kh = 0; kh < 5; ++kh)
 #pragma unroll
-              for (int e = 0; e < 8; ++e) {
-                const int p = e >> 2, c = e & 3;
-                const float val = __uint_as_float(v[kh * 8 + e]);
-                if (par == 0) {
-                  const int kw = 2 * j + p;
-                  if (kw <= 4) {
-                    if (c < 3) red[ch * 77 + (c * 5 + kh) * 5 + kw] = val;
-                    else if (kh == 0 && kw == 0) red[ch * 77 + 75] = val;
-                  }
-                } else {
-                  const int kw = 2 * j + p - 1;
-                  if (kw >= 0 && kw <= 4) {
-                    if (c < 3) red[ch * 77 + (c * 5 + kh) * 5 + kw] += val;
-                    else if (kh == 0 && kw == 0) red[ch * 77 + 75] += val;
-                  }
-                }
+            for (int e = 0; e < 8; ++e) {
+              const int p = e >> 2, c = e & 3;
+              // k = Torch7 index (c*5+kh)*5+kw for a weight tap, 75 for the bias (channel 3 is the constant 1.0)
+              if (par == 0) {
+                const int kw = 2 * j + p;
+                if (kw <= 4 && (c < 3 || (kh == 0 && kw == 0))) sts32(mine + (c < 3 ? (c * 5 + kh) * 5 + kw : 75) * 4, static_cast<int>(v[kh * 8 + e]));
+              } else {
+                const int kw = 2 * j + p - 1;
+                if (kw >= 0 && kw <= 4 && (c < 3 || (kh == 0 && kw == 0))) sts32(mine + (c < 3 ? (c * 5 + kh) * 5 + kw : 75) * 4, static_cast<int>(v[kh * 8 + e]));
               }
-          }
+            }
         }
-        asm volatile("bar.sync 2, 128;" ::: "memory");
       }
+      asm volatile("bar.sync 2, %0;" ::"n"(128 * kBGroups) : "memory");
+      constexpr int kFlushThreads = 128 * kBGroups, kElems = kO * 76;
+      constexpr int kSweeps = (kElems + kFlushThreads - 1) / kFlushThreads;
       const int t = threadIdx.x - 128;
-      for (int e = t; e < kO * 76; e += 128) {
-        const int c2 = e / 76, k = e - c2 * 76;
-        const float val = red[c2 * 77 + k];
-        if (k < kK) atomicAdd(a.gw + c2 * kK + k, val);
-        else if (a.gb != nullptr) atomicAdd(a.gb + c2, val);
+      for (int it = 0; it < kSweeps; ++it) {
+        const int e = ((it + static_cast<int>(blockIdx.x)) % kSweeps) * kFlushThreads + t;
+        if (e < kElems) {
+          const int c2 = e / 76, k = e - c2 * 76;
+          const float val = __int_as_float(lds32(red + (c2 * 77 + k) * 4)) + __int_as_float(lds32(red + ((kO + c2) * 77 + k) * 4));
+          if (k < kK) atomicAdd(a.gw + c2 * kK + k, val);
+          else if (a.gb != nullptr) atomicAdd(a.gb + c2, val);
+        }
       }
     }
   }

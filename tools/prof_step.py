@@ -14,6 +14,8 @@ torch.manual_seed(0)
 m = CifarCNN().cuda()
 tr = tadnn.BatchTrainer(m, 1e-3)
 xs = [torch.randn(4096, 3, 32, 32, device="cuda").bfloat16() for _ in range(4)]
+if m.packs_input:   # the data pipeline packs once (BatchTrainer.fit does it in its widening kernel)
+    xs = [m.pack_input(x) for x in xs]
 ys = [torch.randint(0, 10, (4096,), device="cuda") for _ in range(4)]
 for i in range(steps):
     loss = tr.step(xs[i % 4], ys[i % 4])

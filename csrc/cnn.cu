@@ -8,6 +8,7 @@
 // GEMM epilogue), and everything after the second pooling (dropout, both FC layers,
 // log-softmax, NLL loss and all of their gradients) is ONE fused kernel per direction.
 #include "common.cuh"
+#include "sm100.cuh"
 
 #include <mutex>
 
@@ -507,6 +508,8 @@ __device__ __forceinline__ void stage8(float* dst, int n, int t, Load load) {
 
 __global__ void __launch_bounds__(256) head_fwd_kernel(HeadArgs a) {
   extern __shared__ __align__(16) float sm[];
+  sm100::pdl_wait();
+  sm100::pdl_launch_dependents();
   const int HP = head_hp(a.H);
   const uint32_t seed = a.seed ^ (a.seed_dev != nullptr ? __ldg(a.seed_dev) * 0x9E3779B9u : 0u);
   float* w1t = sm;                          // [64][HP]   w1t[i*HP + j] = w1[j][i]
@@ -637,6 +640,8 @@ __global__ void __launch_bounds__(256) head_fwd_kernel(HeadArgs a) {
 
 __global__ void __launch_bounds__(256) head_bwd_kernel(HeadArgs a) {
   extern __shared__ __align__(16) float sm[];
+  sm100::pdl_wait();
+  sm100::pdl_launch_dependents();
   const int HP = head_hp(a.H);
   const uint32_t seed = a.seed ^ (a.seed_dev != nullptr ? __ldg(a.seed_dev) * 0x9E3779B9u : 0u);
   float* w1s = sm;                          // [HP][64]  as stored (row j), zero padded
@@ -848,6 +853,8 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(HeadArgs a) {
 
 // ---- optimiser / misc elementwise -------------------------------------------------------------
 __global__ void sgd_kernel(float* __restrict__ p, float* __restrict__ g, long long n, float lr, float wd, int zero_grad) {
+  sm100::pdl_wait();
+  sm100::pdl_launch_dependents();
   for (long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x; i < n;
        i += static_cast<long long>(gridDim.x) * blockDim.x) {
     const float w = p[i];
@@ -1103,7 +1110,7 @@ extern "C" int tadnn_head_forward(const tadnn_head_args* h, void* workspace, tad
   static std::atomic<unsigned long long> attr{0};
   if (int rc = ensure_dyn_smem(head_fwd_kernel, 96 * 1024, attr)) return rc;
   TADNN_REQUIRE(smem <= 96 * 1024, "head_forward: shared memory %zu too large", smem);
-  head_fwd_kernel<<<blocks, 256, smem, stream>>>(a);
+  TADNN_CHECK_CUDA(launch_pdl(head_fwd_kernel, dim3(blocks), dim3(256), smem, stream, a));
   TADNN_LAUNCH_CHECK("head_fwd");
   return 0;
 }
@@ -1157,7 +1164,7 @@ extern "C" int tadnn_head_forward_noalloc(const tadnn_head_args* h, tadnn_stream
   TADNN_CHECK_CUDA(cudaMemsetAsync(a.counter, 0, sizeof(unsigned int), stream));
   int blocks = (h->B + kHeadS - 1) / kHeadS;
   if (blocks > kNoAllocMaxBlocks) blocks = kNoAllocMaxBlocks;
-  head_fwd_kernel<<<blocks, 256, smem, stream>>>(a);
+  TADNN_CHECK_CUDA(launch_pdl(head_fwd_kernel, dim3(blocks), dim3(256), smem, stream, a));
   TADNN_LAUNCH_CHECK("head_fwd_noalloc");
   return 0;
 }
@@ -1173,14 +1180,14 @@ extern "C" int tadnn_head_backward(const tadnn_head_args* h, tadnn_stream_t stre
   static std::atomic<unsigned long long> attr{0};
   if (int rc = ensure_dyn_smem(head_bwd_kernel, 160 * 1024, attr)) return rc;
   TADNN_REQUIRE(smem <= 160 * 1024, "head_backward: shared memory %zu too large", smem);
-  head_bwd_kernel<<<blocks, 256, smem, stream>>>(a);
+  TADNN_CHECK_CUDA(launch_pdl(head_bwd_kernel, dim3(blocks), dim3(256), smem, stream, a));
   TADNN_LAUNCH_CHECK("head_bwd");
   return 0;
 }
 
 extern "C" int tadnn_sgd_step(float* p, float* g, long long n, float lr, float weight_decay, int zero_grad, tadnn_stream_t stream_) {
   if (n <= 0) return 0;
-  sgd_kernel<<<grid_for(n, 256), 256, 0, static_cast<cudaStream_t>(stream_)>>>(p, g, n, lr, weight_decay, zero_grad);
+  TADNN_CHECK_CUDA(launch_pdl(sgd_kernel, dim3(grid_for(n, 256)), dim3(256), 0, static_cast<cudaStream_t>(stream_), p, g, n, lr, weight_decay, zero_grad));
   TADNN_LAUNCH_CHECK("sgd_step");
   return 0;
 }

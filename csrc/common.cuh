@@ -71,6 +71,28 @@ inline int ensure_dyn_smem(K kern, int bytes, std::atomic<unsigned long long>& d
   return 0;
 }
 
+// Launch `kern` so that it may overlap the tail of the previous kernel in the stream (programmatic dependent launch):
+// ONLY for kernels that call sm100::pdl_wait() before touching memory written by earlier kernels.  Falls back to a normal
+// launch while the stream is being captured into a CUDA graph, or when TADNN_PDL=0 is set in the environment.
+bool pdl_enabled();
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (pdl_enabled() && cudaStreamIsCapturing(stream, &cap) == cudaSuccess && cap == cudaStreamCaptureStatusNone) {
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+  }
+  return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
+}
+
 // ---- device helpers ---------------------------------------------------------
 __device__ __forceinline__ float bf16_to_f32(__nv_bfloat16 v) { return __bfloat162float(v); }
 

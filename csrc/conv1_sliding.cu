@@ -205,6 +205,8 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1s_fwd_kernel(const Conv1s
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = tmem_base_smem;
+  pdl_wait();                 // everything above touched only this CTA's shared / tensor memory
+  pdl_launch_dependents();
   // The weight operand lives in tensor memory for the whole kernel: row m = (parity, channel) in lane m, its 128 K
   // values as 64 columns of bf16 pairs.  Written by the first epilogue group (one warp per lane quarter).
   if (warp >= kIssuers + 1 && warp < kIssuers + 5) {
@@ -476,6 +478,8 @@ __global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1s
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = tmem_base_smem;
+  pdl_wait();                 // everything above touched only this CTA's shared / tensor memory
+  pdl_launch_dependents();
   const int my_imgs = (a.B - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
 
   if (warp < 3) {
@@ -708,7 +712,7 @@ extern "C" int tadnn_conv1s_pool_forward(const void* x_nhwc4, const void* w_pack
   a.x = static_cast<const __nv_bfloat16*>(x_nhwc4); a.w = static_cast<const __nv_bfloat16*>(w_packed);
   a.p1 = static_cast<__nv_bfloat16*>(p1); a.idx1 = static_cast<unsigned char*>(idx1); a.B = B;
   const int grid = B < sm_count() ? B : sm_count();
-  conv1s_fwd_kernel<true><<<grid, kFwdThreads, kFwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
+  TADNN_CHECK_CUDA(launch_pdl(conv1s_fwd_kernel<true>, dim3(grid), dim3(kFwdThreads), kFwdSmem, static_cast<cudaStream_t>(stream), a));
   TADNN_LAUNCH_CHECK("conv1s_pool_fwd_tcgen05");
   return 0;
 }
@@ -727,7 +731,7 @@ extern "C" int tadnn_conv1s_pool_backward(const void* x_nhwc4, const void* dp1, 
   a.idx1 = const_cast<unsigned char*>(static_cast<const unsigned char*>(idx1));
   a.gw = grad_weight; a.gb = grad_bias; a.B = B; a.rows = rows;
   const int grid = B < sm_count() ? B : sm_count();
-  conv1s_bwd_kernel<<<grid, kBwdThreads, kBwdSmem, static_cast<cudaStream_t>(stream)>>>(a);
+  TADNN_CHECK_CUDA(launch_pdl(conv1s_bwd_kernel, dim3(grid), dim3(kBwdThreads), kBwdSmem, static_cast<cudaStream_t>(stream), a));
   TADNN_LAUNCH_CHECK("conv1s_pool_bwd_tcgen05");
   return 0;
 }

@@ -75,7 +75,6 @@ conv2_fwd_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
     fence_mbar_init();
   }
   if (warp == 2) tmem_alloc<128>(&tmem_base_smem);
-  if (threadIdx.x < kO) s_bias[threadIdx.x] = a.bias[threadIdx.x];
   // rows 125..127 of every A slot are never written by TMA; give them defined (zero) contents once
   for (int i = threadIdx.x; i < kFStages * 3 * 8; i += blockDim.x) {
     const int s = i / 24, rem = i % 24;
@@ -86,6 +85,10 @@ conv2_fwd_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_constan
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = tmem_base_smem;
+  pdl_wait();                 // everything above touched only this CTA's shared / tensor memory
+  pdl_launch_dependents();
+  if (threadIdx.x < kO) s_bias[threadIdx.x] = a.bias[threadIdx.x];
+  __syncthreads();
 
   if (warp == 0) {
     // ===================== TMA producer: 25 (activation box, filter slice) pairs per tile =====================
@@ -263,6 +266,8 @@ conv2_wgrad_kernel(const __grid_constant__ CUtensorMap tma_x, const __grid_const
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = tmem_base_smem;
+  pdl_wait();                 // everything above touched only this CTA's shared / tensor memory
+  pdl_launch_dependents();
 
   if (warp == 0) {
     if (elect_one()) {
@@ -351,6 +356,8 @@ constexpr int kTtCols = kTtFH * kTtFW * kC;      // 4032
 __global__ void __launch_bounds__(256) cnn_pack_shadows_kernel(const float* __restrict__ w1, const float* __restrict__ b1, const float* __restrict__ w2,
                                                                __nv_bfloat16* __restrict__ w1p, __nv_bfloat16* __restrict__ w2p,
                                                                uint4* __restrict__ Tt) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int n_w1 = b1 ? 128 * 128 : 64 * 80, n_w2 = kO * kTaps * kC / 8, n_t = kTtRows * kTtCols / 8;
   const int total = n_w1 + n_w2 + n_t;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
@@ -397,6 +404,8 @@ __global__ void __launch_bounds__(256) cnn_pack_shadows_kernel(const float* __re
 
 // gw2[o, (c*5+kh)*5+kw] += dwp[o, tap*64 + c];  dwp = 0 (ready for the next step's red.adds)
 __global__ void __launch_bounds__(256) conv2_wgrad_unpack_kernel(float* __restrict__ dwp, float* __restrict__ gw) {
+  pdl_wait();
+  pdl_launch_dependents();
   const int total = kO * kTaps * kC;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     const int c = i & 63, tap = (i >> 6) % kTaps, o = i / (kTaps * kC);
@@ -438,7 +447,7 @@ extern "C" int tadnn_conv2_pool_forward(const void* p1, const void* w2_packed, c
   a.B = B;
   a.num_tiles = (B + kFImgs - 1) / kFImgs;
   const int grid = a.num_tiles < sm_count() ? a.num_tiles : sm_count();
-  conv2_fwd_kernel<<<grid, kThreads, kFSmem, static_cast<cudaStream_t>(stream_)>>>(tx, tw, a);
+  TADNN_CHECK_CUDA(launch_pdl(conv2_fwd_kernel, dim3(grid), dim3(kThreads), kFSmem, static_cast<cudaStream_t>(stream_), tx, tw, a));
   TADNN_LAUNCH_CHECK("conv2_pool_fwd_tcgen05");
   return 0;
 }
@@ -462,14 +471,14 @@ extern "C" int tadnn_conv2_wgrad(const void* p1, const void* da2w, float* dw_pac
   if (splits > a.num_kb) splits = a.num_kb;
   if (splits < 1) splits = 1;
   a.splits = splits;
-  conv2_wgrad_kernel<<<kKH * splits, kThreads, kWSmem, static_cast<cudaStream_t>(stream_)>>>(tx, tg, a);
+  TADNN_CHECK_CUDA(launch_pdl(conv2_wgrad_kernel, dim3(kKH * splits), dim3(kThreads), kWSmem, static_cast<cudaStream_t>(stream_), tx, tg, a));
   TADNN_LAUNCH_CHECK("conv2_wgrad_tcgen05");
   return 0;
 }
 
 extern "C" int tadnn_conv2_wgrad_unpack(float* dw_packed, float* grad_weight, tadnn_stream_t stream_) {
   TADNN_REQUIRE(dw_packed && grad_weight, "conv2_wgrad_unpack: null argument");
-  conv2_wgrad_unpack_kernel<<<(kO * kTaps * kC + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream_)>>>(dw_packed, grad_weight);
+  TADNN_CHECK_CUDA(launch_pdl(conv2_wgrad_unpack_kernel, dim3((kO * kTaps * kC + 255) / 256), dim3(256), 0, static_cast<cudaStream_t>(stream_), dw_packed, grad_weight));
   TADNN_LAUNCH_CHECK("conv2_wgrad_unpack");
   return 0;
 }
@@ -479,8 +488,9 @@ extern "C" int tadnn_cnn_pack_shadows(const float* w1, const float* w2, void* w1
   TADNN_REQUIRE(w1 && w2 && w1_packed && w2_packed && toeplitz_t, "cnn_pack_shadows: null argument");
   TADNN_REQUIRE(((reinterpret_cast<uintptr_t>(w2_packed) | reinterpret_cast<uintptr_t>(toeplitz_t)) & 15) == 0, "cnn_pack_shadows: outputs must be 16-byte aligned");
   const int total = 64 * 80 + kO * kTaps * kC / 8 + kTtRows * kTtCols / 8;
-  cnn_pack_shadows_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-      w1, nullptr, w2, static_cast<__nv_bfloat16*>(w1_packed), static_cast<__nv_bfloat16*>(w2_packed), static_cast<uint4*>(toeplitz_t));
+  TADNN_CHECK_CUDA(launch_pdl(cnn_pack_shadows_kernel, dim3((total + 255) / 256), dim3(256), 0, static_cast<cudaStream_t>(stream_), w1,
+                              static_cast<const float*>(nullptr), w2, static_cast<__nv_bfloat16*>(w1_packed), static_cast<__nv_bfloat16*>(w2_packed),
+                              static_cast<uint4*>(toeplitz_t)));
   TADNN_LAUNCH_CHECK("cnn_pack_shadows");
   return 0;
 }
@@ -491,8 +501,8 @@ extern "C" int tadnn_cnn_pack_shadows_sliding(const float* w1, const float* b1, 
   TADNN_REQUIRE(((reinterpret_cast<uintptr_t>(w2_packed) | reinterpret_cast<uintptr_t>(toeplitz_t) | reinterpret_cast<uintptr_t>(w1x_packed)) & 15) == 0,
                 "cnn_pack_shadows_sliding: outputs must be 16-byte aligned");
   const int total = 128 * 128 + kO * kTaps * kC / 8 + kTtRows * kTtCols / 8;
-  cnn_pack_shadows_kernel<<<(total + 255) / 256, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
-      w1, b1, w2, static_cast<__nv_bfloat16*>(w1x_packed), static_cast<__nv_bfloat16*>(w2_packed), static_cast<uint4*>(toeplitz_t));
+  TADNN_CHECK_CUDA(launch_pdl(cnn_pack_shadows_kernel, dim3((total + 255) / 256), dim3(256), 0, static_cast<cudaStream_t>(stream_), w1, b1, w2,
+                              static_cast<__nv_bfloat16*>(w1x_packed), static_cast<__nv_bfloat16*>(w2_packed), static_cast<uint4*>(toeplitz_t)));
   TADNN_LAUNCH_CHECK("cnn_pack_shadows");
   return 0;
 }

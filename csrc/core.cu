@@ -1,5 +1,6 @@
 // Library-wide plumbing: last-error text, launch accounting, device properties.
 #include "common.cuh"
+#include <stdlib.h>
 
 #include <stdarg.h>
 
@@ -23,6 +24,14 @@ void set_error(const char* fmt, ...) {
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
+}
+
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("TADNN_PDL");
+    return !(e && e[0] == '0');
+  }();
+  return on;
 }
 
 int note_launch(const char* kernel_name) {

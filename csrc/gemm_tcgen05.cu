@@ -224,6 +224,8 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
   __syncthreads();
   tc_fence_after_sync();
   const uint32_t tmem_base = tmem_base_smem;
+  pdl_wait();                 // everything above touched only this CTA's shared / tensor memory
+  pdl_launch_dependents();
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -601,7 +603,12 @@ int launch(const tadnn_gemm_args* a, const DevArgs& d, cudaStream_t stream) {
   const int splits = d.split_k > 1 ? d.split_k : 1;
   const int work = num_m * num_n * splits;
   const int grid = work < sm_count() ? work : sm_count();
-  kern<<<grid, kThreads, C::kSmemBytes, stream>>>(ta, tb, tc, tp, d);
+  // plain GEMMs may overlap the tail of the kernel before them; the ones that talk to peers keep the strict stream order
+  if (d.n_push == 0 && d.n_sig == 0 && d.wait_flags == nullptr) {
+    TADNN_CHECK_CUDA(launch_pdl(kern, dim3(grid), dim3(kThreads), C::kSmemBytes, stream, ta, tb, tc, tp, d));
+  } else {
+    kern<<<grid, kThreads, C::kSmemBytes, stream>>>(ta, tb, tc, tp, d);
+  }
   TADNN_LAUNCH_CHECK("gemm_bf16_tcgen05");
   return 0;
 }

@@ -26,6 +26,15 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// ---- programmatic dependent launch -------------------------------------------------
+// A kernel launched with the programmatic-stream-serialization attribute (common.cuh: launch_pdl) may become resident
+// while its predecessor in the stream is still draining.  pdl_wait() blocks until the predecessor grid has completed and
+// its memory is visible: it must come before the first access to anything the predecessor wrote (no-op for a normal
+// launch).  pdl_launch_dependents() lets the successor's blocks be scheduled as soon as every block of this grid has
+// called it (they then sit in their own pdl_wait()).
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---- mbarrier ---------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));

@@ -72,6 +72,9 @@ struct DevArgs {
   const uint32_t* wait_flags;
   uint32_t wait_target;
   int wait_cols_per_src;
+  // structurally sparse B: bit kb of kmask[n_blk] clear = k-block kb of column tile n_blk is all zeros and is skipped
+  int use_kmask;
+  uint32_t kmask[32];
 };
 
 __device__ __forceinline__ uint32_t ld_acquire_sys_u32(const uint32_t* p) {
@@ -246,7 +249,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
           }
           asm volatile("fence.proxy.async;" ::: "memory");  // the TMA (async proxy) reads below must see those writes
         }
+        const uint32_t km = p.use_kmask ? p.kmask[n_blk] : 0xffffffffu;
         for (int kb = kb0; kb < kb1; ++kb) {
+          if (!((km >> (kb & 31)) & 1u)) continue;
           mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * C::kStageBytes;
           uint8_t* sb = sa + kABytes;
@@ -287,10 +292,18 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
         const int split = w % splits;
         const int kb0 = split * kb_per_split;
         const int kb1 = min(num_kb, kb0 + kb_per_split);
+        uint32_t km = 0xffffffffu;
+        if (p.use_kmask) {
+          int m_blk, n_blk;
+          decode_tile(w / splits, num_m, num_n, p.group_m, p.n_rotate, m_blk, n_blk);
+          km = p.kmask[n_blk];
+        }
+        bool first = true;
         mbar_wait(&tmem_empty_bar[acc], acc_phase ^ 1);
         tc_fence_after_sync();
         const uint32_t tmem_d = tmem_base + static_cast<uint32_t>(acc * BN);
         for (int kb = kb0; kb < kb1; ++kb) {
+          if (!((km >> (kb & 31)) & 1u)) continue;
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after_sync();
           const uint32_t a_addr = smem_u32(smem + stage * C::kStageBytes);
@@ -301,8 +314,9 @@ gemm_bf16_tcgen05_kernel(const __grid_constant__ CUtensorMap tma_a,
                                      : make_smem_desc_sw128(a_addr + k * 32, 16, 1024);
             const uint64_t db = B_MN ? make_smem_desc_sw128(b_addr + k * 2048, BK * 128, 1024)
                                      : make_smem_desc_sw128(b_addr + k * 32, 16, 1024);
-            umma_f16(tmem_d, da, db, idesc, (kb > kb0 || k > 0) ? 1u : 0u);
+            umma_f16(tmem_d, da, db, idesc, (!first || k > 0) ? 1u : 0u);
           }
+          first = false;
           umma_commit(&empty_bar[stage]);  // frees the smem slot once these MMAs retire
           if (++stage == C::kStages) {
             stage = 0;
@@ -682,6 +696,20 @@ extern "C" int tadnn_gemm_bf16(const tadnn_gemm_args* a, tadnn_stream_t stream_)
   d.wait_flags = static_cast<const uint32_t*>(a->wait_flags);
   d.wait_target = a->wait_target;
   d.wait_cols_per_src = a->wait_cols_per_src;
+  d.use_kmask = 0;
+  if (a->kblock_mask != nullptr) {
+    const int tn = a->tile_n;
+    TADNN_REQUIRE(tn == 64 || tn == 128 || tn == 256, "tadnn_gemm_bf16: kblock_mask needs an explicit tile_n");
+    const int nn = (a->N + tn - 1) / tn, nk = (a->K + 63) / 64;
+    TADNN_REQUIRE(nn <= 32 && nk <= 32 && a->split_k <= 1 && a->n_kblock_mask == nn,
+                  "tadnn_gemm_bf16: kblock_mask supports <= 32 column tiles and <= 32 k-blocks, no split-K, one word per column tile (%d given, %d tiles)",
+                  a->n_kblock_mask, nn);
+    for (int i = 0; i < nn; ++i) {
+      TADNN_REQUIRE((a->kblock_mask[i] & (nk >= 32 ? 0xffffffffu : ((1u << nk) - 1u))) != 0, "tadnn_gemm_bf16: kblock_mask[%d] selects no k-block", i);
+      d.kmask[i] = a->kblock_mask[i];
+    }
+    d.use_kmask = 1;
+  }
   TADNN_REQUIRE(d.wait_flags == nullptr || (d.wait_cols_per_src > 0 && d.wait_cols_per_src % 64 == 0 && d.flag_stride > 0),
                 "tadnn_gemm_bf16: wait_flags needs wait_cols_per_src (a multiple of 64) and flag_stride");
   if (a->rs_width > 0) {

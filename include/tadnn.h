@@ -95,6 +95,11 @@ typedef struct tadnn_gemm_args {
   const void* wait_flags;
   unsigned int wait_target;
   int wait_cols_per_src;
+  /* Structurally sparse B (e.g. the Toeplitz matrix of a transposed convolution): HOST array with one word per column
+   * tile of width tile_n (which must be given); bit kb clear = the 64-deep k-block kb of that column tile is all zeros
+   * and is neither loaded nor multiplied.  <= 32 column tiles, <= 32 k-blocks, no split-K.  NULL: dense. */
+  const unsigned int* kblock_mask;
+  int n_kblock_mask;
 } tadnn_gemm_args;
 
 int tadnn_gemm_bf16(const tadnn_gemm_args* args, tadnn_stream_t stream);
@@ -411,6 +416,37 @@ int tadnn_head_backward(const tadnn_head_args* a, tadnn_stream_t stream);
  *  - The looked-up address is cached for the life of the process: after a cudaDeviceReset() the
  *    cached value is stale, so a process that resets a device must not call this again on it. */
 int tadnn_head_forward_noalloc(const tadnn_head_args* a, tadnn_stream_t stream);
+
+/* The whole fused step of the example CNN (sliding-operand conv1 path) in one host call (csrc/cnn_step.cu):
+ * phase 1 = pack the bf16 operand copies, forward, loss, and the backward pass down to dp1 (everything but conv1's
+ * gradients: nine launches); phase 2 = conv1's weight and bias gradients (one launch); 3 = both.  The split lets a
+ * data-parallel caller start synchronising the finished gradients before conv1's backward runs.  Every buffer is the
+ * caller's: xq NHWC4 bf16 [B,32,32,4]; parameters and gradients fp32 in Torch7 layouts (gradients are += ); w1x [128,128],
+ * w2p [64,1600], Tt [576,4032] bf16 and dwp [64,1600] fp32 (zero on entry, zero again on return) are the operand copies;
+ * p1/idx1 [B,9,9,64] bf16/u8, p2/idx2 [B,64], hidden [B,100], logp [B,10], loss [1] fp32, da2w [B*9,64] bf16,
+ * dp1 [B,9,9,64] bf16 (rows 7, 8 zero and left alone), head_ws from tadnn_head_workspace_bytes (zero-filled once).
+ * tt_mask: HOST k-block mask of Tt for 256-wide column tiles (16 words) or NULL.  forward_only: stop after the loss. */
+typedef struct tadnn_cnn_step_args {
+  const void* xq;
+  const long long* target;
+  int B;
+  const float *w1, *b1, *w2, *b2, *fw1, *fb1, *fw2, *fb2;
+  float *gw1, *gb1, *gw2, *gb2, *gfw1, *gfb1, *gfw2, *gfb2;
+  void *w1x, *w2p, *Tt;
+  float* dwp;
+  void *p1, *idx1, *p2, *idx2;
+  float *hidden, *logp, *loss;
+  void *da2w, *dp1, *head_ws;
+  float dropout_p;
+  unsigned int seed;
+  const unsigned int* seed_dev;
+  float grad_scale;
+  const unsigned int* tt_mask;
+  int n_tt_mask;
+  int phase;
+  int forward_only;
+} tadnn_cnn_step_args;
+int tadnn_cnn_step(const tadnn_cnn_step_args* args, tadnn_stream_t stream);
 
 /* p -= lr * (g + wd * p); optionally g = 0.  Replaces accUpdateGradParameters' in-place step
  * (datamodule.lua:142) for batched training on the flat buffer. */

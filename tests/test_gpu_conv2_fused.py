@@ -193,3 +193,25 @@ def test_conv1_backward_bias_side_output(B):
     K.colsum_relu_mask(dp1, p1, gb_ref)
     assert torch.equal(gw, gw_ref) or ((gw - gw_ref).norm() / gw_ref.norm()).item() < 1e-5
     assert torch.allclose(gb, gb_ref, rtol=1e-4, atol=1e-3)
+
+
+def test_gemm_kblock_mask_skips_only_structural_zeros():
+    """The transposed conv2 as a GEMM against the Toeplitz matrix: with the k-block mask (structural zeros skipped) the result
+    is bit-identical to the dense product."""
+    from tadnn.models.cifar_cnn import _TT_MASK
+    from tadnn.ops import cnn as K
+    torch.manual_seed(3)
+    w1 = torch.randn(64, 75, device="cuda")
+    w2 = torch.randn(64, 1600, device="cuda") * 0.05
+    w1p = torch.empty(64, 80, device="cuda", dtype=torch.bfloat16)
+    w2p = torch.empty(64, 1600, device="cuda", dtype=torch.bfloat16)
+    Tt = torch.empty(576, 4032, device="cuda", dtype=torch.bfloat16)
+    K.cnn_pack_shadows(w1, w2, w1p, w2p, Tt)
+    assert sum(bin(m).count("1") for m in _TT_MASK) < 0.7 * 9 * len(_TT_MASK)
+    for B in (5, 300, 1000):
+        g = torch.randn(B, 576, device="cuda").bfloat16()
+        dense = K.gemm_bf16(g, Tt, b_mn_major=True, tile_n=256)
+        sparse = K.gemm_bf16(g, Tt, b_mn_major=True, tile_n=256, kblock_mask=_TT_MASK)
+        assert torch.equal(dense, sparse)
+        ref = g.float() @ Tt.float()
+        assert ((sparse.float() - ref).norm() / ref.norm()).item() < 1e-2

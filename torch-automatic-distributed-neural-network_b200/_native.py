@@ -34,6 +34,7 @@ class GemmArgs(C.Structure):
         ("tile_n", C.c_int), ("rs_width", C.c_int), ("aux_tanh_out", C.c_void_p), ("ld_aux", C.c_int), ("n_rotate", C.c_int), ("rs_slab_major", C.c_int),
         ("sig_flags", C.c_void_p * 8), ("n_sig", C.c_int), ("sig_src", C.c_int), ("flag_stride", C.c_int),
         ("wait_flags", C.c_void_p), ("wait_target", C.c_uint), ("wait_cols_per_src", C.c_int),
+        ("kblock_mask", C.POINTER(C.c_uint)), ("n_kblock_mask", C.c_int),
     ]
 
 
@@ -98,6 +99,9 @@ def ptr(t) -> int:
 
 
 def stream_ptr(stream=None) -> int:
+    """Raw cudaStream_t of ``stream`` (default: the current stream of the current device).  Called once per kernel launch:
+    goes straight to the two C accessors instead of building a ``torch.cuda.Stream`` object (5 us each, ~60 us per step)."""
+    if stream is not None:
+        return int(stream.cuda_stream)
     import torch
-    s = stream if stream is not None else torch.cuda.current_stream()
-    return int(s.cuda_stream)
+    return int(torch._C._cuda_getCurrentRawStream(torch._C._cuda_getDevice()))

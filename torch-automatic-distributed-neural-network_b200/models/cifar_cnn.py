@@ -47,6 +47,26 @@ def _shadows(dev, wkey: int):
     return sh
 
 
+def _toeplitz_kblock_mask(tile_n: int = 256):
+    """Which 64-deep k-blocks (= window position pos of conv2's 3x3 pooled outputs) of the Toeplitz matrix
+    ``Tt[pos*64 + o, (fy*9 + fx)*64 + c]`` are non-zero for each ``tile_n``-wide column tile: tap (kh, kw) =
+    (fy - pos // 3, fx - pos % 3) must lie inside the 5x5 filter.  About half of the blocks are structural zeros."""
+    px_per_tile = tile_n // 64
+    masks = []
+    for t in range((63 + px_per_tile - 1) // px_per_tile):
+        m = 0
+        for p in range(t * px_per_tile, min(63, (t + 1) * px_per_tile)):
+            fy, fx = divmod(p, 9)
+            for pos in range(9):
+                if 0 <= fy - pos // 3 < 5 and 0 <= fx - pos % 3 < 5:
+                    m |= 1 << pos
+        masks.append(m)
+    return masks
+
+
+_TT_MASK = _toeplitz_kblock_mask(256)
+
+
 def _dp1_buffer(dev, B):
     """[B,9,9,64] gradient buffer whose rows y >= 7 are zero and stay zero (the dgrad GEMM writes y < 7 only)."""
     key = (str(dev), int(B))
@@ -172,7 +192,8 @@ def _cnn_backward(sv, gw1, gb1, gw2, gb2, gfw1, gfb1, gfw2, gfb2, gloss=None, ta
         K.conv2_wgrad(p1, da2w, sh["dwp"])
         K.conv2_wgrad_unpack(sh["dwp"], gw2)
         dp1 = _dp1_buffer(dev, B)
-        K.gemm_bf16(da2w.view(B, 576), sh["Tt"], b_mn_major=True, out=dp1.view(B, 81 * 64)[:, :7 * 9 * 64])
+        K.gemm_bf16(da2w.view(B, 576), sh["Tt"], b_mn_major=True, out=dp1.view(B, 81 * 64)[:, :7 * 9 * 64], tile_n=256,
+                    kblock_mask=_TT_MASK)
         if tail_ready is not None:
             tail_ready()  # every gradient except conv1's is complete (and nothing below reads those parameters)
         if sv.get("sliding"):
@@ -363,11 +384,60 @@ class CifarCNN(torch.nn.Module, T7Protocol):
         self._step += 1
         pd = self.dropout if self.training else 0.0
         seed = (self._seed * 2654435761 + self._step * 40503) & 0xFFFFFFFF
+        if self.packs_input and all(p.dtype == torch.float32 and p.grad.dtype == torch.float32 for p in ps):
+            return self._native_step(x, target, ps, pd, seed, tail_ready)
         with torch.no_grad():
             loss, _logp, sv = _cnn_forward(x, target, *[p.data for p in ps], pd, seed, self.fused_conv1, self.conv2_mode,
                                            seed_dev=getattr(self, "_seed_dev", None), sliding=self.conv1_kernel == "sliding")
             cb = (lambda: tail_ready(self.conv2_weight)) if (tail_ready is not None and sv.get("fused2")) else None
             _cnn_backward(sv, *[p.grad for p in ps], tail_ready=cb)
+        return loss
+
+    def _native_step(self, x, target, ps, pd, seed, tail_ready):
+        """The fused step through ``tadnn_cnn_step`` (csrc/cnn_step.cu): one or two native calls launch all ten kernels;
+        activations live in a workspace kept per (device, batch size)."""
+        from ..ops import cnn as K
+        dev, B = x.device, x.shape[0]
+        xq = x.contiguous() if is_packed_input(x) else self.pack_input(x)
+        ws = self.__dict__.get("_step_ws")
+        if ws is None or ws["key"] != (dev, B, self.conv2_weight.data_ptr()):
+            sh = _shadows(dev, self.conv2_weight.data_ptr())
+            bf, u8, f32 = torch.bfloat16, torch.uint8, torch.float32
+            t = {"p1": torch.empty((B, 9, 9, 64), device=dev, dtype=bf), "idx1": torch.empty((B, 9, 9, 64), device=dev, dtype=u8),
+                 "p2": torch.empty((B, 64), device=dev, dtype=bf), "idx2": torch.empty((B, 64), device=dev, dtype=u8),
+                 "hidden": torch.empty((B, 100), device=dev, dtype=f32), "logp": torch.empty((B, 10), device=dev, dtype=f32),
+                 "da2w": torch.empty((B * 9, 64), device=dev, dtype=bf), "dp1": _dp1_buffer(dev, B), "head_ws": K.head_workspace(dev),
+                 "w1x": sh["w1x"], "w2p": sh["w2p"], "Tt": sh["Tt"], "dwp": sh["dwp"]}
+            a = K.CnnStepArgs()
+            for n, v in t.items():
+                setattr(a, n, v.data_ptr())
+            a.B = B
+            a.grad_scale = 1.0
+            a.tt_mask = (C.c_uint * len(_TT_MASK))(*_TT_MASK)
+            a.n_tt_mask = len(_TT_MASK)
+            ws = {"key": (dev, B, self.conv2_weight.data_ptr()), "t": t, "a": a}
+            self.__dict__["_step_ws"] = ws
+        a = ws["a"]
+        tgt = target if (target.dtype == torch.int64 and target.device == dev and target.is_contiguous()) \
+            else target.to(device=dev, dtype=torch.int64).contiguous()
+        loss = torch.empty((), device=dev, dtype=torch.float32)
+        a.xq, a.target, a.loss = xq.data_ptr(), tgt.data_ptr(), loss.data_ptr()
+        a.w1, a.b1, a.w2, a.b2, a.fw1, a.fb1, a.fw2, a.fb2 = [p.data_ptr() for p in ps]
+        a.gw1, a.gb1, a.gw2, a.gb2, a.gfw1, a.gfb1, a.gfw2, a.gfb2 = [p.grad.data_ptr() for p in ps]
+        a.dropout_p, a.seed = float(pd), int(seed)
+        sd = getattr(self, "_seed_dev", None)
+        a.seed_dev = sd.data_ptr() if sd is not None else None
+        a.forward_only = 0
+        if tail_ready is None:
+            a.phase = 3
+            K.cnn_step(a)
+        else:
+            a.phase = 1
+            K.cnn_step(a)
+            tail_ready(self.conv2_weight)   # every gradient except conv1's is complete
+            a.phase = 2
+            K.cnn_step(a)
+        ws["keep"] = (xq, tgt)   # inputs of the launches just queued: alive until the next step replaces them
         return loss
 
     # ---- the reference's own workload: one sample per step (datamodule.lua:134-158) ----------------

@@ -21,6 +21,22 @@ class HeadArgs(C.Structure):
     ]
 
 
+class CnnStepArgs(C.Structure):
+    """Mirror of ``tadnn_cnn_step_args`` (include/tadnn.h)."""
+    _fields_ = ([("xq", C.c_void_p), ("target", C.c_void_p), ("B", C.c_int)]
+                + [(n, C.c_void_p) for n in ("w1", "b1", "w2", "b2", "fw1", "fb1", "fw2", "fb2",
+                                             "gw1", "gb1", "gw2", "gb2", "gfw1", "gfb1", "gfw2", "gfb2",
+                                             "w1x", "w2p", "Tt", "dwp", "p1", "idx1", "p2", "idx2",
+                                             "hidden", "logp", "loss", "da2w", "dp1", "head_ws")]
+                + [("dropout_p", C.c_float), ("seed", C.c_uint), ("seed_dev", C.c_void_p), ("grad_scale", C.c_float),
+                   ("tt_mask", C.POINTER(C.c_uint)), ("n_tt_mask", C.c_int), ("phase", C.c_int), ("forward_only", C.c_int)])
+
+
+def cnn_step(args: "CnnStepArgs") -> None:
+    """Forward + backward of the fused CNN step as one native call (csrc/cnn_step.cu)."""
+    _native.check(_native.lib().tadnn_cnn_step(C.byref(args), _s()), "tadnn_cnn_step")
+
+
 _F4 = C.c_float * 4
 C_ll = C.c_longlong
 
@@ -282,5 +298,5 @@ def auto_split_k(M: int, N: int, K: int, tile_n: int = 256) -> int:
     return max(1, min(kb, 148 // max(1, tiles)))
 
 
-__all__ = ["nhwc4_pack", "conv1s_weight_pack", "conv1s_pool_forward", "conv1s_pool_backward", "cnn_pack_shadows_sliding", "u8_to_bf16", "conv2_pool_forward", "conv2_wgrad", "conv2_wgrad_unpack", "cnn_pack_shadows", "conv1_pool_backward_bias", "im2col_winfirst", "conv_toeplitz_pack", "expand_corner", "conv1_weight_pack", "conv1_pool_forward", "conv1_pool_backward", "im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "colsum_relu_mask_corner", "conv_weight_pack",
+__all__ = ["CnnStepArgs", "cnn_step", "nhwc4_pack", "conv1s_weight_pack", "conv1s_pool_forward", "conv1s_pool_backward", "cnn_pack_shadows_sliding", "u8_to_bf16", "conv2_pool_forward", "conv2_wgrad", "conv2_wgrad_unpack", "cnn_pack_shadows", "conv1_pool_backward_bias", "im2col_winfirst", "conv_toeplitz_pack", "expand_corner", "conv1_weight_pack", "conv1_pool_forward", "conv1_pool_backward", "im2col", "col2im", "maxpool_fwd", "maxpool_relu_bwd", "colsum_bf16", "colsum_relu_mask", "colsum_relu_mask_corner", "conv_weight_pack",
            "conv_wgrad_unpack", "head_workspace", "sgd_step", "auto_split_k", "HeadArgs", "gemm_bf16"]

@@ -23,7 +23,7 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False,
               tile_n: int = 0, rs_width: int = 0, aux_tanh_out: torch.Tensor | None = None,
               n_rotate: int = 0, rs_slab_major: bool = False, sig_flags=None, sig_src: int = 0,
               flag_stride: int = 0, wait_flags: int = 0, wait_target: int = 0, wait_cols_per_src: int = 0,
-              stream=None) -> torch.Tensor:
+              kblock_mask=None, stream=None) -> torch.Tensor:
     """out[M,N] = act(alpha * A·Bᵀ + bias).
 
     a: [M,K] (or [K,M] if a_mn_major), b: [N,K] (or [K,N] if b_mn_major); bf16, last dim
@@ -32,6 +32,8 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False,
     offset ``push_col_offset`` (fused all-gather).  ``sig_flags`` (one raw pointer per target, own rank
     included if it consumes too) makes that push self-announcing and ``wait_flags``/``wait_target``/
     ``wait_cols_per_src`` make this GEMM the consumer of such a gathered A operand (K13, include/tadnn.h).
+    ``kblock_mask`` (sequence of ints, one per ``tile_n``-wide column tile): bit kb clear = k-block kb (64 deep) of that
+    column tile of B is structurally zero and is skipped.
     """
     assert a.is_cuda and b.is_cuda and a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16
     assert a.dim() == 2 and b.dim() == 2 and a.stride(1) == 1 and b.stride(1) == 1
@@ -76,6 +78,9 @@ def gemm_bf16(a: torch.Tensor, b: torch.Tensor, *, a_mn_major: bool = False,
         args.sig_flags[i] = int(ptr)
     args.sig_src, args.flag_stride = int(sig_src), int(flag_stride)
     args.wait_flags, args.wait_target, args.wait_cols_per_src = int(wait_flags), int(wait_target), int(wait_cols_per_src)
+    if kblock_mask is not None:
+        km = (C.c_uint * len(kblock_mask))(*[int(v) for v in kblock_mask])
+        args.kblock_mask, args.n_kblock_mask = km, len(kblock_mask)
     if aux_tanh_out is not None:
         assert aux_tanh_out.dtype == torch.bfloat16 and aux_tanh_out.stride(1) == 1 and aux_tanh_out.shape == (M, N)
         args.aux_tanh_out, args.ld_aux = aux_tanh_out.data_ptr(), aux_tanh_out.stride(0)

@@ -105,17 +105,25 @@ class FlatBuffer:
         """Re-point ``p.grad`` at the flat views if user code replaced them (e.g.
         ``zero_grad(set_to_none=True)`` followed by a backward).  Returns #copies made."""
         n = 0
+        views = self.__dict__.get("_grad_views")
+        if views is None:   # built once: slicing + view per parameter is most of this function's cost on the per-step path
+            views = [(p, g.region[g.half + off:g.half + off + p.numel()].view(p.shape))
+                     for g in self.groups.values() for p, off in zip(g.params, g.offsets)]
+            self.__dict__["_grad_views"] = views
+        stale = [(p, gv) for p, gv in views if p.grad is not gv]
+        if not stale:
+            return 0
         with torch.no_grad():
-            for g in self.groups.values():
-                for p, off in zip(g.params, g.offsets):
-                    gv = g.region[g.half + off:g.half + off + p.numel()].view(p.shape)
-                    if p.grad is None:
-                        gv.zero_()
-                        p.grad = gv
-                    elif p.grad.data_ptr() != gv.data_ptr():
-                        gv.copy_(p.grad)
-                        p.grad = gv
-                        n += 1
+            for p, gv in stale:
+                if p.grad is None:
+                    gv.zero_()
+                    p.grad = gv
+                elif p.grad.data_ptr() != gv.data_ptr():
+                    gv.copy_(p.grad)
+                    p.grad = gv
+                    n += 1
+                else:
+                    p.grad = gv
         return n
 
     def zero_grads(self):

@@ -926,7 +926,7 @@ extern "C" int tadnn_allreduce_ll(tadnn_comm* c, unsigned long long ll_off, unsi
                 "allreduce_ll: staging area or data range outside the heap");
   const int n = static_cast<int>(count);
   int blocks = (n + 511) / 512;
-  if (blocks > 32) blocks = 32;
+  if (blocks > 64) blocks = 64;
   if (sgd) allreduce_ll_kernel<1><<<blocks, 512, 0, static_cast<cudaStream_t>(stream_)>>>(c->dev, ll_off, off_bytes, param_off, n, scale, lr, weight_decay, epoch);
   else allreduce_ll_kernel<0><<<blocks, 512, 0, static_cast<cudaStream_t>(stream_)>>>(c->dev, ll_off, off_bytes, 0, n, scale, 0.f, 0.f, epoch);
   TADNN_LAUNCH_CHECK(sgd ? "allreduce_sgd_ll" : "allreduce_ll");

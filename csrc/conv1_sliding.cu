@@ -450,7 +450,9 @@ __device__ __forceinline__ void dy_rows(const uint32_t (&g)[9], const uint32_t (
   r0[7] = r1[7] = r2[7] = 0u;
 }
 
-__global__ void __launch_bounds__(kBwdThreads, 1) conv1s_bwd_kernel(const Conv1sArgs a) {
+// launch bound of 896 threads = at most 72 registers: with the 640 threads actually launched that leaves room on the SM for a
+// 512-thread communication kernel of the data-parallel step to run next to this one
+__global__ void __launch_bounds__(896, 1) conv1s_bwd_kernel(const Conv1sArgs a) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   uint8_t* ximg = smem;                                   // kXS images (+128 B of zeros: kh' = 5 of the last rows reads past the last one)

@@ -126,7 +126,7 @@ int tadnn_gemm_bf16_2cta(const void* A, int lda, const void* B, int ldb, void* C
 #define TADNN_COMM_CHANNELS 8
 #define TADNN_COMM_MAX_BLOCKS 512
 #define TADNN_IPC_HANDLE_BYTES 64
-#define TADNN_LL_MAX_FLOATS 16384 /* largest message of the low-latency all-reduce (64 KB) */
+#define TADNN_LL_MAX_FLOATS 131072 /* largest message of the low-latency all-reduce (512 KB) */
 
 typedef struct tadnn_comm tadnn_comm;
 

@@ -63,7 +63,7 @@ def main():
                     fails.append(f"allreduce n={n} {dtype} algo={algo}: ranks disagree bitwise")
     # low-latency path (algo 4 = {value, epoch} pairs, no barrier): many calls in a row, varying sizes
     for it in range(60):
-        n = (1, 7, 640, 4864, 16384)[it % 5]
+        n = (1, 7, 640, 4864, 16384, 115000)[it % 6]
         view = big[:n]
         x = torch.randn(n, device=dev)
         view.copy_(x)
@@ -176,7 +176,7 @@ def main():
     # ---- gradient all-reduce fused with the SGD step: every algo, vs the two-pass statement
     for n in (64, 4800, 114944, (1 << 20) + 64):
         for algo in ((1, 2, 3, 4) if ctx.has_multicast else (1, 2, 4)):
-            if algo == 4 and n > 16384:
+            if algo == 4 and n > 131072:
                 continue
             if algo == 1 and n > (1 << 18):
                 continue

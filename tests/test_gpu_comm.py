@@ -98,9 +98,9 @@ def test_allreduce_ll_emulated_single_launch(world):
     row (both parities of the double-buffered staging area), all ranks in one cooperative launch."""
     from tadnn import _native
     lib = _native.lib()
-    LL = 16384
+    from tadnn.parallel.symm import LL_MAX_FLOATS as LL
     ll_bytes = 2 * world * LL * 8
-    heap = 8 << 20
+    heap = ll_bytes + (8 << 20)
     comms = (C.c_void_p * world)()
     _native.check(lib.tadnn_comm_create_local(world, C.c_ulonglong(heap), comms), "create_local")
     try:

@@ -39,7 +39,7 @@ CH_DEFAULT = 0   # mpi.allreduceTensor & friends on the compute stream
 CH_DP = 1        # data-parallel gradient/parameter sync on the comm stream
 CH_TP = 2        # model-parallel layer collectives
 CH_BARRIER = 3
-LL_MAX_FLOATS = 16384  # TADNN_LL_MAX_FLOATS: largest message of the low-latency all-reduce
+LL_MAX_FLOATS = 131072  # TADNN_LL_MAX_FLOATS: largest message of the low-latency all-reduce
 
 
 class CommTimeout(_native.NativeError):
@@ -361,13 +361,13 @@ class SymmContext:
 
     def allreduce_offset(self, off: int, count: int, dtype: torch.dtype, scale: float = 1.0,
                          algo: int = 0, max_blocks: int = 0, channel: int = CH_DEFAULT, stream=None):
-        """``algo``: 0 auto (low-latency pairs up to 64 KB of fp32, then one-shot / NVLS / two-shot by size),
+        """``algo``: 0 auto (low-latency pairs up to 512 KB of fp32, then one-shot / NVLS / two-shot by size),
         1 one-shot, 2 two-shot, 3 NVLS, 4 low-latency."""
         self.check()
         if self._ll_ok(count, dtype, algo, channel):
             return self._ll_launch(off, 0, count, scale, False, 0.0, 0.0, channel, stream)
         if algo == 4:
-            raise ValueError("low-latency all-reduce: fp32 messages of at most 64 KB on channels 0-2 only")
+            raise ValueError("low-latency all-reduce: fp32 messages of at most 512 KB on channels 0-2 only")
         _native.check(_native.lib().tadnn_allreduce(
             self.handle, C.c_ulonglong(off), C.c_ulonglong(count), C.c_int(_DT[dtype]),
             C.c_float(scale), C.c_int(algo), C.c_int(max_blocks), C.c_int(channel),

@@ -16,6 +16,9 @@ from typing import Callable, Iterator, Optional
 import torch
 
 
+_DP_TAIL = os.environ.get("TADNN_DP_TAIL", "1") not in ("0", "false")
+
+
 class BatchTrainer:
     def __init__(self, model: torch.nn.Module, learningRate: float = 1e-3, weightDecay: float = 0.0,
                  criterion: Optional[Callable] = None):
@@ -76,7 +79,10 @@ class BatchTrainer:
                 # synchronised SGD step as fused all-reduce+update kernels: the range whose gradients are
                 # complete early goes on the side stream from inside backward, the rest at the end
                 lr, wd = self.learningRate, self.weightDecay
-                loss = self.model.forward_backward(x, y, tail_ready=lambda p: st.fused_tail(p, lr, wd))
+                # TADNN_DP_TAIL=0: no early synchronisation of the finished gradients on the side stream (one fused
+                # all-reduce + update at the end of backward instead)
+                tail = (lambda p: st.fused_tail(p, lr, wd)) if _DP_TAIL else None
+                loss = self.model.forward_backward(x, y, tail_ready=tail)
                 st.fused_finish(self.model, lr, wd)
                 self.steps += 1
                 return loss.detach()

@@ -100,7 +100,7 @@ class BatchTrainer:
     def fit(self, data: torch.Tensor, targets: torch.Tensor, batch: int, steps: int,
             start: int = 0, depth: int = 4, input_affine=None) -> Iterator[float]:
         """Run ``steps`` steps over ``data``/``targets`` (host tensors, ideally pinned; wraps
-        around), yielding each step's loss as a Python float (read one step late).  Per step:
+        around), yielding each step's loss as a Python float (read two steps late, so that the host stays ahead of the device).  Per step:
         one H2D copy of that step's inputs (and one of its labels) and one D2H read of its loss.
 
         ``data`` may be ``uint8`` (what CIFAR is on disk: 3 KB per image instead of 6 KB as bf16):
@@ -142,41 +142,50 @@ class BatchTrainer:
             wide = [torch.empty((batch,) + tuple(data.shape[1:]), dtype=torch.bfloat16, device=dev) for _ in range(depth)]
         ready = [torch.cuda.Event() for _ in range(depth)]
         consumed = [torch.cuda.Event() for _ in range(depth)]
-        host_loss = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
-        loss_ev = [torch.cuda.Event(), torch.cuda.Event()]
-        loss_ready = [torch.cuda.Event(), torch.cuda.Event()]
+        LAG = 2   # a loss is read LAG steps after its step was queued: the host stays that far ahead of the device
+        host_loss = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(LAG + 1)]
+        loss_ev = [torch.cuda.Event() for _ in range(LAG + 1)]
+        loss_ready = [torch.cuda.Event() for _ in range(LAG + 1)]
         rs = self.__dict__.setdefault("_read_stream", torch.cuda.Stream())  # loss read-back: never blocks the compute stream
-        dev_loss = [torch.zeros((), dtype=torch.float32, device=dev) for _ in range(2)]
+        dev_loss = [torch.zeros((), dtype=torch.float32, device=dev) for _ in range(LAG + 1)]
 
         ws = self.__dict__.setdefault("_widen_stream", torch.cuda.Stream()) if u8 else None
         copied = [torch.cuda.Event() for _ in range(depth)]
         widened = [torch.cuda.Event() for _ in range(depth)]
 
+        set_stream = torch.cuda.set_stream
+
         def issue(s):
             k = s % depth
             i = ((start + s) % nb) * batch
-            with torch.cuda.stream(cs):
-                if s >= depth:
-                    cs.wait_event(consumed[k])   # step s - depth has consumed this slot (its bytes were widened before that)
-                bufs[k][0].copy_(data[i:i + batch], non_blocking=True)
-                bufs[k][1].copy_(targets[i:i + batch], non_blocking=True)
-                if not u8:
-                    ready[k].record(cs)
-                else:
-                    copied[k].record(cs)
+            try:
+                _issue(s, k, i)
+            finally:
+                set_stream(main)
+
+        def _issue(s, k, i):
+            set_stream(cs)
+            if s >= depth:
+                cs.wait_event(consumed[k])   # step s - depth has consumed this slot (its bytes were widened before that)
+            bufs[k][0].copy_(data[i:i + batch], non_blocking=True)
+            bufs[k][1].copy_(targets[i:i + batch], non_blocking=True)
+            if not u8:
+                ready[k].record(cs)
+            else:
+                copied[k].record(cs)
             if u8:
                 # the widening kernel runs on its own stream: it may have to wait for SMs while the persistent compute
                 # kernels are resident, and the copy stream must keep the PCIe link busy meanwhile
-                with torch.cuda.stream(ws):
-                    ws.wait_event(copied[k])
-                    if s >= depth:
-                        ws.wait_event(consumed[k])                     # wide[k] of step s - depth has been consumed
-                    if packer is not None:
-                        packer(bufs[k][0], aff, out=wide[k])
-                    else:
-                        u8_to_bf16(bufs[k][0], plane, C, aff[0], aff[1], out=wide[k])
-                    widened[k].record(ws)
-                    ready[k].record(ws)
+                set_stream(ws)
+                ws.wait_event(copied[k])
+                if s >= depth:
+                    ws.wait_event(consumed[k])                     # wide[k] of step s - depth has been consumed
+                if packer is not None:
+                    packer(bufs[k][0], aff, out=wide[k])
+                else:
+                    u8_to_bf16(bufs[k][0], plane, C, aff[0], aff[1], out=wide[k])
+                widened[k].record(ws)
+                ready[k].record(ws)
 
         for s in range(min(depth - 1, steps)):
             issue(s)
@@ -187,20 +196,24 @@ class BatchTrainer:
             main.wait_event(ready[k])
             loss = self.step(wide[k] if u8 else bufs[k][0], bufs[k][1])
             consumed[k].record(main)
-            j = s & 1
+            j = s % (LAG + 1)
             dev_loss[j].copy_(loss)          # the step's loss tensor may be reused by the next step: keep a copy
             loss_ready[j].record(main)
-            with torch.cuda.stream(rs):
+            set_stream(rs)                   # (torch.cuda.stream() as a context manager costs ~8 us per use)
+            try:
                 rs.wait_event(loss_ready[j])
                 host_loss[j].copy_(dev_loss[j], non_blocking=True)
                 loss_ev[j].record(rs)
-            if s >= 1:
-                loss_ev[j ^ 1].synchronize()
-                yield float(host_loss[j ^ 1])
-        if steps >= 1:
-            j = (steps - 1) & 1
-            loss_ev[j].synchronize()
-            yield float(host_loss[j])
+            finally:
+                set_stream(main)
+            if s >= LAG:
+                jj = (s - LAG) % (LAG + 1)
+                loss_ev[jj].synchronize()
+                yield float(host_loss[jj])
+        for s2 in range(max(0, steps - LAG), steps):
+            jj = s2 % (LAG + 1)
+            loss_ev[jj].synchronize()
+            yield float(host_loss[jj])
         self.h2d_bytes_per_step = batch * (data[0].numel() * data.element_size() + targets[0].numel() * targets.element_size())
         self.d2h_bytes_per_step = 4
 

@@ -506,7 +506,12 @@ __device__ __forceinline__ void stage8(float* dst, int n, int t, Load load) {
   }
 }
 
-__global__ void __launch_bounds__(256) head_fwd_kernel(HeadArgs a) {
+// FIXED: the example network's sizes (D = 64, H = 100, NC = 10) as compile-time constants: the index arithmetic of the
+// staging loops (divisions by H) was most of the 8 K instructions each warp of these kernels executed.
+template <bool FIXED>
+__global__ void __launch_bounds__(256) head_fwd_kernel(HeadArgs a_in) {
+  HeadArgs a = a_in;
+  if (FIXED) { a.D = 64; a.H = 100; a.NC = 10; }
   extern __shared__ __align__(16) float sm[];
   sm100::pdl_wait();
   sm100::pdl_launch_dependents();
@@ -638,7 +643,10 @@ __global__ void __launch_bounds__(256) head_fwd_kernel(HeadArgs a) {
   }
 }
 
-__global__ void __launch_bounds__(256) head_bwd_kernel(HeadArgs a) {
+template <bool FIXED>
+__global__ void __launch_bounds__(256) head_bwd_kernel(HeadArgs a_in) {
+  HeadArgs a = a_in;
+  if (FIXED) { a.D = 64; a.H = 100; a.NC = 10; }
   extern __shared__ __align__(16) float sm[];
   sm100::pdl_wait();
   sm100::pdl_launch_dependents();
@@ -1108,9 +1116,13 @@ extern "C" int tadnn_head_forward(const tadnn_head_args* h, void* workspace, tad
   if (blocks > cap) blocks = cap;
   const size_t smem = head_fwd_smem(h->D, h->H, h->NC);
   static std::atomic<unsigned long long> attr{0};
-  if (int rc = ensure_dyn_smem(head_fwd_kernel, 96 * 1024, attr)) return rc;
+  static std::atomic<unsigned long long> attr_fixed{0};
+  if (int rc = ensure_dyn_smem(head_fwd_kernel<false>, 96 * 1024, attr)) return rc;
+  if (int rc = ensure_dyn_smem(head_fwd_kernel<true>, 96 * 1024, attr_fixed)) return rc;
+  const bool fixed = h->D == 64 && h->H == 100 && h->NC == 10;
   TADNN_REQUIRE(smem <= 96 * 1024, "head_forward: shared memory %zu too large", smem);
-  TADNN_CHECK_CUDA(launch_pdl(head_fwd_kernel, dim3(blocks), dim3(256), smem, stream, a));
+  if (fixed) TADNN_CHECK_CUDA(launch_pdl(head_fwd_kernel<true>, dim3(blocks), dim3(256), smem, stream, a));
+  else TADNN_CHECK_CUDA(launch_pdl(head_fwd_kernel<false>, dim3(blocks), dim3(256), smem, stream, a));
   TADNN_LAUNCH_CHECK("head_fwd");
   return 0;
 }
@@ -1152,7 +1164,7 @@ extern "C" int tadnn_head_forward_noalloc(const tadnn_head_args* h, tadnn_stream
     scratch = g_noalloc_ptr[dev];
     if (scratch == nullptr) {
       TADNN_CHECK_CUDA(cudaGetSymbolAddress(&scratch, tadnn_head_noalloc_scratch));
-      TADNN_CHECK_CUDA(cudaFuncSetAttribute(head_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+      TADNN_CHECK_CUDA(cudaFuncSetAttribute(head_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
       g_noalloc_ptr[dev] = scratch;
     }
   }
@@ -1164,7 +1176,7 @@ extern "C" int tadnn_head_forward_noalloc(const tadnn_head_args* h, tadnn_stream
   TADNN_CHECK_CUDA(cudaMemsetAsync(a.counter, 0, sizeof(unsigned int), stream));
   int blocks = (h->B + kHeadS - 1) / kHeadS;
   if (blocks > kNoAllocMaxBlocks) blocks = kNoAllocMaxBlocks;
-  TADNN_CHECK_CUDA(launch_pdl(head_fwd_kernel, dim3(blocks), dim3(256), smem, stream, a));
+  TADNN_CHECK_CUDA(launch_pdl(head_fwd_kernel<false>, dim3(blocks), dim3(256), smem, stream, a));
   TADNN_LAUNCH_CHECK("head_fwd_noalloc");
   return 0;
 }
@@ -1178,9 +1190,12 @@ extern "C" int tadnn_head_backward(const tadnn_head_args* h, tadnn_stream_t stre
   if (blocks > sm_count()) blocks = sm_count();
   const size_t smem = head_bwd_smem(h->D, h->H, h->NC);
   static std::atomic<unsigned long long> attr{0};
-  if (int rc = ensure_dyn_smem(head_bwd_kernel, 160 * 1024, attr)) return rc;
+  static std::atomic<unsigned long long> attr_fixed{0};
+  if (int rc = ensure_dyn_smem(head_bwd_kernel<false>, 160 * 1024, attr)) return rc;
+  if (int rc = ensure_dyn_smem(head_bwd_kernel<true>, 160 * 1024, attr_fixed)) return rc;
   TADNN_REQUIRE(smem <= 160 * 1024, "head_backward: shared memory %zu too large", smem);
-  TADNN_CHECK_CUDA(launch_pdl(head_bwd_kernel, dim3(blocks), dim3(256), smem, stream, a));
+  if (h->D == 64 && h->H == 100 && h->NC == 10) TADNN_CHECK_CUDA(launch_pdl(head_bwd_kernel<true>, dim3(blocks), dim3(256), smem, stream, a));
+  else TADNN_CHECK_CUDA(launch_pdl(head_bwd_kernel<false>, dim3(blocks), dim3(256), smem, stream, a));
   TADNN_LAUNCH_CHECK("head_bwd");
   return 0;
 }

@@ -506,6 +506,16 @@ __device__ __forceinline__ void stage8(float* dst, int n, int t, Load load) {
   }
 }
 
+// global -> shared without a register round trip (Ampere-style cp.async): every copy of a staging phase is in flight at
+// once, so the phase costs one L2 latency instead of one per batch of register loads
+__device__ __forceinline__ void cp_async4(float* dst, const float* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(dst))), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async16(float* dst, const float* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(dst))), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
 // FIXED: the example network's sizes (D = 64, H = 100, NC = 10) as compile-time constants: the index arithmetic of the
 // staging loops (divisions by H) was most of the 8 K instructions each warp of these kernels executed.
 template <bool FIXED>
@@ -527,6 +537,13 @@ __global__ void __launch_bounds__(256) head_fwd_kernel(HeadArgs a_in) {
   __shared__ float block_loss;
   __shared__ bool is_last;
   const int t = threadIdx.x;
+  if (FIXED) {   // HP == H, D == 64: no padding to write; the transposed fc1 weights go element by element
+    for (int i = t; i < kHeadD * 100; i += 256) {
+      const int j = i >> 6, d = i & 63;          // coalesced global reads, conflict-free transposed writes
+      cp_async4(w1t + d * 100 + j, a.w1 + i);
+    }
+    for (int i = t; i < 10 * 100 / 4; i += 256) cp_async16(w2s + 4 * i, a.w2 + 4 * i);
+  } else {
   stage8(w1t, kHeadD * HP, t, [&](int i) {
     const int d = i / HP, j = i - d * HP;
     return (d < a.D && j < a.H) ? __ldg(a.w1 + j * a.D + d) : 0.f;
@@ -535,6 +552,7 @@ __global__ void __launch_bounds__(256) head_fwd_kernel(HeadArgs a_in) {
     const int c = i / HP, j = i - c * HP;
     return j < a.H ? __ldg(a.w2 + c * a.H + j) : 0.f;
   });
+  }
   for (int i = t; i < HP; i += 256) b1[i] = i < a.H ? __ldg(a.b1 + i) : 0.f;
   if (t < kHeadC) b2[t] = t < a.NC ? __ldg(a.b2 + t) : 0.f;
   const int nJ = HP >> 2;
@@ -543,6 +561,7 @@ __global__ void __launch_bounds__(256) head_fwd_kernel(HeadArgs a_in) {
   const int chunks = (a.B + kHeadS - 1) / kHeadS;
   for (int ch = blockIdx.x; ch < chunks; ch += gridDim.x) {
     const int base = ch * kHeadS;
+    if (FIXED) cp_async_wait_all();   // (the weights; nothing is pending after the first chunk)
     __syncthreads();
     {
       float v[8];
@@ -661,6 +680,10 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(HeadArgs a_in) {
   float* sdl = sh + kHeadS * HP;            // [32][32]  dL/dlogits
   float* sgb = sdl + kHeadS * kHeadC;       // [8][64]   bias-gradient partials of the layer before the pool
   const int t = threadIdx.x;
+  if (FIXED) {   // both weight matrices are stored exactly as staged: 16-byte asynchronous copies, waited for with the first chunk
+    for (int i = t; i < 100 * kHeadD / 4; i += 256) cp_async16(w1s + 4 * i, a.w1 + 4 * i);
+    for (int i = t; i < 10 * 100 / 4; i += 256) cp_async16(w2s + 4 * i, a.w2 + 4 * i);
+  } else {
   stage8(w1s, HP * kHeadD, t, [&](int i) {
     const int j = i >> 6, d = i & 63;
     return (j < a.H && d < a.D) ? __ldg(a.w1 + j * a.D + d) : 0.f;
@@ -669,6 +692,7 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(HeadArgs a_in) {
     const int c = i / HP, j = i - c * HP;
     return j < a.H ? __ldg(a.w2 + c * a.H + j) : 0.f;
   });
+  }
   const float inv_b = a.grad_scale * (a.grad_scale_dev != nullptr ? *a.grad_scale_dev : 1.0f) / static_cast<float>(a.B);
   const int nJ = HP >> 2;
   // register accumulators
@@ -691,18 +715,31 @@ __global__ void __launch_bounds__(256) head_bwd_kernel(HeadArgs a_in) {
     const int base = ch * kHeadS;
     __syncthreads();
     // ---- A: stage the chunk
+    const bool async_chunk = FIXED && base + kHeadS <= a.B;   // a full chunk of the fixed-size network: hidden and logp are contiguous
+    if (async_chunk) {
+      const float* hsrc = a.hbuf + static_cast<long long>(base) * 100;
+      for (int i = t; i < kHeadS * 100 / 4; i += 256) cp_async16(sh + 4 * i, hsrc + 4 * i);
+      const float* lsrc = a.logp + static_cast<long long>(base) * 10;
+      for (int i = t; i < kHeadS * 10; i += 256) {
+        const int s = i / 10, c = i - s * 10;
+        cp_async4(sdl + s * kHeadC + c, lsrc + i);
+      }
+    }
     stage8(sd, kHeadS * kHeadD, t, [&](int i) {
       const int s = i >> 6, d = i & 63;
       return (base + s < a.B && d < a.D) ? __bfloat162float(a.p2[static_cast<long long>(base + s) * a.D + d]) : 0.f;
     });
-    stage8(sh, kHeadS * HP, t, [&](int i) {
-      const int s = i / HP, j = i - s * HP;
-      return (base + s < a.B && j < a.H) ? __ldg(a.hbuf + static_cast<long long>(base + s) * a.H + j) : 0.f;
-    });
-    stage8(sdl, kHeadS * kHeadC, t, [&](int i) {
-      const int s = i >> 5, c = i & 31;
-      return (base + s < a.B && c < a.NC) ? __ldg(a.logp + static_cast<long long>(base + s) * a.NC + c) : 1.f;
-    });
+    if (!async_chunk) {
+      stage8(sh, kHeadS * HP, t, [&](int i) {
+        const int s = i / HP, j = i - s * HP;
+        return (base + s < a.B && j < a.H) ? __ldg(a.hbuf + static_cast<long long>(base + s) * a.H + j) : 0.f;
+      });
+      stage8(sdl, kHeadS * kHeadC, t, [&](int i) {
+        const int s = i >> 5, c = i & 31;
+        return (base + s < a.B && c < a.NC) ? __ldg(a.logp + static_cast<long long>(base + s) * a.NC + c) : 1.f;
+      });
+    }
+    if (FIXED) cp_async_wait_all();   // the chunk's copies and, the first time, the weights
     __syncthreads();
     // dropout on the staged input; dL/dlogits from the staged log-probabilities (own elements only: no sync needed in between)
 #pragma unroll
@@ -1119,7 +1156,7 @@ extern "C" int tadnn_head_forward(const tadnn_head_args* h, void* workspace, tad
   static std::atomic<unsigned long long> attr_fixed{0};
   if (int rc = ensure_dyn_smem(head_fwd_kernel<false>, 96 * 1024, attr)) return rc;
   if (int rc = ensure_dyn_smem(head_fwd_kernel<true>, 96 * 1024, attr_fixed)) return rc;
-  const bool fixed = h->D == 64 && h->H == 100 && h->NC == 10;
+  const bool fixed = h->D == 64 && h->H == 100 && h->NC == 10 && ((reinterpret_cast<uintptr_t>(h->w1) | reinterpret_cast<uintptr_t>(h->w2)) & 15) == 0;
   TADNN_REQUIRE(smem <= 96 * 1024, "head_forward: shared memory %zu too large", smem);
   if (fixed) TADNN_CHECK_CUDA(launch_pdl(head_fwd_kernel<true>, dim3(blocks), dim3(256), smem, stream, a));
   else TADNN_CHECK_CUDA(launch_pdl(head_fwd_kernel<false>, dim3(blocks), dim3(256), smem, stream, a));
@@ -1194,7 +1231,9 @@ extern "C" int tadnn_head_backward(const tadnn_head_args* h, tadnn_stream_t stre
   if (int rc = ensure_dyn_smem(head_bwd_kernel<false>, 160 * 1024, attr)) return rc;
   if (int rc = ensure_dyn_smem(head_bwd_kernel<true>, 160 * 1024, attr_fixed)) return rc;
   TADNN_REQUIRE(smem <= 160 * 1024, "head_backward: shared memory %zu too large", smem);
-  if (h->D == 64 && h->H == 100 && h->NC == 10) TADNN_CHECK_CUDA(launch_pdl(head_bwd_kernel<true>, dim3(blocks), dim3(256), smem, stream, a));
+  if (h->D == 64 && h->H == 100 && h->NC == 10 &&
+      ((reinterpret_cast<uintptr_t>(h->w1) | reinterpret_cast<uintptr_t>(h->w2) | reinterpret_cast<uintptr_t>(h->hidden)) & 15) == 0)
+    TADNN_CHECK_CUDA(launch_pdl(head_bwd_kernel<true>, dim3(blocks), dim3(256), smem, stream, a));
   else TADNN_CHECK_CUDA(launch_pdl(head_bwd_kernel<false>, dim3(blocks), dim3(256), smem, stream, a));
   TADNN_LAUNCH_CHECK("head_bwd");
   return 0;

@@ -73,8 +73,9 @@ inline int ensure_dyn_smem(K kern, int bytes, std::atomic<unsigned long long>& d
 
 // Launch `kern` so that it may overlap the tail of the previous kernel in the stream (programmatic dependent launch):
 // ONLY for kernels that call sm100::pdl_wait() before touching memory written by earlier kernels.  Falls back to a normal
-// launch while the stream is being captured into a CUDA graph, or when TADNN_PDL=0 is set in the environment.
+// launch when TADNN_PDL=0 is set in the environment (TADNN_PDL_GRAPH=0: only inside CUDA-graph capture).
 bool pdl_enabled();
+bool pdl_in_graphs();   // the attribute is kept while a stream is being captured (programmatic edges in the graph) unless TADNN_PDL_GRAPH=0
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
   cudaLaunchConfig_t cfg = {};
@@ -86,7 +87,7 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-  if (pdl_enabled() && cudaStreamIsCapturing(stream, &cap) == cudaSuccess && cap == cudaStreamCaptureStatusNone) {
+  if (pdl_enabled() && cudaStreamIsCapturing(stream, &cap) == cudaSuccess && (cap == cudaStreamCaptureStatusNone || pdl_in_graphs())) {
     cfg.attrs = attr;
     cfg.numAttrs = 1;
   }

@@ -34,6 +34,14 @@ bool pdl_enabled() {
   return on;
 }
 
+bool pdl_in_graphs() {
+  static const bool on = [] {
+    const char* e = getenv("TADNN_PDL_GRAPH");
+    return !(e && e[0] == '0');
+  }();
+  return on;
+}
+
 int note_launch(const char* kernel_name) {
   std::lock_guard<std::mutex> lk(g_mu);
   ++g_launches;

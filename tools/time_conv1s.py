@@ -16,4 +16,5 @@ dp1[:, :7, :7] = torch.randn(B, 7, 7, 64, device="cuda").bfloat16()
 gw, gb = torch.zeros(64, 75, device="cuda"), torch.zeros(64, device="cuda")
 print(tag, "conv1s bwd us (median, min):", timeit(lambda: K.conv1s_pool_backward(xq, dp1, idx1, gw, gb, rows=7)))
 for Bn in (148, 1024):
+    print(tag, f"conv1s fwd B={Bn} us:", timeit(lambda: K.conv1s_pool_forward(xq[:Bn], wx)))
     print(tag, f"conv1s bwd B={Bn} us:", timeit(lambda: K.conv1s_pool_backward(xq[:Bn], dp1[:Bn], idx1[:Bn], gw, gb, rows=7)))

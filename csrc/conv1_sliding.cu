@@ -308,11 +308,19 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1s_fwd_kernel(const Conv1s
       tc_fence_after_sync();
       const bool two = t < 4;        // two pooled rows (18 windows), or the last one of the image (9 windows)
       int key[18];
+      // the accumulator stage goes back to the MMA issuers as soon as its last column is in registers, before the keys
+      // of that row are computed
+      auto release = [&]() {
+        tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&t_empty[grp]);   // 128 arrivals on one shared-memory word would serialise
+      };
       {
         uint32_t v[48];
         tmem_ld_32x32b_x32(taddr, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
         tmem_ld_32x32b_x16(taddr + 32, &v[32]);
         tmem_ld_wait();
+        if (!two) release();
         if (par == 0) pool_row_keys<0>(v, *reinterpret_cast<int(*)[9]>(&key[0]));
         else pool_row_keys<1>(v, *reinterpret_cast<int(*)[9]>(&key[0]));
       }
@@ -321,12 +329,10 @@ __global__ void __launch_bounds__(kFwdThreads, 1) conv1s_fwd_kernel(const Conv1s
         tmem_ld_32x32b_x32(taddr + 48, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
         tmem_ld_32x32b_x16(taddr + 80, &v[32]);
         tmem_ld_wait();
+        release();
         if (par == 0) pool_row_keys<0>(v, *reinterpret_cast<int(*)[9]>(&key[9]));
         else pool_row_keys<1>(v, *reinterpret_cast<int(*)[9]>(&key[9]));
       }
-      tc_fence_before_sync();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&t_empty[grp]);   // 128 arrivals on one shared-memory word would serialise
       // Window wi is finished by the thread whose parity equals wi & 1; the other one hands its key over through the
       // exchange buffer of this tile's parity (double-buffered: one barrier per tile is enough).
       const uint32_t xb = xg + static_cast<uint32_t>(((tc >> 2) & 1) * (kGroups * kXchBytes));

@@ -357,6 +357,10 @@ constexpr int kLLMaxFloats = TADNN_LL_MAX_FLOATS;
 template <int MODE>
 __global__ void __launch_bounds__(512) allreduce_ll_kernel(CommDev c, size_t ll_off, size_t data_off, size_t p_off, int n, float scale,
                                                            float lr, float wd, uint32_t epoch) {
+  // programmatic dependent launch: the gradients were written by the kernel before this one; the kernel after it (the next
+  // step's operand packing) waits for this grid's completion in its own griddepcontrol.wait
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int rank = my_rank(c);
   const int stride = gridDim.x * blockDim.x;
   const int tid = blockIdx.x * blockDim.x + threadIdx.x;
@@ -927,8 +931,11 @@ extern "C" int tadnn_allreduce_ll(tadnn_comm* c, unsigned long long ll_off, unsi
   const int n = static_cast<int>(count);
   int blocks = (n + 511) / 512;
   if (blocks > 64) blocks = 64;
-  if (sgd) allreduce_ll_kernel<1><<<blocks, 512, 0, static_cast<cudaStream_t>(stream_)>>>(c->dev, ll_off, off_bytes, param_off, n, scale, lr, weight_decay, epoch);
-  else allreduce_ll_kernel<0><<<blocks, 512, 0, static_cast<cudaStream_t>(stream_)>>>(c->dev, ll_off, off_bytes, 0, n, scale, 0.f, 0.f, epoch);
+  const size_t zero = 0;
+  if (sgd) TADNN_CHECK_CUDA(launch_pdl(allreduce_ll_kernel<1>, dim3(blocks), dim3(512), 0, static_cast<cudaStream_t>(stream_), c->dev, static_cast<size_t>(ll_off),
+                                       static_cast<size_t>(off_bytes), static_cast<size_t>(param_off), n, scale, lr, weight_decay, epoch));
+  else TADNN_CHECK_CUDA(launch_pdl(allreduce_ll_kernel<0>, dim3(blocks), dim3(512), 0, static_cast<cudaStream_t>(stream_), c->dev, static_cast<size_t>(ll_off),
+                                   static_cast<size_t>(off_bytes), zero, n, scale, 0.f, 0.f, epoch));
   TADNN_LAUNCH_CHECK(sgd ? "allreduce_sgd_ll" : "allreduce_ll");
   return 0;
 }

@@ -30,7 +30,7 @@ ENV_SWITCHES = {
     "TADNN_SYMM_STAGING_MB": "staging area inside the heap for tensors that live outside it (default 128)",
     "TADNN_COMM_LL": "0 = never use the low-latency pair all-reduce (fp32 messages up to 512 KB)",
     "TADNN_DP_FUSED_SGD": "0 = separate all-reduce and optimiser launches instead of the fused all-reduce + SGD kernels",
-    "TADNN_DP_TAIL": "0 = no early synchronisation of the finished gradients on a side stream during conv1's backward",
+    "TADNN_DP_TAIL": "1 / 0 = force / forbid the early synchronisation of the finished gradients on a side stream during conv1's backward (default: on above two ranks)",
     "TADNN_PDL": "0 = plain stream order instead of programmatic dependent launch between the kernels of a step",
     "TADNN_PDL_GRAPH": "0 = no programmatic-dependency edges inside captured CUDA graphs (per-sample step)",
     "TADNN_MP_AUTOFUSE": "0 = a Sequential of MP* layers keeps its per-layer kernels instead of fusing itself",

@@ -139,8 +139,10 @@ struct Conv1sArgs {
 
 // ======================================= forward =======================================
 // A tile = 6 conv rows (2 pooled rows, N = 96 positions) or conv rows 24..26 (N = 48): 5 tiles per image, 8 MMAs each.
-// Four accumulator stages of 128 TMEM columns, one per epilogue group (4 warps = the 128 accumulator lanes): with
-// 16 epilogue warps every scheduler has four of them to hide tcgen05.ld and shared-memory latency behind.
+// Tensor memory: four accumulator stages of 96 columns, one per epilogue group (4 warps = the 128 accumulator lanes; with
+// 16 epilogue warps every scheduler has four of them to hide tcgen05.ld and shared-memory latency behind), then 64
+// columns that hold the weight operand for the whole kernel (the MMAs take A from tensor memory: with A in shared
+// memory an N = 96 MMA is bound by the operand port at 56 cycles instead of 48, tools/experiments/umma_rate.cu).
 constexpr int kSlots = 8;                     // staged images
 constexpr int kGroups = 4;
 constexpr int kTilesPerImg = 5;
